@@ -1,0 +1,571 @@
+// Scene definitions shared by the product host API (rtc::) and the oracle (orc::).
+//
+// Each function is a template over an API bundle `A` exposing the reference crate's builder
+// names (Matrix, Vector, Color, Material, Pattern, Noise, Element, ShapeArgs, GroupKind,
+// PointLight, World, Camera, ObjData, ObjParser).  The bodies transcribe the PARAMETERS of
+// the reference's example binaries' construct_world() (cited per scene) — scene data, not
+// algorithm — so that the CUDA path and the oracle are fed the same scene through two
+// independent builder implementations.  Resolution is an argument because every bin
+// hard-codes its own.
+#pragma once
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+namespace scenes {
+
+constexpr double PI = 3.14159265358979323846264338327950288;  // std::f64::consts::PI
+
+inline std::string& data_dir() {
+    static std::string d = "data";
+    return d;
+}
+
+// Binary mesh fixture written by tools/make_mesh_fixture.py from an OBJ file:
+//   "RTCMESH1" | u32 nv, nvn, ntri, ngroups | nv*3 f64 | nvn*3 f64 |
+//   ntri * (u32 p1,p2,p3,n1,n2,n3 (1-based; n = 0 when absent), u32 group) | ngroups * (u32 len, bytes)
+template <class A>
+typename A::ObjData load_mesh_fixture(const std::string& path) {
+    std::ifstream in(path, std::ios::binary);
+    if (!in) throw std::runtime_error("scenes: cannot open mesh fixture " + path);
+    char magic[8];
+    in.read(magic, 8);
+    if (std::memcmp(magic, "RTCMESH1", 8) != 0) throw std::runtime_error("scenes: bad mesh fixture magic in " + path);
+    uint32_t hdr[4];
+    in.read((char*)hdr, sizeof hdr);
+    typename A::ObjData d;
+    std::vector<double> buf(3 * (size_t)hdr[0]);
+    in.read((char*)buf.data(), buf.size() * 8);
+    for (uint32_t i = 0; i < hdr[0]; i++) d.vertices.push_back(A::Vector::point(buf[3 * i], buf[3 * i + 1], buf[3 * i + 2]));
+    buf.resize(3 * (size_t)hdr[1]);
+    in.read((char*)buf.data(), buf.size() * 8);
+    for (uint32_t i = 0; i < hdr[1]; i++) d.normals.push_back(A::Vector::vector(buf[3 * i], buf[3 * i + 1], buf[3 * i + 2]));
+    for (uint32_t i = 0; i < hdr[2]; i++) {
+        uint32_t r[7];
+        in.read((char*)r, sizeof r);
+        typename A::ObjData::Tri t;
+        for (int c = 0; c < 3; c++) { t.p[c] = r[c]; t.n[c] = r[3 + c]; }
+        t.has_n = r[3] && r[4] && r[5];
+        t.group = r[6];
+        d.triangles.push_back(t);
+    }
+    for (uint32_t g = 0; g < hdr[3]; g++) {
+        uint32_t len;
+        in.read((char*)&len, 4);
+        std::string name(len, '\0');
+        in.read(name.data(), len);
+        d.groups.push_back(name);
+    }
+    if (!in) throw std::runtime_error("scenes: truncated mesh fixture " + path);
+    return d;
+}
+
+template <class A>
+struct Scene {
+    typename A::Camera camera;
+    typename A::World world;
+};
+
+// --- C1a: World::default() with the camera of the reference's only end-to-end test ---------
+// src/world.rs:152-183, src/image.rs:130-137 (11x11, fov pi/2, from (0,0,-5) to origin, up +y)
+template <class A>
+Scene<A> default_world(size_t hsize, size_t vsize) {
+    using V = typename A::Vector;
+    Scene<A> s;
+    s.world = A::World::default_world();
+    s.camera = A::Camera::make(hsize, vsize, PI / 2.0,
+                               A::Camera::transform(V::point(0.0, 0.0, -5.0), V::point(0.0, 0.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- C1b: authored "three spheres + plane floor + one light" (no chapter-7 bin exists) ------
+template <class A>
+Scene<A> three_spheres(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    typename A::ShapeArgs floor;
+    floor.material.pattern = P::plain(C::make(1.0, 0.9, 0.9));
+    floor.material.specular = 0.0;
+    typename A::ShapeArgs middle;
+    middle.transform = M::translation(-0.5, 1.0, 0.5);
+    middle.material.pattern = P::plain(C::make(0.1, 1.0, 0.5));
+    middle.material.diffuse = 0.7;
+    middle.material.specular = 0.3;
+    typename A::ShapeArgs right;
+    right.transform = M::translation(1.5, 0.5, -0.5) * M::scaling(0.5, 0.5, 0.5);
+    right.material.pattern = P::plain(C::make(0.5, 1.0, 0.1));
+    right.material.diffuse = 0.7;
+    right.material.specular = 0.3;
+    typename A::ShapeArgs left;
+    left.transform = M::translation(-1.5, 0.33, -0.75) * M::scaling(0.33, 0.33, 0.33);
+    left.material.pattern = P::plain(C::make(1.0, 0.8, 0.1));
+    left.material.diffuse = 0.7;
+    left.material.specular = 0.3;
+    s.world.lights.push_back({C::white(), V::point(-10.0, 10.0, -10.0)});
+    s.world.elements.push_back(E::plane(floor));
+    s.world.elements.push_back(E::sphere(middle));
+    s.world.elements.push_back(E::sphere(right));
+    s.world.elements.push_back(E::sphere(left));
+    s.camera = A::Camera::make(hsize, vsize, PI / 3.0,
+                               A::Camera::transform(V::point(0.0, 1.5, -5.0), V::point(0.0, 1.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- C2: src/bin/chapter11_glass_air_bubble.rs:15-77 (native 4096x4096) ---------------------
+template <class A>
+Scene<A> glass_air_bubble(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    typename A::ShapeArgs floor;
+    floor.transform = M::translation(0.0, -10.0, 0.0);
+    floor.material.pattern = P::checkers(M::id(), P::plain(C::white()), P::plain(C::black()));
+    floor.material.specular = 0.0;
+    typename A::ShapeArgs glass;
+    glass.material.pattern = P::plain(C::black());
+    glass.material.diffuse = 0.1;
+    glass.material.shininess = 300.0;
+    glass.material.reflective = 1.0;
+    glass.material.transparency = 1.0;
+    glass.material.refractive_index = 1.52;
+    typename A::ShapeArgs air = glass;
+    air.transform = M::scaling(0.5, 0.5, 0.5);
+    air.material.refractive_index = 1.0;
+    s.world.lights.push_back({C::make(0.7, 0.7, 0.7), V::point(20.0, 10.0, 0.0)});
+    s.world.elements.push_back(E::plane(floor));
+    s.world.elements.push_back(E::sphere(glass));
+    s.world.elements.push_back(E::sphere(air));
+    s.camera = A::Camera::make(hsize, vsize, PI / 3.0,
+                               A::Camera::transform(V::point(0.0, 2.5, 0.0), V::point(0.0, 0.0, 0.0), V::vector(0.0, 0.0, 1.0)));
+    return s;
+}
+
+// --- C3a: src/bin/chapter14_hexagon.rs:16-89 (native 4096x2160) -----------------------------
+template <class A>
+Scene<A> hexagon(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    typename A::Material material;
+    material.pattern = P::point_jitter(
+        A::Noise::Simplex(0.3),
+        P::stripes(M::rotation_z(PI / 2.0) * M::scaling(0.05, 0.05, 0.05), P::plain(C::white()), P::plain(C::black())));
+    std::vector<E> sides;
+    for (int n = 0; n < 6; n++) {
+        typename A::ShapeArgs corner;
+        corner.transform = M::translation(0.0, 0.0, -1.0) * M::scaling(0.25, 0.25, 0.25);
+        typename A::ShapeArgs edge;
+        edge.transform = M::translation(0.0, 0.0, -1.0) * M::rotation_y(-PI / 6.0) * M::rotation_z(-PI / 2.0) *
+                         M::scaling(0.25, 1.0, 0.25);
+        std::vector<E> side;
+        side.push_back(E::sphere(corner));
+        side.push_back(E::cylinder(edge, 0.0, 1.0, false));
+        sides.push_back(E::composite(M::rotation_y((double)n * PI / 3.0), std::nullopt, G::Aggregation, std::move(side)));
+    }
+    s.world.lights.push_back({C::white(), V::point(1.0, 6.9, -4.9)});
+    s.world.elements.push_back(E::composite(M::id(), material, G::Aggregation, std::move(sides)));
+    s.camera = A::Camera::make(hsize, vsize, 0.314,
+                               A::Camera::transform(V::point(8.0, 5.0, 8.0), V::point(0.0, 0.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- C3b: src/bin/chapter14_benchmark.rs:15-109 (native 4096x2160) --------------------------
+template <class A>
+Scene<A> benchmark(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto sphere_block = [](size_t n, double h) {
+        std::vector<E> elements;
+        for (size_t x = 0; x < n; x++)
+            for (size_t z = 0; z < n; z++)
+                for (size_t y = 0; y < n; y++) {
+                    typename A::ShapeArgs a;
+                    a.transform = M::translation(0.1 + (double)x * h, 0.1 + (double)y * h, 0.1 + (double)z * h) *
+                                  M::scaling(0.1, 0.1, 0.1);
+                    a.material.pattern = P::plain(C::black());
+                    elements.push_back(E::sphere(a));
+                }
+        return elements;
+    };
+    typename A::ShapeArgs backdrop;
+    backdrop.material.pattern = P::plain(C::white());
+    backdrop.material.specular = 0.0;
+    const size_t n = 5;
+    const double h = 0.3;
+    std::vector<E> spheres;
+    const double offset = (double)(n - 1) * (0.1 + h) - 0.1;
+    for (int x = 0; x < 2; x++)
+        for (int z = 0; z < 2; z++)
+            for (int y = 0; y < 2; y++)
+                spheres.push_back(E::composite(M::translation((double)x * offset, (double)y * offset, (double)z * offset),
+                                               std::nullopt, G::Aggregation, sphere_block(n, h)));
+    typename A::Material material;
+    material.pattern = P::gradient(M::scaling(1.0, 2.9, 1.0) * M::rotation_z(PI / 2.0), P::plain(C::make(1.0, 0.0, 0.0)),
+                                   P::plain(C::make(0.0, 0.0, 1.0)));
+    s.world.lights.push_back({C::white(), V::point(-5.0, 7.0, -1.0)});
+    s.world.elements.push_back(E::plane(backdrop));
+    s.world.elements.push_back(E::composite(M::id(), material, G::Aggregation, std::move(spheres)));
+    s.camera = A::Camera::make(hsize, vsize, 1.0,
+                               A::Camera::transform(V::point(-8.0, 8.0, -8.0), V::point(2.0, 2.0, 2.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- C4: src/bin/chapter15_teapot.rs:16-92 (native 4096x2160; mesh = obj/teapot_high.obj) ---
+template <class A>
+Scene<A> teapot_from(const typename A::ObjData& mesh, size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    typename A::Material pot;
+    pot.pattern = P::plain(C::make(0.7, 0.7, 1.0));
+    pot.ambient = 0.1;
+    pot.diffuse = 0.6;
+    pot.specular = 0.4;
+    pot.reflective = 0.1;
+    pot.shininess = 5.0;
+    E teapot = A::ObjParser::build(mesh, M::rotation_x(-PI / 2.0), pot);
+    typename A::Material material;
+    material.pattern = P::plain(C::black());
+    material.ambient = 0.02;
+    material.diffuse = 0.7;
+    material.specular = 0.0;
+    material.reflective = 0.5;
+    typename A::ShapeArgs floor;
+    floor.material = material;
+    typename A::ShapeArgs left_wall;
+    left_wall.material = material;
+    left_wall.transform = M::rotation_y(-PI / 4.0) * M::translation(0.0, 0.0, 30.0) * M::rotation_x(PI / 2.0);
+    typename A::ShapeArgs right_wall;
+    right_wall.material = material;
+    right_wall.transform = M::rotation_y(PI / 4.0) * M::translation(0.0, 0.0, 30.0) * M::rotation_x(PI / 2.0);
+    s.world.elements.push_back(E::plane(floor));
+    s.world.elements.push_back(E::plane(left_wall));
+    s.world.elements.push_back(E::plane(right_wall));
+    s.world.elements.push_back(std::move(teapot));
+    s.world.lights.push_back({C::make(0.7, 0.7, 0.7), V::point(-100.0, 100.0, -100.0)});
+    s.world.lights.push_back({C::make(0.7, 0.7, 0.7), V::point(100.0, 100.0, -100.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.4,
+                               A::Camera::transform(V::point(0.0, 30.0, -50.0), V::point(0.0, 0.0, 10.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+template <class A>
+Scene<A> teapot(size_t hsize, size_t vsize) {
+    return teapot_from<A>(load_mesh_fixture<A>(data_dir() + "/teapot_high.mesh"), hsize, vsize);
+}
+template <class A>
+Scene<A> teapot_low(size_t hsize, size_t vsize) {
+    return teapot_from<A>(load_mesh_fixture<A>(data_dir() + "/teapot_low.mesh"), hsize, vsize);
+}
+
+// --- C5: authored CSG + Simplex/fractal-noise scene (no such bin exists) --------
+// Nested CSG (difference of (cube ∩ sphere) and a union of three cylinders), a glass CSG lens,
+// a cone∪sphere, every Mixture kind and both Jitter kinds with Noise::Simplex and Noise::Fractal.
+template <class A>
+Scene<A> csg_noise(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    using N = typename A::Noise;
+    Scene<A> s;
+
+    // floor: checkers of (jittered rings, fractal-jittered gradient)
+    typename A::ShapeArgs floor;
+    floor.material.pattern = P::checkers(
+        M::scaling(2.0, 2.0, 2.0),
+        P::point_jitter(N::Simplex(0.15), P::ring(M::scaling(0.2, 0.2, 0.2), P::plain(C::make(0.9, 0.85, 0.7)), P::plain(C::make(0.3, 0.25, 0.2)))),
+        P::point_jitter(N::Fractal(0.4, 4), P::gradient(M::rotation_y(0.5), P::plain(C::make(0.2, 0.3, 0.6)), P::plain(C::make(0.8, 0.9, 1.0)))));
+    floor.material.specular = 0.1;
+    floor.material.reflective = 0.15;
+
+    // back wall: blend of stripes and ring-gradient, colour-jittered
+    typename A::ShapeArgs wall;
+    wall.transform = M::translation(0.0, 0.0, 9.0) * M::rotation_x(PI / 2.0);
+    wall.material.pattern = P::color_jitter(
+        N::Fractal(0.08, 3),
+        P::blend(M::id(), P::stripes(M::scaling(0.5, 0.5, 0.5) * M::rotation_y(0.3), P::plain(C::make(0.7, 0.2, 0.2)), P::plain(C::make(0.9, 0.8, 0.3))),
+                 P::ring_gradient(M::scaling(1.5, 1.5, 1.5), P::plain(C::make(0.1, 0.4, 0.3)), P::plain(C::make(0.9, 0.9, 0.9)))));
+    wall.material.specular = 0.0;
+
+    // classic CSG: (cube ∩ sphere) − (cylX ∪ cylY ∪ cylZ)
+    typename A::ShapeArgs cube;
+    cube.material.pattern = P::color_jitter(N::Simplex(0.1), P::stripes(M::scaling(0.25, 0.25, 0.25), P::plain(C::make(0.85, 0.3, 0.2)), P::plain(C::make(0.95, 0.8, 0.6))));
+    cube.material.reflective = 0.2;
+    typename A::ShapeArgs ball;
+    ball.transform = M::scaling(1.35, 1.35, 1.35);
+    ball.material.pattern = P::plain(C::make(0.2, 0.3, 0.8));
+    ball.material.shininess = 50.0;
+    auto cyl = [](const typename A::Matrix& t, const typename A::Color& c) {
+        typename A::ShapeArgs a;
+        a.transform = t * M::scaling(0.6, 1.0, 0.6);
+        a.material.pattern = P::plain(c);
+        return E::cylinder(a, -1.5, 1.5, true);
+    };
+    std::vector<E> cxy;
+    cxy.push_back(cyl(M::rotation_z(PI / 2.0), C::make(0.9, 0.1, 0.1)));
+    cxy.push_back(cyl(M::id(), C::make(0.1, 0.9, 0.1)));
+    std::vector<E> cxyz;
+    cxyz.push_back(E::composite(M::id(), std::nullopt, G::Union, std::move(cxy)));
+    cxyz.push_back(cyl(M::rotation_x(PI / 2.0), C::make(0.1, 0.1, 0.9)));
+    std::vector<E> body;
+    body.push_back(E::cube(cube));
+    body.push_back(E::sphere(ball));
+    std::vector<E> diff;
+    diff.push_back(E::composite(M::id(), std::nullopt, G::Intersection, std::move(body)));
+    diff.push_back(E::composite(M::id(), std::nullopt, G::Union, std::move(cxyz)));
+    E classic = E::composite(M::translation(-2.2, 1.35, 0.5) * M::rotation_y(0.6) * M::rotation_x(-0.3), std::nullopt, G::Difference, std::move(diff));
+
+    // glass lens: intersection of two offset spheres (transparent + reflective -> Schlick + containers)
+    typename A::Material glass;
+    glass.pattern = P::plain(C::make(0.05, 0.05, 0.08));
+    glass.diffuse = 0.1;
+    glass.ambient = 0.05;
+    glass.shininess = 300.0;
+    glass.reflective = 0.5;
+    glass.transparency = 0.5;
+    glass.refractive_index = 1.52;
+    typename A::ShapeArgs l1;
+    l1.transform = M::translation(0.0, 0.0, -0.6);
+    typename A::ShapeArgs l2;
+    l2.transform = M::translation(0.0, 0.0, 0.6);
+    std::vector<E> lens_parts;
+    lens_parts.push_back(E::sphere(l1));
+    lens_parts.push_back(E::sphere(l2));
+    E lens = E::composite(M::translation(1.0, 1.3, -2.0) * M::rotation_y(-0.4) * M::scaling(1.3, 1.3, 1.3), glass, G::Intersection, std::move(lens_parts));
+
+    // cone ∪ sphere inside a plain group with its own transform (CSG under Aggregation)
+    typename A::ShapeArgs cone;
+    cone.transform = M::translation(0.0, 1.0, 0.0);
+    cone.material.pattern = P::point_jitter(N::Fractal(0.25, 5), P::checkers(M::scaling(0.3, 0.3, 0.3), P::plain(C::make(0.9, 0.6, 0.1)), P::plain(C::make(0.2, 0.1, 0.4))));
+    typename A::ShapeArgs top;
+    top.transform = M::translation(0.0, 1.2, 0.0) * M::scaling(0.55, 0.55, 0.55);
+    top.material.pattern = P::ring_gradient(M::scaling(0.2, 0.2, 0.2), P::plain(C::make(0.9, 0.9, 0.2)), P::plain(C::make(0.1, 0.5, 0.5)));
+    top.material.reflective = 0.3;
+    std::vector<E> cs;
+    cs.push_back(E::cone(cone, -1.0, 0.0, true));
+    cs.push_back(E::sphere(top));
+    std::vector<E> grp;
+    grp.push_back(E::composite(M::id(), std::nullopt, G::Union, std::move(cs)));
+    typename A::ShapeArgs pedestal;
+    pedestal.transform = M::translation(0.0, -0.25, 0.0) * M::scaling(0.9, 0.25, 0.9);
+    pedestal.material.pattern = P::plain(C::make(0.6, 0.6, 0.65));
+    grp.push_back(E::cube(pedestal));
+    E tower = E::composite(M::translation(3.4, 0.5, 1.5) * M::rotation_y(0.8) * M::scaling(1.2, 1.2, 1.2), std::nullopt, G::Aggregation, std::move(grp));
+
+    s.world.lights.push_back({C::make(0.8, 0.8, 0.8), V::point(-6.0, 9.0, -8.0)});
+    s.world.lights.push_back({C::make(0.35, 0.35, 0.4), V::point(7.0, 5.0, -6.0)});
+    s.world.elements.push_back(E::plane(floor));
+    s.world.elements.push_back(E::plane(wall));
+    s.world.elements.push_back(std::move(classic));
+    s.world.elements.push_back(std::move(lens));
+    s.world.elements.push_back(std::move(tower));
+    s.camera = A::Camera::make(hsize, vsize, 0.9,
+                               A::Camera::transform(V::point(0.5, 3.2, -9.0), V::point(0.3, 1.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- fuzz: seeded random scenes covering every primitive / pattern / group kind --------------
+struct Rng {  // splitmix64 — identical stream for both API instantiations
+    uint64_t s;
+    explicit Rng(uint64_t seed) : s(seed) {}
+    uint64_t next() {
+        uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    double uni() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); }
+    double range(double a, double b) { return a + (b - a) * uni(); }
+    int below(int n) { return (int)(next() % (uint64_t)n); }
+    bool chance(double p) { return uni() < p; }
+    // three draws in a guaranteed order (function-argument evaluation order is unspecified in C++)
+    struct D3 { double a, b, c; };
+    D3 d3(double a0, double a1, double b0, double b1, double c0, double c1) {
+        D3 d;
+        d.a = range(a0, a1);
+        d.b = range(b0, b1);
+        d.c = range(c0, c1);
+        return d;
+    }
+};
+
+template <class A>
+typename A::Color fuzz_color(Rng& r) {
+    Rng::D3 d = r.d3(0.05, 1.0, 0.05, 1.0, 0.05, 1.0);
+    return A::Color::make(d.a, d.b, d.c);
+}
+
+template <class A>
+typename A::Matrix fuzz_small_transform(Rng& r) {
+    using M = typename A::Matrix;
+    Rng::D3 sc = r.d3(0.15, 1.5, 0.15, 1.5, 0.15, 1.5);
+    M m = M::scaling(sc.a, sc.b, sc.c);
+    if (r.chance(0.5)) m = M::rotation_y(r.range(-3.0, 3.0)) * m;
+    if (r.chance(0.3)) m = M::rotation_z(r.range(-1.0, 1.0)) * m;
+    if (r.chance(0.2)) {
+        Rng::D3 sh = r.d3(-0.3, 0.3, -0.3, 0.3, 0.0, 0.0);
+        m = M::shearing(sh.a, 0.0, 0.0, sh.b, 0.0, 0.0) * m;
+    }
+    return m;
+}
+
+template <class A>
+typename A::Pattern fuzz_pattern(Rng& r, int depth) {
+    using P = typename A::Pattern; using N = typename A::Noise;
+    if (depth <= 0 || r.chance(0.35)) return P::plain(fuzz_color<A>(r));
+    int k = r.below(8);
+    if (k < 6) {
+        typename A::Matrix t = fuzz_small_transform<A>(r);
+        P l = fuzz_pattern<A>(r, depth - 1);
+        P rr = fuzz_pattern<A>(r, depth - 1);
+        switch (k) {
+            case 0: return P::blend(t, l, rr);
+            case 1: return P::checkers(t, l, rr);
+            case 2: return P::ring_gradient(t, l, rr);
+            case 3: return P::ring(t, l, rr);
+            case 4: return P::gradient(t, l, rr);
+            default: return P::stripes(t, l, rr);
+        }
+    }
+    bool simplex = r.chance(0.5);
+    double nscale = r.range(0.05, 0.5);
+    size_t octaves = (size_t)(1 + r.below(4));
+    typename A::Noise n = simplex ? N::Simplex(nscale) : N::Fractal(nscale, octaves);
+    if (k == 6) return P::color_jitter(n, fuzz_pattern<A>(r, depth - 1));
+    return P::point_jitter(n, fuzz_pattern<A>(r, depth - 1));
+}
+
+template <class A>
+typename A::Material fuzz_material(Rng& r) {
+    typename A::Material m;
+    m.pattern = fuzz_pattern<A>(r, 3);
+    m.ambient = r.range(0.0, 0.3);
+    m.diffuse = r.range(0.2, 0.9);
+    m.specular = r.chance(0.3) ? 0.0 : r.range(0.1, 0.9);
+    m.shininess = r.range(5.0, 300.0);
+    if (r.chance(0.35)) m.reflective = r.range(0.1, 1.0);
+    if (r.chance(0.25)) {
+        m.transparency = r.range(0.2, 1.0);
+        m.refractive_index = r.range(1.0, 2.4);
+    }
+    return m;
+}
+
+template <class A>
+typename A::Element fuzz_primitive(Rng& r, double spread) {
+    using M = typename A::Matrix; using V = typename A::Vector; using E = typename A::Element;
+    typename A::ShapeArgs a;
+    Rng::D3 tr = r.d3(-spread, spread, 0.0, spread, -spread, spread);
+    typename A::Matrix local = fuzz_small_transform<A>(r);
+    a.transform = M::translation(tr.a, tr.b, tr.c) * local;
+    a.material = fuzz_material<A>(r);
+    a.casts_shadow = !r.chance(0.1);
+    switch (r.below(7)) {
+        case 0: return E::sphere(a);
+        case 1: return E::cube(a);
+        case 2: { double lo = r.range(-1.5, 0.0); double len = r.range(0.3, 2.0); bool closed = r.chance(0.6); return E::cylinder(a, lo, lo + len, closed); }
+        case 3: { double lo = r.range(-1.2, 0.0); double len = r.range(0.3, 1.5); bool closed = r.chance(0.6); return E::cone(a, lo, lo + len, closed); }
+        case 4: {
+            Rng::D3 q1 = r.d3(-1, 1, -1, 1, -1, 1), q2 = r.d3(-1, 1, -1, 1, -1, 1), q3 = r.d3(-1, 1, -1, 1, -1, 1);
+            V p1 = V::point(q1.a, q1.b, q1.c);
+            V p2 = V::point(q2.a, q2.b, q2.c);
+            V p3 = V::point(q3.a, q3.b, q3.c);
+            return E::triangle(a, p1, p2, p3);
+        }
+        case 5: {
+            Rng::D3 q1 = r.d3(-1, 1, -1, 1, -1, 1), q2 = r.d3(-1, 1, -1, 1, -1, 1), q3 = r.d3(-1, 1, -1, 1, -1, 1);
+            V p1 = V::point(q1.a, q1.b, q1.c);
+            V p2 = V::point(q2.a, q2.b, q2.c);
+            V p3 = V::point(q3.a, q3.b, q3.c);
+            Rng::D3 m1 = r.d3(-1, 1, 0.2, 1, -1, 1), m2 = r.d3(-1, 1, 0.2, 1, -1, 1), m3 = r.d3(-1, 1, 0.2, 1, -1, 1);
+            V n1 = V::vector(m1.a, m1.b, m1.c).normalize();
+            V n2 = V::vector(m2.a, m2.b, m2.c).normalize();
+            V n3 = V::vector(m3.a, m3.b, m3.c).normalize();
+            return E::smooth_triangle(a, p1, p2, p3, n1, n2, n3);
+        }
+        default: return E::sphere(a);
+    }
+}
+
+template <class A>
+typename A::Element fuzz_element(Rng& r, int depth, double spread) {
+    using M = typename A::Matrix; using E = typename A::Element; using G = typename A::GroupKind;
+    if (depth <= 0 || r.chance(0.55)) return fuzz_primitive<A>(r, spread);
+    Rng::D3 gt = r.d3(-1.0, 1.0, 0.0, 1.0, -1.0, 1.0);
+    double gr = r.range(-3.0, 3.0);
+    M t = M::translation(gt.a, gt.b, gt.c) * M::rotation_y(gr);
+    std::optional<typename A::Material> mat;
+    if (r.chance(0.3)) mat = fuzz_material<A>(r);
+    if (r.chance(0.4)) {  // CSG: exactly two children
+        std::vector<E> c;
+        c.push_back(fuzz_element<A>(r, depth - 1, spread * 0.5));
+        c.push_back(fuzz_element<A>(r, depth - 1, spread * 0.5));
+        G kinds[3] = {G::Union, G::Intersection, G::Difference};
+        int which = r.below(3);
+        return E::composite(t, mat, kinds[which], std::move(c));
+    }
+    std::vector<E> c;
+    int n = 1 + r.below(4);
+    for (int i = 0; i < n; i++) c.push_back(fuzz_element<A>(r, depth - 1, spread * 0.7));
+    return E::composite(t, mat, G::Aggregation, std::move(c));
+}
+
+template <class A>
+Scene<A> fuzz(uint64_t seed, size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using E = typename A::Element;
+    Rng r(seed * 0x2545F4914F6CDD1Dull + 12345);
+    Scene<A> s;
+    int nl = 1 + r.below(3);
+    for (int i = 0; i < nl; i++) {
+        Rng::D3 lc = r.d3(0.3, 1.0, 0.3, 1.0, 0.3, 1.0);
+        Rng::D3 lp = r.d3(-10, 10, 4, 12, -10, -2);
+        s.world.lights.push_back({A::Color::make(lc.a, lc.b, lc.c), V::point(lp.a, lp.b, lp.c)});
+    }
+    if (r.chance(0.8)) {
+        typename A::ShapeArgs floor;
+        floor.material = fuzz_material<A>(r);
+        floor.material.transparency = 0.0;
+        if (r.chance(0.3)) floor.transform = M::translation(0.0, -0.5, 0.0) * M::rotation_x(r.range(-0.1, 0.1));
+        s.world.elements.push_back(E::plane(floor));
+    }
+    int n = 2 + r.below(6);
+    for (int i = 0; i < n; i++) s.world.elements.push_back(fuzz_element<A>(r, 3, 3.0));
+    double fov = r.range(0.6, 1.3);
+    Rng::D3 from = r.d3(-3, 3, 1.5, 5, -9, -6);
+    Rng::D3 to = r.d3(-0.5, 0.5, 0.5, 1.5, 0.0, 0.0);
+    s.camera = A::Camera::make(hsize, vsize, fov,
+                               A::Camera::transform(V::point(from.a, from.b, from.c), V::point(to.a, to.b, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- registry ---------------------------------------------------------------------------------
+inline const std::vector<std::string>& scene_names() {
+    static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
+                                               "benchmark",     "teapot",        "teapot_low",       "csg_noise"};
+    return n;
+}
+
+// name is one of scene_names() or "fuzz:<seed>"
+template <class A>
+Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
+    if (name == "default_world") return default_world<A>(hsize, vsize);
+    if (name == "three_spheres") return three_spheres<A>(hsize, vsize);
+    if (name == "glass_air_bubble") return glass_air_bubble<A>(hsize, vsize);
+    if (name == "hexagon") return hexagon<A>(hsize, vsize);
+    if (name == "benchmark") return benchmark<A>(hsize, vsize);
+    if (name == "teapot") return teapot<A>(hsize, vsize);
+    if (name == "teapot_low") return teapot_low<A>(hsize, vsize);
+    if (name == "csg_noise") return csg_noise<A>(hsize, vsize);
+    if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
+    throw std::runtime_error("scenes: unknown scene '" + name + "'");
+}
+
+}  // namespace scenes
