@@ -1,0 +1,114 @@
+// Harness glue (not part of the C ABI): builds the named scenes of scenes/scenes.hpp through the product's host
+// builder API (raytracer_challenge_b200/host/raytracer.hpp), flattens them and drives include/rtc.h.
+// Loaded from Python (ctypes) by tests/, bench.py and __graft_entry__.py.
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "../raytracer_challenge_b200/host/raytracer.hpp"
+#include "../scenes/scenes.hpp"
+
+namespace {
+struct HostApi {
+    using Matrix = rtc::Matrix;
+    using Vector = rtc::Vector;
+    using Color = rtc::Color;
+    using Noise = rtc::Noise;
+    using Pattern = rtc::Pattern;
+    using Material = rtc::Material;
+    using ShapeArgs = rtc::ShapeArgs;
+    using Element = rtc::Element;
+    using GroupKind = rtc::GroupKind;
+    using PointLight = rtc::PointLight;
+    using World = rtc::World;
+    using Camera = rtc::Camera;
+    using ObjData = rtc::ObjData;
+    using ObjParser = rtc::ObjParser;
+};
+
+struct Session {
+    std::unique_ptr<rtc::FlatScene> flat;
+    rtc_camera camera{};
+    rtc_scene* scene = nullptr;
+};
+
+void set_err(char* err, int errlen, const std::string& m) {
+    if (err && errlen > 0) {
+        std::strncpy(err, m.c_str(), (size_t)errlen - 1);
+        err[errlen - 1] = 0;
+    }
+}
+}  // namespace
+
+extern "C" {
+
+// Builds + flattens the scene on the host.  device >= 0: also uploads it to that GPU.  device < 0: host only
+// (validation through rtc_scene_validate; no GPU touched).
+int drv_open(const char* name, const char* data_dir, int hsize, int vsize, int device, void** out, int64_t* stats16, char* err, int errlen) {
+    try {
+        if (data_dir && *data_dir) scenes::data_dir() = data_dir;
+        auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
+        auto s = std::make_unique<Session>();
+        s->flat = std::make_unique<rtc::FlatScene>(sc.world);
+        s->camera = sc.camera.to_c();
+        const rtc_scene_desc d = s->flat->desc();
+        if (device >= 0) {
+            if (rtc_scene_create(&d, device, &s->scene) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+            if (stats16) for (int k = 0; k < 16; ++k) stats16[k] = rtc_scene_stat(s->scene, k);
+        } else {
+            if (rtc_scene_validate(&d, stats16) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+        }
+        *out = s.release();
+        return 0;
+    } catch (const std::exception& e) {
+        set_err(err, errlen, e.what());
+        return 1;
+    }
+}
+
+void drv_close(void* h) {
+    Session* s = (Session*)h;
+    if (!s) return;
+    if (s->scene) rtc_scene_destroy(s->scene);
+    delete s;
+}
+
+const rtc_scene_desc* drv_desc_tmp(void* h, rtc_scene_desc* storage) {
+    *storage = ((Session*)h)->flat->desc();
+    return storage;
+}
+const rtc_camera* drv_camera(void* h) { return &((Session*)h)->camera; }
+rtc_scene* drv_scene(void* h) { return ((Session*)h)->scene; }
+
+int drv_render(void* h, const rtc_opts* opts, double* out_rgb, rtc_stats* stats, char* err, int errlen) {
+    Session* s = (Session*)h;
+    if (!s || !s->scene) { set_err(err, errlen, "drv_render: scene was opened without a device"); return 1; }
+    if (rtc_render(s->scene, &s->camera, opts, out_rgb, stats) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+    return 0;
+}
+
+int drv_render_device(void* h, const rtc_opts* opts, double** dev, uint64_t* n, rtc_stats* stats, char* err, int errlen) {
+    Session* s = (Session*)h;
+    if (!s || !s->scene) { set_err(err, errlen, "drv_render_device: scene was opened without a device"); return 1; }
+    if (rtc_render_device(s->scene, &s->camera, opts, dev, n, stats) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+    return 0;
+}
+
+// Image::par_render + Image::ppm through the public host API (the path a bin would take): returns the PPM text length.
+int64_t drv_par_render_ppm(const char* name, const char* data_dir, int hsize, int vsize, int device, char* out, int64_t out_cap, char* err, int errlen) {
+    try {
+        if (data_dir && *data_dir) scenes::data_dir() = data_dir;
+        auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
+        rtc::RenderOptions ro;
+        ro.device = device;
+        rtc::Image img = rtc::Image::par_render(sc.camera, sc.world, ro);
+        const std::string ppm = img.ppm();
+        if ((int64_t)ppm.size() <= out_cap) std::memcpy(out, ppm.data(), ppm.size());
+        return (int64_t)ppm.size();
+    } catch (const std::exception& e) {
+        set_err(err, errlen, e.what());
+        return -1;
+    }
+}
+
+}  // extern "C"

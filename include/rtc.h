@@ -1,0 +1,206 @@
+/*
+ * rtc.h — C ABI of the B200-native render path (drop-in boundary for the reference's
+ * `Image::par_render(camera: &Camera, world: &World) -> Image`, /root/reference/src/image.rs:65-81).
+ *
+ * The reference (a pure-Rust crate) has no FFI today; these are the entry points its
+ * `src/image.rs` would bind through `extern "C"` (see INTEGRATION.md for the Rust stub).
+ * Everything crossing the boundary is plain-old-data in host memory: the caller flattens its
+ * `World` (already holding baked per-primitive matrices, src/shape.rs:47-72) into the arrays
+ * below; the library copies what it needs during rtc_scene_create and builds its own device
+ * structures (BVH, SoA tables).  No CPU fallback exists: without a CUDA device every call fails.
+ *
+ * Numeric contract: all reference arithmetic is f64 and so is every parity-critical device
+ * computation; matrices are row-major 4x4 (src/linalg/matrix.rs:7-10) and must be affine
+ * (last row 0 0 0 1), which is all the reference's constructors can produce.
+ */
+#ifndef RTC_H
+#define RTC_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTC_ABI_VERSION 1
+
+/* Geometry kinds: src/shape.rs:465-498 */
+enum rtc_prim_kind {
+    RTC_SPHERE = 0,
+    RTC_PLANE = 1,
+    RTC_CUBE = 2,
+    RTC_CYLINDER = 3,
+    RTC_CONE = 4,
+    RTC_TRIANGLE = 5,
+    RTC_SMOOTH_TRIANGLE = 6
+};
+
+/* Group kinds: src/shape.rs:161-167 */
+enum rtc_group_kind { RTC_UNION = 0, RTC_INTERSECTION = 1, RTC_DIFFERENCE = 2, RTC_AGGREGATION = 3 };
+
+/* Pattern node kinds: src/material.rs:58-65,190-194,226-234 */
+enum rtc_pattern_kind {
+    RTC_PAT_DEBUG = 0,
+    RTC_PAT_PLAIN = 1,
+    RTC_PAT_JITTER_COLOR = 2,
+    RTC_PAT_JITTER_POINT = 3,
+    RTC_PAT_BLEND = 4,
+    RTC_PAT_CHECKERS = 5,
+    RTC_PAT_RING_GRADIENT = 6,
+    RTC_PAT_RING = 7,
+    RTC_PAT_GRADIENT = 8,
+    RTC_PAT_STRIPES = 9
+};
+
+/* Noise kinds: src/noise.rs:4-7 */
+enum rtc_noise_kind { RTC_NOISE_SIMPLEX = 0, RTC_NOISE_FRACTAL = 1 };
+
+/* One primitive = the render-time content of `Shape` (src/shape.rs:296-306) after
+ * propagate_inverses.  Primitives are listed in depth-first order of World.elements. */
+typedef struct rtc_prim {
+    int32_t kind;          /* rtc_prim_kind */
+    int32_t material;      /* index into materials[] */
+    int32_t casts_shadow;  /* src/shape.rs:304 */
+    int32_t closed;        /* cylinder / cone caps */
+    double transform_inv[16];     /* world -> object */
+    double transform_inv_tsp[16]; /* normal matrix */
+    double material_inv[16];      /* world -> pattern space (src/shape.rs:61-70) */
+    double min, max;              /* cylinder / cone y-range */
+    double p1[3], e1[3], e2[3];   /* triangles: as precomputed at src/shape.rs:369-412 */
+    double n1[3], n2[3], n3[3];   /* smooth triangle normals; flat triangle: n in n1 */
+} rtc_prim;
+
+/* One group = `Group` (src/shape.rs:180-185) with its world-space box.  nodes[0] is a virtual
+ * root (kind AGGREGATION, no box gate: World::intersect, src/world.rs:18-24) whose children are
+ * World.elements.  children[first_child .. first_child+n_children): value >= 0 is a primitive
+ * index, value < 0 is ~node_index. */
+typedef struct rtc_node {
+    int32_t kind; /* rtc_group_kind */
+    int32_t first_child;
+    int32_t n_children;
+    int32_t reserved;
+    double bbox_min[3];
+    double bbox_max[3];
+} rtc_node;
+
+/* `Material` (src/material.rs:18-28) */
+typedef struct rtc_material {
+    double ambient, diffuse, specular, shininess, reflective, transparency, refractive_index;
+    int32_t pattern; /* root index into patterns[] */
+    int32_t reserved;
+} rtc_material;
+
+/* One node of a `Pattern` tree (src/material.rs:58-65) */
+typedef struct rtc_pattern {
+    int32_t kind;       /* rtc_pattern_kind */
+    int32_t left;       /* Mixture: left child; Jitter: the inner pattern */
+    int32_t right;      /* Mixture: right child */
+    int32_t noise_kind; /* Jitter: rtc_noise_kind */
+    int32_t octaves;    /* Jitter with fractal noise */
+    int32_t reserved;
+    double noise_scale;
+    double color[3];          /* Plain */
+    double transform_inv[16]; /* Mixture */
+} rtc_pattern;
+
+/* `PointLight` (src/light.rs:4-8) */
+typedef struct rtc_light {
+    double intensity[3];
+    double origin[3];
+} rtc_light;
+
+typedef struct rtc_scene_desc {
+    int32_t abi_version; /* RTC_ABI_VERSION */
+    int32_t n_prims, n_nodes, n_children, n_materials, n_patterns, n_lights;
+    const rtc_prim* prims;
+    const rtc_node* nodes;
+    const int32_t* children;
+    const rtc_material* materials;
+    const rtc_pattern* patterns;
+    const rtc_light* lights;
+} rtc_scene_desc;
+
+/* The six values `Camera::ray_at_pixel` reads (src/camera.rs:5-13,39-55) */
+typedef struct rtc_camera {
+    int32_t hsize, vsize;
+    double transform_inv[16];
+    double pixel_size, half_width, half_height;
+} rtc_camera;
+
+#define RTC_FLAG_BRUTE_FORCE 1u /* test every primitive for every ray (no BVH culling); validation only */
+
+typedef struct rtc_opts {
+    int32_t fuel;          /* src/config.rs:2 (FUEL = 5) */
+    int32_t spp_x, spp_y;  /* supersampling grid; 1x1 = the reference's single centre ray */
+    int32_t shard_index;   /* this call renders tiles t with t % shard_count == shard_index */
+    int32_t shard_count;   /* 1 = whole image */
+    int32_t tile_w, tile_h;/* shard tile size in pixels (0 -> 8x4) */
+    uint32_t flags;
+    int32_t win_x0, win_y0, win_w, win_h; /* render only this window of the camera image (0,0,0,0 = all) */
+} rtc_opts;
+
+typedef struct rtc_stats {
+    uint64_t rays_primary, rays_shadow, rays_reflected, rays_refracted; /* R_uniq: rays actually traced */
+    uint64_t rays_ref;       /* R_ref: World::intersect queries the reference would issue for the same image */
+    uint64_t kernel_launches;
+    uint64_t pixels;         /* pixels produced by this call (shard) */
+    double ms_total;         /* rtc_render entry -> last pixel in host memory */
+    double ms_kernels;       /* CUDA-event time of all kernels of this call */
+    double ms_trace_shade;   /* CUDA-event time of the wavefront kernels only */
+    double ms_d2h;           /* device -> host copy */
+    int32_t overflow;        /* non-zero: an on-chip list overflowed; result invalid (call fails) */
+    int32_t reserved;
+} rtc_stats;
+
+typedef struct rtc_scene rtc_scene;
+
+/* Number of CUDA devices visible (0 or negative status on failure -> rtc_last_error). */
+int rtc_device_count(void);
+
+/* Copies and uploads the scene to CUDA device `device`, building the BVH.  0 = ok. */
+int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
+
+void rtc_scene_destroy(rtc_scene* scene);
+
+/* Blocking render into caller-allocated host memory: out_rgb holds one (r,g,b) f64 triple per
+ * output slot (see rtc_shard_pixels; shard_count == 1: the whole window row-major, `y*w + x`, like
+ * Image.pixels, src/image.rs:114-116).
+ * Replaces the body of Image::par_render (src/image.rs:65-81).  0 = ok. */
+int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* out_rgb, rtc_stats* stats);
+
+/* Same, but leaves the result in device memory owned by the scene (valid until the next render
+ * or destroy); *out_dev_rgb receives the device pointer (f64 triples), *out_pixels the count. */
+int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double** out_dev_rgb,
+                      uint64_t* out_pixels, rtc_stats* stats);
+
+/* Output slots of shard (shard_index, shard_count) of a w x h window.  The window is cut into tile_w x tile_h
+ * tiles (default 8x4, numbered row-major); shard i owns tiles i, i+shard_count, ...; its output lists the owned
+ * tiles in ascending order, each tile row-major and FULL size: slots that fall outside the window (partial edge
+ * tiles) are padding.  Returns the slot count; if out_indices != NULL it receives, per slot, the linear window
+ * index y*w+x of the pixel or 0xffffffff for padding.  With shard_count == 1 rtc_render instead returns the plain
+ * row-major window (w*h pixels, no padding).  Host-side helper; needs no GPU. */
+uint64_t rtc_shard_pixels(int32_t w, int32_t h, int32_t tile_w, int32_t tile_h, int32_t shard_index, int32_t shard_count,
+                          uint32_t* out_indices);
+
+/* `Color::clamp` (src/color.rs:42-46) applied to n doubles -> n bytes, on the host. */
+void rtc_quantize(const double* rgb, uint8_t* out, uint64_t n);
+
+/* Scene build facts (rtc_scene_stat keys). */
+enum rtc_stat_key {
+    RTC_STAT_PRIMS = 0, RTC_STAT_BVH_NODES = 1, RTC_STAT_BVH_DEPTH = 2, RTC_STAT_UNBOUNDED = 3,
+    RTC_STAT_GATES_EXACT = 4, RTC_STAT_GATES_CONSERVATIVE = 5, RTC_STAT_GATES_ALWAYS_PASS = 6,
+    RTC_STAT_CSG_ROOTS = 7, RTC_STAT_XFORMS = 8, RTC_STAT_FEATURES = 9, RTC_STAT_BVH_ITEMS = 10
+};
+int64_t rtc_scene_stat(const rtc_scene* scene, int key);
+
+/* Runs the host half of scene upload only (validation, flattening, BVH build) — no GPU needed.  0 = the
+ * scene would be accepted; stats (optional, 16 entries indexed by rtc_stat_key) are filled on success. */
+int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16);
+
+/* Thread-local message for the last non-zero status. */
+const char* rtc_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTC_H */

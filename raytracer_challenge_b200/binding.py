@@ -1,0 +1,184 @@
+"""ctypes bindings over include/rtc.h (librtc.so) and the scene harness (librtc_driver.so).
+
+No CPU fallback: if the CUDA library is missing or no device is visible, rendering raises RtcError.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_DIR = os.path.join(ROOT, "raytracer_challenge_b200", "lib")
+DATA_DIR = os.path.join(ROOT, "data")
+SCENES = ["default_world", "three_spheres", "glass_air_bubble", "hexagon", "benchmark", "teapot", "teapot_low", "csg_noise"]
+
+
+class RtcError(RuntimeError):
+    pass
+
+
+class Opts(C.Structure):  # rtc_opts
+    _fields_ = [("fuel", C.c_int32), ("spp_x", C.c_int32), ("spp_y", C.c_int32), ("shard_index", C.c_int32),
+                ("shard_count", C.c_int32), ("tile_w", C.c_int32), ("tile_h", C.c_int32), ("flags", C.c_uint32),
+                ("win_x0", C.c_int32), ("win_y0", C.c_int32), ("win_w", C.c_int32), ("win_h", C.c_int32)]
+
+    def __init__(self, fuel=5, spp=(1, 1), shard=(0, 1), tile=(0, 0), flags=0, window=None):
+        super().__init__()
+        self.fuel = fuel
+        self.spp_x, self.spp_y = spp
+        self.shard_index, self.shard_count = shard
+        self.tile_w, self.tile_h = tile
+        self.flags = flags
+        if window:
+            self.win_x0, self.win_y0, self.win_w, self.win_h = window
+
+
+class Stats(C.Structure):  # rtc_stats
+    _fields_ = [("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_reflected", C.c_uint64),
+                ("rays_refracted", C.c_uint64), ("rays_ref", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("pixels", C.c_uint64), ("ms_total", C.c_double), ("ms_kernels", C.c_double),
+                ("ms_trace_shade", C.c_double), ("ms_d2h", C.c_double), ("overflow", C.c_int32), ("reserved", C.c_int32)]
+
+    @property
+    def rays(self):
+        return self.rays_primary + self.rays_shadow + self.rays_reflected + self.rays_refracted
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+
+
+STAT_KEYS = ["prims", "bvh_nodes", "bvh_depth", "unbounded", "gates_exact", "gates_conservative", "gates_always_pass",
+             "csg_roots", "xforms", "features", "bvh_items"]
+
+
+def lib_paths():
+    return {"librtc": os.path.join(LIB_DIR, "librtc.so"), "driver": os.path.join(LIB_DIR, "librtc_driver.so"),
+            "oracle": os.path.join(ROOT, "build", "liboracle.so")}
+
+
+_rtc = None
+_drv = None
+
+
+def load_rtc():
+    """Loads the product library; raises if it has not been built (there is no fallback path)."""
+    global _rtc
+    if _rtc is None:
+        path = lib_paths()["librtc"]
+        if not os.path.exists(path):
+            raise RtcError(f"{path} is missing: run `python -m raytracer_challenge_b200._build` (no CPU fallback exists)")
+        lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
+        lib.rtc_last_error.restype = C.c_char_p
+        lib.rtc_device_count.restype = C.c_int
+        lib.rtc_shard_pixels.restype = C.c_uint64
+        lib.rtc_shard_pixels.argtypes = [C.c_int32] * 6 + [C.c_void_p]
+        lib.rtc_quantize.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        lib.rtc_scene_stat.restype = C.c_int64
+        lib.rtc_scene_stat.argtypes = [C.c_void_p, C.c_int]
+        lib.rtc_scene_validate.argtypes = [C.c_void_p, C.c_void_p]
+        lib.rtc_scene_create.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.rtc_scene_destroy.argtypes = [C.c_void_p]
+        lib.rtc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.rtc_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _rtc = lib
+    return _rtc
+
+
+def load_driver():
+    global _drv
+    if _drv is None:
+        load_rtc()
+        path = lib_paths()["driver"]
+        if not os.path.exists(path):
+            raise RtcError(f"{path} is missing: run `python -m raytracer_challenge_b200._build`")
+        lib = C.CDLL(path)
+        lib.drv_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        lib.drv_close.argtypes = [C.c_void_p]
+        lib.drv_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        lib.drv_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        lib.drv_par_render_ppm.restype = C.c_int64
+        lib.drv_par_render_ppm.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
+        lib.drv_scene.restype = C.c_void_p
+        lib.drv_scene.argtypes = [C.c_void_p]
+        lib.drv_camera.restype = C.c_void_p
+        lib.drv_camera.argtypes = [C.c_void_p]
+        _drv = lib
+    return _drv
+
+
+def device_count():
+    return load_rtc().rtc_device_count()
+
+
+def quantize(rgb):
+    """Color::clamp (src/color.rs:42-46) on an array of f64 -> uint8 of the same shape."""
+    a = np.ascontiguousarray(rgb, dtype=np.float64)
+    out = np.empty(a.shape, dtype=np.uint8)
+    load_rtc().rtc_quantize(a.ctypes.data, out.ctypes.data, a.size)
+    return out
+
+
+def shard_pixels(w, h, shard_index, shard_count, tile=(0, 0)):
+    lib = load_rtc()
+    n = lib.rtc_shard_pixels(w, h, tile[0], tile[1], shard_index, shard_count, None)
+    idx = np.empty(n, dtype=np.uint32)
+    lib.rtc_shard_pixels(w, h, tile[0], tile[1], shard_index, shard_count, idx.ctypes.data)
+    return idx
+
+
+class Session:
+    """A named scene (scenes/scenes.hpp) built through the host builder API and, if device >= 0, uploaded."""
+
+    def __init__(self, name, hsize, vsize, device=0, data_dir=DATA_DIR):
+        self.lib = load_driver()
+        self.name, self.hsize, self.vsize, self.device = name, hsize, vsize, device
+        self.handle = C.c_void_p()
+        stats = (C.c_int64 * 16)()
+        err = C.create_string_buffer(1024)
+        rc = self.lib.drv_open(name.encode(), data_dir.encode(), hsize, vsize, device, C.byref(self.handle), stats, err, 1024)
+        if rc != 0:
+            raise RtcError(err.value.decode())
+        self.build_stats = {k: int(stats[i]) for i, k in enumerate(STAT_KEYS)}
+
+    def close(self):
+        if self.handle:
+            self.lib.drv_close(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def out_shape(self, opts):
+        w, h = (opts.win_w, opts.win_h) if opts.win_w > 0 and opts.win_h > 0 else (self.hsize, self.vsize)
+        if opts.shard_count <= 1:
+            return (h, w, 3)
+        n = load_rtc().rtc_shard_pixels(w, h, opts.tile_w, opts.tile_h, opts.shard_index, opts.shard_count, None)
+        return (n, 3)
+
+    def render(self, opts=None, out=None):
+        """rtc_render: host buffer in, host pixels out (f64 rgb).  Returns (image, Stats)."""
+        opts = opts or Opts()
+        shape = self.out_shape(opts)
+        if out is None:
+            out = np.empty(shape, dtype=np.float64)
+        stats = Stats()
+        err = C.create_string_buffer(1024)
+        rc = self.lib.drv_render(self.handle, C.byref(opts), out.ctypes.data, C.byref(stats), err, 1024)
+        if rc != 0:
+            raise RtcError(err.value.decode())
+        return out, stats
+
+    def render_device(self, opts=None):
+        """rtc_render_device: result stays in HBM.  Returns (device pointer, pixel count, Stats)."""
+        opts = opts or Opts()
+        dev = C.c_void_p()
+        n = C.c_uint64()
+        stats = Stats()
+        err = C.create_string_buffer(1024)
+        rc = self.lib.drv_render_device(self.handle, C.byref(opts), C.byref(dev), C.byref(n), C.byref(stats), err, 1024)
+        if rc != 0:
+            raise RtcError(err.value.decode())
+        return dev.value, n.value, stats

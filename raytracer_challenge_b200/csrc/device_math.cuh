@@ -1,0 +1,265 @@
+// Device maths of the render path: f64 vectors, affine transforms and the per-primitive intersectors
+// and normals.  Every parity-critical expression keeps the reference's operation order and the
+// translation unit is compiled with -fmad=false, so no multiply-add is contracted and t, u, v, hit
+// points and normals are bit-identical to the reference's scalar f64 code (division and sqrt are IEEE
+// correctly rounded on the device).
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#include "device_scene.h"
+
+namespace rtcdev {
+
+#define RTC_EPSILON 0.00001  // src/config.rs:1
+
+struct V3 {
+    double x, y, z;
+};
+__device__ __forceinline__ V3 mk(double x, double y, double z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3 operator*(V3 a, double s) { return mk(a.x * s, a.y * s, a.z * s); }
+// src/linalg/vector.rs:39-49
+__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) { return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+// src/linalg/vector.rs:24-37
+__device__ __forceinline__ double magnitude(V3 a) { return sqrt(a.x * a.x + a.y * a.y + a.z * a.z); }
+__device__ __forceinline__ V3 normalize(V3 a) {
+    const double m = magnitude(a);
+    return mk(a.x / m, a.y / m, a.z / m);
+}
+// src/linalg/vector.rs:75-77
+__device__ __forceinline__ V3 reflect(V3 v, V3 n) { return v - n * (2.0 * dot(v, n)); }
+
+// src/linalg/matrix.rs:261-284 restricted to affine matrices: for a point the w-term is m[r][3] * 1.0, for a
+// direction it is m[r][3] * 0.0 (adds a zero), so three products and two / three sums reproduce the 4x4 result.
+__device__ __forceinline__ V3 xf_point(const double* __restrict__ m, V3 p) {
+    return mk(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3], m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7],
+              m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]);
+}
+__device__ __forceinline__ V3 xf_dir(const double* __restrict__ m, V3 d) {
+    return mk(m[0] * d.x + m[1] * d.y + m[2] * d.z, m[4] * d.x + m[5] * d.y + m[6] * d.z, m[8] * d.x + m[9] * d.y + m[10] * d.z);
+}
+__device__ __forceinline__ V3 xf_normal(const double* __restrict__ t, V3 n) {  // 3x3, row-major
+    return mk(t[0] * n.x + t[1] * n.y + t[2] * n.z, t[3] * n.x + t[4] * n.y + t[5] * n.z, t[6] * n.x + t[7] * n.y + t[8] * n.z);
+}
+
+struct Ray {
+    V3 o, d;
+};
+
+// src/approx.rs:19-23 against 0.0
+__device__ __forceinline__ bool approx0(double a) { return fabs(a) < RTC_EPSILON; }
+
+// src/shape.rs:635-653.  fmin/fmax drop a NaN operand exactly like f64::min/max.
+__device__ __forceinline__ void cube_axis(double origin, double direction, double lo, double hi, double& t0, double& t1) {
+    const double n0 = lo - origin, n1 = hi - origin;
+    double a, b;
+    if (fabs(direction) >= RTC_EPSILON) {
+        a = n0 / direction;
+        b = n1 / direction;
+    } else {
+        a = n0 * CUDART_INF;
+        b = n1 * CUDART_INF;
+    }
+    if (a > b) { t0 = b; t1 = a; } else { t0 = a; t1 = b; }
+}
+// src/bounding_box.rs:80-92 (no t-range clipping)
+__device__ __forceinline__ bool box_gate(const Gate& g, const Ray& r) {
+    double x0, x1, y0, y1, z0, z1;
+    cube_axis(r.o.x, r.d.x, g.lo[0], g.hi[0], x0, x1);
+    cube_axis(r.o.y, r.d.y, g.lo[1], g.hi[1], y0, y1);
+    cube_axis(r.o.z, r.d.z, g.lo[2], g.hi[2], z0, z1);
+    return fmax(fmax(x0, y0), z0) <= fmin(fmin(x1, y1), z1);
+}
+
+// Crossings of one primitive with the object-space ray, in the reference's emission order.
+struct Roots {
+    double t[4];
+    int n;
+    double u, v;  // triangles only
+};
+
+// src/shape.rs:592-620
+__device__ __forceinline__ void isect_sphere(const Ray& r, Roots& out) {
+    const double a = dot(r.d, r.d);
+    const double b = 2.0 * dot(r.d, r.o);
+    const double c = dot(r.o, r.o) - 1.0;
+    const double disc = b * b - 4.0 * a * c;
+    if (disc < 0.0) return;
+    const double sq = sqrt(disc);
+    out.t[0] = (-b - sq) / (2.0 * a);
+    out.t[1] = (-b + sq) / (2.0 * a);
+    out.n = 2;
+}
+// src/shape.rs:622-633
+__device__ __forceinline__ void isect_plane(const Ray& r, Roots& out) {
+    if (approx0(r.d.y)) return;
+    out.t[0] = -r.o.y / r.d.y;
+    out.n = 1;
+}
+// src/shape.rs:655-680
+__device__ __forceinline__ void isect_cube(const Ray& r, Roots& out) {
+    double x0, x1, y0, y1, z0, z1;
+    cube_axis(r.o.x, r.d.x, -1.0, 1.0, x0, x1);
+    cube_axis(r.o.y, r.d.y, -1.0, 1.0, y0, y1);
+    cube_axis(r.o.z, r.d.z, -1.0, 1.0, z0, z1);
+    const double tmin = fmax(fmax(x0, y0), z0);
+    const double tmax = fmin(fmin(x1, y1), z1);
+    if (tmin <= tmax) {
+        out.t[0] = tmin;
+        out.t[1] = tmax;
+        out.n = 2;
+    }
+}
+// src/shape.rs:682-722
+__device__ __forceinline__ void isect_caps(const Ray& r, double lo, double hi, double lo_radius, double hi_radius, bool closed, Roots& out) {
+    if (!closed || approx0(r.d.y)) return;
+    double t = (lo - r.o.y) / r.d.y;
+    double x = r.o.x + t * r.d.x, z = r.o.z + t * r.d.z;
+    if ((x * x + z * z) <= lo_radius * lo_radius) out.t[out.n++] = t;
+    t = (hi - r.o.y) / r.d.y;
+    x = r.o.x + t * r.d.x;
+    z = r.o.z + t * r.d.z;
+    if ((x * x + z * z) <= hi_radius * hi_radius) out.t[out.n++] = t;
+}
+// src/shape.rs:724-768
+__device__ __forceinline__ void isect_cylinder(const Ray& r, double lo, double hi, bool closed, Roots& out) {
+    const double a = r.d.x * r.d.x + r.d.z * r.d.z;
+    if (!approx0(a)) {
+        const double b = 2.0 * r.o.x * r.d.x + 2.0 * r.o.z * r.d.z;
+        const double c = r.o.x * r.o.x + r.o.z * r.o.z - 1.0;
+        const double disc = b * b - 4.0 * a * c;
+        if (disc >= 0.0) {
+            const double sq = sqrt(disc);
+            const double t0 = (-b - sq) / (2.0 * a);
+            const double y0 = r.o.y + t0 * r.d.y;
+            if (lo < y0 && y0 < hi) out.t[out.n++] = t0;
+            const double t1 = (-b + sq) / (2.0 * a);
+            const double y1 = r.o.y + t1 * r.d.y;
+            if (lo < y1 && y1 < hi) out.t[out.n++] = t1;
+        }
+    }
+    isect_caps(r, lo, hi, 1.0, 1.0, closed, out);
+}
+// src/shape.rs:770-822 (the single-root branch has no y-range check)
+__device__ __forceinline__ void isect_cone(const Ray& r, double lo, double hi, bool closed, Roots& out) {
+    const double a = r.d.x * r.d.x - r.d.y * r.d.y + r.d.z * r.d.z;
+    const double b = 2.0 * r.o.x * r.d.x - 2.0 * r.o.y * r.d.y + 2.0 * r.o.z * r.d.z;
+    if (!approx0(a) || !approx0(b)) {
+        const double c = r.o.x * r.o.x - r.o.y * r.o.y + r.o.z * r.o.z;
+        if (!approx0(a)) {
+            const double disc = b * b - 4.0 * a * c;
+            if (disc >= 0.0) {
+                const double sq = sqrt(disc);
+                const double t0 = (-b - sq) / (2.0 * a);
+                const double y0 = r.o.y + t0 * r.d.y;
+                if (lo < y0 && y0 < hi) out.t[out.n++] = t0;
+                const double t1 = (-b + sq) / (2.0 * a);
+                const double y1 = r.o.y + t1 * r.d.y;
+                if (lo < y1 && y1 < hi) out.t[out.n++] = t1;
+            }
+        } else {
+            out.t[out.n++] = -c / (2.0 * b);
+        }
+    }
+    isect_caps(r, lo, hi, lo, hi, closed, out);
+}
+// src/shape.rs:824-860 (Moller-Trumbore, no test on t)
+__device__ __forceinline__ void isect_triangle(const Ray& r, V3 p1, V3 e1, V3 e2, Roots& out) {
+    const V3 dir_cross_e2 = cross(r.d, e2);
+    const double det = dot(e1, dir_cross_e2);
+    if (fabs(det) < RTC_EPSILON) return;
+    const double f = 1.0 / det;
+    const V3 p1_to_origin = r.o - p1;
+    const double u = f * dot(p1_to_origin, dir_cross_e2);
+    if (u < 0.0 || u > 1.0) return;
+    const V3 origin_cross_e1 = cross(p1_to_origin, e1);
+    const double v = f * dot(r.d, origin_cross_e1);
+    if (v < 0.0 || u + v > 1.0) return;
+    out.t[0] = f * dot(e2, origin_cross_e1);
+    out.u = u;
+    out.v = v;
+    out.n = 1;
+}
+
+__device__ __forceinline__ void load_tri(const double* __restrict__ rec, V3& a, V3& b, V3& c) {
+    // 80-byte record, 16-byte aligned: five 128-bit loads
+    const double2* q = reinterpret_cast<const double2*>(rec);
+    const double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3), q4 = __ldg(q + 4);
+    a = mk(q0.x, q0.y, q1.x);
+    b = mk(q1.y, q2.x, q2.y);
+    c = mk(q3.x, q3.y, q4.x);
+}
+
+// All crossings of primitive `p` with the WORLD ray (src/shape.rs:414-417 + :862-885).
+__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, Roots& out) {
+    out.n = 0;
+    const double* m = sc.xforms[p.xform].inv;
+    Ray r;
+    r.o = xf_point(m, world.o);
+    r.d = xf_dir(m, world.d);
+    const int kind = p.kind_flags & 0xff;
+    switch (kind) {
+        case 0: isect_sphere(r, out); break;
+        case 1: isect_plane(r, out); break;
+        case 2: isect_cube(r, out); break;
+        case 3: isect_cylinder(r, sc.ranges[2 * p.geom], sc.ranges[2 * p.geom + 1], (p.kind_flags & 0x200) != 0, out); break;
+        case 4: isect_cone(r, sc.ranges[2 * p.geom], sc.ranges[2 * p.geom + 1], (p.kind_flags & 0x200) != 0, out); break;
+        default: {
+            V3 p1, e1, e2;
+            load_tri(sc.tri_pe + 10 * (size_t)p.geom, p1, e1, e2);
+            isect_triangle(r, p1, e1, e2, out);
+        }
+    }
+}
+
+// src/shape.rs:419-427 + :887-946 — world normal at a world point (not yet flipped towards the eye)
+__device__ __forceinline__ V3 prim_normal(const Scene& sc, const Prim& p, V3 world_point, double u, double v) {
+    const Xform& xf = sc.xforms[p.xform];
+    const V3 q = xf_point(xf.inv, world_point);
+    const int kind = p.kind_flags & 0xff;
+    V3 n;
+    switch (kind) {
+        case 0: n = q; break;
+        case 1: n = mk(0.0, 1.0, 0.0); break;
+        case 2: {
+            const double ax = fabs(q.x), ay = fabs(q.y), az = fabs(q.z);
+            const double mx = fmax(fmax(ax, ay), az);
+            if (mx == ax) n = mk(q.x, 0.0, 0.0);
+            else if (mx == ay) n = mk(0.0, q.y, 0.0);
+            else n = mk(0.0, 0.0, q.z);
+            break;
+        }
+        case 3:
+        case 4: {
+            const double lo = sc.ranges[2 * p.geom], hi = sc.ranges[2 * p.geom + 1];
+            const double dist = q.x * q.x + q.z * q.z;
+            if (dist < 1.0 && q.y >= hi - RTC_EPSILON) n = mk(0.0, 1.0, 0.0);
+            else if (dist < 1.0 && q.y <= lo + RTC_EPSILON) n = mk(0.0, -1.0, 0.0);
+            else if (kind == 3) n = mk(q.x, 0.0, q.z);
+            else {
+                double y = sqrt(dist);
+                if (q.y > 0.0) y = -y;
+                n = mk(q.x, y, q.z);
+            }
+            break;
+        }
+        case 5: {
+            const double* rec = sc.tri_n + 10 * (size_t)p.geom;
+            n = mk(rec[0], rec[1], rec[2]);
+            break;
+        }
+        default: {
+            V3 n1, n2, n3;
+            load_tri(sc.tri_n + 10 * (size_t)p.geom, n1, n2, n3);
+            n = n2 * u + n3 * v + n1 * (1.0 - u - v);  // src/shape.rs:943
+        }
+    }
+    return normalize(xf_normal(xf.tsp, n));
+}
+
+}  // namespace rtcdev

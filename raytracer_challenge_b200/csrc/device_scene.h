@@ -1,0 +1,115 @@
+// Device-side scene layout (HBM-resident, read-only during a render; everything fits in L2).
+// Built by scene_build.cpp from the rtc.h arrays; consumed by render_kernels.cu.
+#pragma once
+#include <stdint.h>
+
+namespace rtcdev {
+
+constexpr int MAX_LIGHTS = 16;
+constexpr int MAX_PATTERN_FRAMES = 8;   // nesting of Blend/Gradient/RingGradient/ColorJitter along one path
+constexpr int MAX_CSG_LIST = 48;        // crossings held while evaluating one top-level CSG item
+constexpr int MAX_CSG_MARKS = 8;        // CSG nesting depth
+constexpr int MAX_CROSSINGS = 64;       // crossings (t <= t_hit) replayed for n1/n2 (src/intersection.rs:70-103)
+constexpr int MAX_CONTAINERS = 24;      // simultaneously open shapes during that replay
+constexpr int BVH_STACK = 48;
+
+// Kernel feature bits (compile-time variants of the wavefront kernel)
+constexpr int FEAT_TRANSPARENT = 1;  // some material has transparency != 0: n1/n2 replay needed
+constexpr int FEAT_CSG = 2;          // CSG items present
+constexpr int FEAT_GATES = 4;        // group boxes that must be evaluated exactly
+
+// Per distinct (transform_inv, transform_inv_tsp) pair.  Affine: rows 0..2 only.
+struct Xform {
+    double inv[12];  // world -> object, row-major 3x4
+    double tsp[9];   // upper 3x3 of transform_inv_tsp (normals)
+    double pad[3];
+};  // 192 B
+
+struct MatInv {
+    double m[16];  // world -> pattern space, full row-major 4x4: pattern space carries w (see device_pattern.cuh)
+};
+
+// kind_flags: bits 0..7 kind (rtc_prim_kind), bit 8 casts_shadow, bit 9 closed
+struct Prim {
+    int32_t kind_flags;
+    int32_t material;
+    int32_t xform;
+    int32_t matinv;
+    int32_t geom;        // triangles: slot in tri_pe / tri_n; cylinder / cone: slot in ranges
+    uint32_t gate_mask;  // non-trivial ancestor group boxes that must pass (src/shape.rs:251)
+    int32_t pad0, pad1;
+};  // 32 B
+
+struct Material {
+    double ambient, diffuse, specular, shininess, reflective, transparency, refractive_index;
+    int32_t pattern;
+    int32_t flags;  // bit 0: pattern is Plain (colour inlined below)
+    double plain[3];
+    double pad;
+};  // 96 B
+
+struct Pattern {
+    int32_t kind, left, right, noise_kind;
+    int32_t octaves, pad;
+    double noise_scale;
+    double color[3];
+    double m[16];  // mixture transform_inv, full row-major 4x4
+    double pad2;
+};  // 192 B
+
+struct Light {
+    double intensity[3];
+    double origin[3];
+};
+
+struct Gate {  // a group box that is neither always-passing nor provably conservative: evaluated exactly per ray
+    double lo[3], hi[3];
+};
+
+// BVH2 node, 64 B, two float4-aligned child boxes (outward-rounded, padded) + two child links.
+// link >= 0: inner node index; link < 0: leaf, ~link = (first_item << 2) | (count - 1), count <= 4.
+struct BvhNode {
+    float lo0[3], hi0[3];
+    float lo1[3], hi1[3];
+    int32_t c0, c1;
+    int32_t pad0, pad1;
+};
+
+// CSG evaluation program of one top-level CSG item (post-order over its subtree).
+//   OP_PRIM  a = primitive index
+//   OP_BEGIN                     (push list length)
+//   OP_END   a = group kind, b/c = primitive index range [b, c) of the LEFT child's subtree
+struct CsgOp {
+    int32_t op, a, b, c;
+};
+enum { OP_PRIM = 0, OP_BEGIN = 1, OP_END = 2 };
+struct CsgRoot {
+    int32_t first_op, n_ops;
+    int32_t prim_begin, prim_end;  // all primitives of the subtree are [prim_begin, prim_end)
+};
+
+struct Scene {
+    const Prim* prims;
+    const Xform* xforms;
+    const MatInv* matinvs;
+    const double* tri_pe;   // 10 doubles per triangle: p1, e1, e2, pad   (16-byte aligned records)
+    const double* tri_n;    // 10 doubles per triangle: n1, n2, n3, pad
+    const double* ranges;   // 2 doubles per cylinder / cone: min, max
+    const Material* materials;
+    const Pattern* patterns;
+    const Light* lights;
+    const Gate* gates;
+    const BvhNode* bvh;
+    const int32_t* leaf_items;  // >= 0 primitive index, < 0: ~csg_root index
+    const int32_t* unbounded;   // items tested for every ray (planes, cones, infinite cylinders, CSG holding one)
+    const CsgOp* csg_ops;
+    const CsgRoot* csg_roots;
+    int32_t n_prims, n_lights, n_gates, n_unbounded, n_bvh_items, n_csg_roots;
+    int32_t bvh_root;        // link of the root (may be a leaf); valid only if n_bvh_items > 0
+    int32_t all_cast_shadow; // every primitive casts shadows -> shadow queries may stop at the first hit
+    int32_t max_children;    // max over materials of (reflective != 0) + (transparency != 0)
+    int32_t pad;
+    double root_lo[3], root_hi[3];  // f64 bounds of all BVH items (already padded)
+};
+
+}  // namespace rtcdev

@@ -1,0 +1,339 @@
+// Ray queries against the flattened scene: closest hit, shadow test and the crossing list that feeds n1/n2.
+// They replace World::intersect + Intersection::sort + Intersection::hit (src/world.rs:18-24,
+// src/intersection.rs:123-132), which test every primitive and sort every crossing for every ray.
+//
+// Culling is done on a BVH2 whose boxes are fp32, outward-rounded and padded by 4e-6 * (scene extent): the
+// computed slab interval of a padded box always contains the exact interval of the true box (DESIGN.md,
+// "conservative fp32 culling"), so the set of primitives that reach the exact f64 intersectors is a superset
+// of those the ray really crosses and the result equals the brute-force scan.  Accepted primitives are
+// intersected in f64 with the reference's own arithmetic.  Ties in t resolve to the lower primitive index
+// (= depth-first order = what the reference's stable sort yields).
+#pragma once
+#include "device_math.cuh"
+
+namespace rtcdev {
+
+struct Hit {
+    double t;
+    int prim;
+    double u, v;
+};
+struct Cross {
+    double t;
+    int prim;
+    int pad;
+};
+
+__device__ __forceinline__ bool allows_intersection(int kind, bool left_hit, bool in_left, bool in_right) {  // src/shape.rs:169-178
+    if (kind == 0) return (left_hit && !in_right) || (!left_hit && !in_left);
+    if (kind == 1) return (left_hit && in_right) || (!left_hit && in_left);
+    return (left_hit && !in_right) || (!left_hit && in_left);
+}
+
+template <int FEAT>
+__device__ __forceinline__ uint32_t gates_passed(const Scene& sc, const Ray& ray) {
+    uint32_t m = 0;
+    if (FEAT & FEAT_GATES)
+        for (int g = 0; g < sc.n_gates; ++g)
+            if (box_gate(sc.gates[g], ray)) m |= 1u << g;
+    return m;
+}
+template <int FEAT>
+__device__ __forceinline__ bool gate_ok(const Prim& p, uint32_t passed) {
+    return !(FEAT & FEAT_GATES) || (p.gate_mask & ~passed) == 0u;
+}
+
+// Group::intersect for a CSG subtree (src/shape.rs:230-269): gather, stable-sort by t, filter, recursively.
+// Returns the number of surviving crossings in `list` (sorted by t), or -1 on overflow.
+template <int FEAT>
+__device__ __noinline__ int csg_eval(const Scene& sc, const CsgRoot& root, const Ray& ray, uint32_t passed, Cross* list) {
+    int marks[MAX_CSG_MARKS];
+    int nm = 0, n = 0;
+    for (int k = 0; k < root.n_ops; ++k) {
+        const CsgOp op = sc.csg_ops[root.first_op + k];
+        if (op.op == OP_PRIM) {
+            const Prim p = sc.prims[op.a];
+            if (!gate_ok<FEAT>(p, passed)) continue;
+            Roots r;
+            prim_roots(sc, p, ray, r);
+            if (n + r.n > MAX_CSG_LIST) return -1;
+            for (int j = 0; j < r.n; ++j) { list[n].t = r.t[j]; list[n].prim = op.a; n++; }
+        } else if (op.op == OP_BEGIN) {
+            marks[nm++] = n;
+        } else {
+            const int m = marks[--nm];
+            for (int i = m + 1; i < n; ++i) {  // stable insertion sort by t
+                const Cross c = list[i];
+                int j = i - 1;
+                while (j >= m && list[j].t > c.t) { list[j + 1] = list[j]; --j; }
+                list[j + 1] = c;
+            }
+            bool in_left = false, in_right = false;
+            int out = m;
+            for (int i = m; i < n; ++i) {
+                const bool left_hit = list[i].prim >= op.b && list[i].prim < op.c;
+                const bool keep = allows_intersection(op.a, left_hit, in_left, in_right);
+                if (left_hit) in_left = !in_left; else in_right = !in_right;
+                if (keep) list[out++] = list[i];
+            }
+            n = out;
+        }
+    }
+    return n;
+}
+
+// ---- fp32 BVH walk ---------------------------------------------------------------------------
+struct Walk {
+    float ox, oy, oz, ix, iy, iz;
+    double te;   // world t of the re-origin
+    float tlo;   // lower end of the admissible interval, relative to te
+};
+
+// mode 0: hits with t >= 0 (closest / shadow); mode 1: every crossing up to tmax (also negative t).
+// Returns false if the ray cannot touch any BVH item.
+__device__ __forceinline__ bool walk_setup(const Scene& sc, const Ray& ray, int mode, Walk& w) {
+    double tn = -CUDART_INF, tf = CUDART_INF;
+    const double o[3] = {ray.o.x, ray.o.y, ray.o.z}, d[3] = {ray.d.x, ray.d.y, ray.d.z};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double inv = 1.0 / d[k];
+        const double a = (sc.root_lo[k] - o[k]) * inv, b = (sc.root_hi[k] - o[k]) * inv;
+        tn = fmax(tn, fmin(a, b));
+        tf = fmin(tf, fmax(a, b));
+    }
+    if (!(tn <= tf)) return false;
+    if (mode == 0) {
+        if (tf < 0.0) return false;
+        w.te = fmax(tn, 0.0);
+        w.tlo = __double2float_rd(-w.te);
+    } else {
+        w.te = fmin(fmax(0.0, tn), tf);
+        w.tlo = -CUDART_INF_F;
+    }
+    if (!(fabs(w.te) <= 1.7e308)) { w.te = 0.0; w.tlo = mode == 0 ? 0.0f : -CUDART_INF_F; }
+    w.ox = (float)(o[0] + w.te * d[0]);
+    w.oy = (float)(o[1] + w.te * d[1]);
+    w.oz = (float)(o[2] + w.te * d[2]);
+    w.ix = 1.0f / (float)d[0];
+    w.iy = 1.0f / (float)d[1];
+    w.iz = 1.0f / (float)d[2];
+    return true;
+}
+
+__device__ __forceinline__ bool slab(const Walk& w, float lx, float ly, float lz, float hx, float hy, float hz, float thi, float& tnear) {
+    const float ax = (lx - w.ox) * w.ix, bx = (hx - w.ox) * w.ix;
+    const float ay = (ly - w.oy) * w.iy, by = (hy - w.oy) * w.iy;
+    const float az = (lz - w.oz) * w.iz, bz = (hz - w.oz) * w.iz;
+    const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), w.tlo));
+    const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), thi));
+    tnear = t0;
+    return t0 <= t1;
+}
+
+// Visitor protocol:  bool V::item(int id)   -> true stops the walk;   double V::tmax()  -> current upper bound on t.
+template <class V>
+__device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v) {
+    if (sc.n_bvh_items == 0) return;
+    if (brute) {
+        for (int i = 0; i < sc.n_bvh_items; ++i)
+            if (v.item(sc.leaf_items[i])) return;
+        return;
+    }
+    Walk w;
+    if (!walk_setup(sc, ray, mode, w)) return;
+    int stack[BVH_STACK];
+    int sp = 0;
+    int link = sc.bvh_root;
+    for (;;) {
+        if (link >= 0) {
+            const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
+            const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+            const float thi = __double2float_ru(__dsub_ru(v.tmax(), w.te));
+            float n0, n1;
+            const bool h0 = slab(w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
+            const bool h1 = slab(w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
+            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+            if (h0 && h1) {
+                const bool first0 = n0 <= n1;
+                stack[sp++] = first0 ? c1 : c0;
+                link = first0 ? c0 : c1;
+                continue;
+            }
+            if (h0) { link = c0; continue; }
+            if (h1) { link = c1; continue; }
+        } else {
+            const int enc = ~link;
+            const int first = enc >> 2, count = (enc & 3) + 1;
+            for (int i = 0; i < count; ++i)
+                if (v.item(sc.leaf_items[first + i])) return;
+        }
+        if (sp == 0) return;
+        link = stack[--sp];
+    }
+}
+
+// ---- closest hit ---------------------------------------------------------------------------------
+template <int FEAT>
+struct ClosestVisitor {
+    const Scene& sc;
+    const Ray& ray;
+    uint32_t passed;
+    Hit best;
+    double limit;   // exclusive upper bound on t (shadow queries on scenes with non-casting shapes), else +inf
+    int* overflow;
+    __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : limit; }
+    __device__ __forceinline__ void offer(double t, int prim, double u, double v) {
+        if (t >= 0.0 && t < limit && (best.prim < 0 || t < best.t || (t == best.t && prim < best.prim))) {
+            best.t = t; best.prim = prim; best.u = u; best.v = v;
+        }
+    }
+    __device__ __forceinline__ bool item(int id) {
+        if (!(FEAT & FEAT_CSG) || id >= 0) {
+            const Prim p = sc.prims[id];
+            if (!gate_ok<FEAT>(p, passed)) return false;
+            Roots r;
+            prim_roots(sc, p, ray, r);
+            for (int k = 0; k < r.n; ++k) offer(r.t[k], id, r.u, r.v);
+        } else {
+            Cross list[MAX_CSG_LIST];
+            const int n = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
+            if (n < 0) { *overflow = 1; return true; }
+            for (int k = 0; k < n; ++k)
+                if (list[k].t >= 0.0) {  // list is sorted: the first non-negative entry is this item's hit
+                    double u = 0.0, v = 0.0;
+                    const Prim p = sc.prims[list[k].prim];
+                    if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
+                        Roots r;
+                        prim_roots(sc, p, ray, r);
+                        u = r.u; v = r.v;
+                    }
+                    offer(list[k].t, list[k].prim, u, v);
+                    break;
+                }
+        }
+        return false;
+    }
+};
+
+template <int FEAT>
+__device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, int* overflow) {
+    ClosestVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), Hit{0.0, -1, 0.0, 0.0}, limit, overflow};
+    for (int i = 0; i < sc.n_unbounded; ++i) v.item(sc.unbounded[i]);
+    walk_bvh(sc, ray, 0, brute, v);
+    return v.best;
+}
+
+// ---- shadow query: World::is_shadowed (src/world.rs:26-48) -------------------------------------------
+template <int FEAT>
+struct AnyVisitor {
+    const Scene& sc;
+    const Ray& ray;
+    uint32_t passed;
+    double dist;
+    bool found;
+    int* overflow;
+    __device__ __forceinline__ double tmax() const { return dist; }
+    __device__ __forceinline__ bool item(int id) {
+        if (!(FEAT & FEAT_CSG) || id >= 0) {
+            const Prim p = sc.prims[id];
+            if (!gate_ok<FEAT>(p, passed)) return false;
+            Roots r;
+            prim_roots(sc, p, ray, r);
+            for (int k = 0; k < r.n; ++k)
+                if (r.t[k] >= 0.0 && r.t[k] < dist) { found = true; return true; }
+        } else {
+            Cross list[MAX_CSG_LIST];
+            const int n = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
+            if (n < 0) { *overflow = 1; return true; }
+            for (int k = 0; k < n; ++k)
+                if (list[k].t >= 0.0 && list[k].t < dist) { found = true; return true; }
+        }
+        return false;
+    }
+};
+
+// shadowed <=> the nearest crossing with t >= 0 belongs to a casting shape and has t < distance.
+template <int FEAT>
+__device__ __forceinline__ bool is_shadowed(const Scene& sc, const Ray& ray, double dist, bool brute, int* overflow) {
+    if (sc.all_cast_shadow) {  // then "nearest t < dist" <=> "any t in [0, dist)": stop at the first one
+        AnyVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), dist, false, overflow};
+        for (int i = 0; i < sc.n_unbounded; ++i)
+            if (v.item(sc.unbounded[i])) return v.found;
+        walk_bvh(sc, ray, 0, brute, v);
+        return v.found;
+    }
+    const Hit h = closest_hit<FEAT>(sc, ray, dist, brute, overflow);
+    return h.prim >= 0 && (sc.prims[h.prim].kind_flags & 0x100) != 0;
+}
+
+// ---- n1 / n2: replay of the container walk of Intersection::prepare_state (src/intersection.rs:70-103) ----
+template <int FEAT>
+struct CollectVisitor {
+    const Scene& sc;
+    const Ray& ray;
+    uint32_t passed;
+    double thit;
+    Cross* out;
+    int n;
+    int* overflow;
+    __device__ __forceinline__ double tmax() const { return thit; }
+    __device__ __forceinline__ bool push(double t, int prim) {
+        if (!(t <= thit)) return false;
+        if (n >= MAX_CROSSINGS) { *overflow = 1; return true; }
+        out[n].t = t; out[n].prim = prim; n++;
+        return false;
+    }
+    __device__ __forceinline__ bool item(int id) {
+        if (!(FEAT & FEAT_CSG) || id >= 0) {
+            const Prim p = sc.prims[id];
+            if (!gate_ok<FEAT>(p, passed)) return false;
+            Roots r;
+            prim_roots(sc, p, ray, r);
+            for (int k = 0; k < r.n; ++k)
+                if (push(r.t[k], id)) return true;
+        } else {
+            Cross list[MAX_CSG_LIST];
+            const int m = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
+            if (m < 0) { *overflow = 1; return true; }
+            for (int k = 0; k < m; ++k)
+                if (push(list[k].t, list[k].prim)) return true;
+        }
+        return false;
+    }
+};
+
+template <int FEAT>
+__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, const Hit& hit, bool brute, double& n1, double& n2, int* overflow) {
+    Cross xs[MAX_CROSSINGS];
+    CollectVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), hit.t, xs, 0, overflow};
+    for (int i = 0; i < sc.n_unbounded; ++i) v.item(sc.unbounded[i]);
+    walk_bvh(sc, ray, 1, brute, v);
+    const int n = v.n;
+    for (int i = 1; i < n; ++i) {  // order of the reference's sorted list: by t, ties in depth-first primitive order
+        const Cross c = xs[i];
+        int j = i - 1;
+        while (j >= 0 && (xs[j].t > c.t || (xs[j].t == c.t && xs[j].prim > c.prim))) { xs[j + 1] = xs[j]; --j; }
+        xs[j + 1] = c;
+    }
+    int open[MAX_CONTAINERS];
+    int no = 0;
+    n1 = 1.0;
+    n2 = 1.0;
+    for (int i = 0; i < n; ++i) {
+        const bool is_hit = xs[i].t == hit.t && xs[i].prim == hit.prim;  // Intersection::eq, src/intersection.rs:135-139
+        if (is_hit) n1 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
+        int at = -1;
+        for (int k = 0; k < no; ++k)
+            if (open[k] == xs[i].prim) at = k;
+        if (at >= 0) {
+            for (int k = at; k + 1 < no; ++k) open[k] = open[k + 1];
+            no--;
+        } else {
+            if (no >= MAX_CONTAINERS) { *overflow = 1; return; }
+            open[no++] = xs[i].prim;
+        }
+        if (is_hit) n2 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
+    }
+}
+
+}  // namespace rtcdev

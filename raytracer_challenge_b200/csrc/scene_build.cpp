@@ -1,0 +1,498 @@
+#include "scene_build.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <limits>
+#include <map>
+
+namespace rtchost {
+namespace {
+
+using rtcdev::BvhNode;
+constexpr double INF = std::numeric_limits<double>::infinity();
+
+struct Box {
+    double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
+    bool bounded = true;  // false: must be tested for every ray
+    void add(const double p[3]) {
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); }
+    }
+    void add(const Box& b) {
+        if (!b.bounded) bounded = false;
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], b.lo[k]); hi[k] = std::max(hi[k], b.hi[k]); }
+    }
+    bool empty() const { return lo[0] > hi[0]; }
+};
+
+// The reference's cofactor inverse (src/linalg/matrix.rs:162-207) returns a last row that is (0,0,0,1) only up to
+// rounding (element [3][3] is det3/det computed along two different paths), so "affine" is tested with a tolerance.
+bool affine(const double m[16]) {
+    return std::fabs(m[12]) <= 1e-9 && std::fabs(m[13]) <= 1e-9 && std::fabs(m[14]) <= 1e-9 && std::fabs(m[15] - 1.0) <= 1e-9;
+}
+bool all_finite(const double* v, int n) {
+    for (int i = 0; i < n; ++i)
+        if (!std::isfinite(v[i])) return false;
+    return true;
+}
+
+// General 3x4 affine inverse (object -> world from world -> object); only used for bounds, which are padded.
+bool invert_affine(const double m[16], double out[12]) {
+    const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (det == 0.0 || !std::isfinite(det)) return false;
+    const double r[9] = {(e * i - f * h) / det, (c * h - b * i) / det, (b * f - c * e) / det,
+                         (f * g - d * i) / det, (a * i - c * g) / det, (c * d - a * f) / det,
+                         (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det};
+    for (int row = 0; row < 3; ++row) {
+        for (int col = 0; col < 3; ++col) out[row * 4 + col] = r[row * 3 + col];
+        out[row * 4 + 3] = -(r[row * 3] * m[3] + r[row * 3 + 1] * m[7] + r[row * 3 + 2] * m[11]);
+    }
+    return true;
+}
+void xf_point(const double m[12], const double p[3], double out[3]) {
+    for (int r = 0; r < 3; ++r) out[r] = m[r * 4] * p[0] + m[r * 4 + 1] * p[1] + m[r * 4 + 2] * p[2] + m[r * 4 + 3];
+}
+
+// World-space bounds of one primitive, or unbounded.  Planes (src/shape.rs:954-957), cylinders with an
+// infinite range and ALL cones are unbounded: a cone's single-root branch (src/shape.rs:811-818) has no
+// y-range check, so its crossings are not confined to [min, max].
+Box prim_bounds(const rtc_prim& p) {
+    Box b;
+    double fwd[12];
+    if (!invert_affine(p.transform_inv, fwd)) { b.bounded = false; return b; }
+    double olo[3], ohi[3];
+    switch (p.kind) {
+        case RTC_SPHERE:
+        case RTC_CUBE:
+            for (int k = 0; k < 3; ++k) { olo[k] = -1.0; ohi[k] = 1.0; }
+            break;
+        case RTC_CYLINDER:
+            if (!std::isfinite(p.min) || !std::isfinite(p.max)) { b.bounded = false; return b; }
+            olo[0] = -1.0; ohi[0] = 1.0; olo[2] = -1.0; ohi[2] = 1.0;
+            olo[1] = std::min(p.min, p.max); ohi[1] = std::max(p.min, p.max);
+            break;
+        case RTC_TRIANGLE:
+        case RTC_SMOOTH_TRIANGLE: {
+            double v[3][3];
+            for (int k = 0; k < 3; ++k) { v[0][k] = p.p1[k]; v[1][k] = p.p1[k] + p.e1[k]; v[2][k] = p.p1[k] + p.e2[k]; }
+            for (auto& q : v) { double w[3]; xf_point(fwd, q, w); b.add(w); }
+            goto pad;
+        }
+        default:  // plane, cone
+            b.bounded = false;
+            return b;
+    }
+    for (int c = 0; c < 8; ++c) {
+        const double q[3] = {(c & 4) ? ohi[0] : olo[0], (c & 2) ? ohi[1] : olo[1], (c & 1) ? ohi[2] : olo[2]};
+        double w[3];
+        xf_point(fwd, q, w);
+        b.add(w);
+    }
+pad:
+    for (int k = 0; k < 3; ++k) {
+        if (!std::isfinite(b.lo[k]) || !std::isfinite(b.hi[k])) { b.bounded = false; return b; }
+        const double e = 1e-9 * std::max({1.0, std::fabs(b.lo[k]), std::fabs(b.hi[k])});
+        b.lo[k] -= e;
+        b.hi[k] += e;
+    }
+    return b;
+}
+
+float f32_down(double x) {
+    float f = (float)x;
+    if ((double)f > x) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+    return f;
+}
+float f32_up(double x) {
+    float f = (float)x;
+    if ((double)f < x) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+    return f;
+}
+
+// ---- binned-SAH BVH2 over item boxes ------------------------------------------------------
+struct Builder {
+    const std::vector<Box>& boxes;  // per item
+    std::vector<int32_t> order;     // item permutation; leaves reference ranges of it
+    std::vector<BvhNode> nodes;
+    double pad;
+    int depth = 0;
+
+    static double area(const Box& b) {
+        if (b.empty()) return 0.0;
+        const double dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+        return 2.0 * (dx * dy + dy * dz + dz * dx);
+    }
+    Box range_box(int begin, int end) const {
+        Box b;
+        for (int i = begin; i < end; ++i) b.add(boxes[(size_t)order[(size_t)i]]);
+        return b;
+    }
+    void store_box(float lo[3], float hi[3], const Box& b) const {
+        for (int k = 0; k < 3; ++k) { lo[k] = f32_down(b.lo[k] - pad); hi[k] = f32_up(b.hi[k] + pad); }
+    }
+    static int32_t leaf_link(int begin, int count) { return ~((begin << 2) | (count - 1)); }
+
+    // returns the link for range [begin, end)
+    int32_t build(int begin, int end, int level) {
+        depth = std::max(depth, level);
+        const int n = end - begin;
+        if (n <= 1) return leaf_link(begin, n);
+        // split candidates on the centroid bounds
+        Box cb;
+        for (int i = begin; i < end; ++i) {
+            const Box& b = boxes[(size_t)order[(size_t)i]];
+            const double c[3] = {0.5 * (b.lo[0] + b.hi[0]), 0.5 * (b.lo[1] + b.hi[1]), 0.5 * (b.lo[2] + b.hi[2])};
+            cb.add(c);
+        }
+        constexpr int NB = 16;
+        double best_cost = INF;
+        int best_axis = -1, best_bin = -1;
+        for (int axis = 0; axis < 3; ++axis) {
+            const double ext = cb.hi[axis] - cb.lo[axis];
+            if (!(ext > 0.0)) continue;
+            Box bin_box[NB];
+            int bin_n[NB] = {0};
+            for (int i = begin; i < end; ++i) {
+                const Box& b = boxes[(size_t)order[(size_t)i]];
+                const double c = 0.5 * (b.lo[axis] + b.hi[axis]);
+                int k = (int)((c - cb.lo[axis]) / ext * NB);
+                k = std::min(std::max(k, 0), NB - 1);
+                bin_box[k].add(b);
+                bin_n[k]++;
+            }
+            double right_area[NB];
+            int right_n[NB];
+            Box acc;
+            int cnt = 0;
+            for (int k = NB - 1; k > 0; --k) {
+                acc.add(bin_box[k]);
+                cnt += bin_n[k];
+                right_area[k] = area(acc);
+                right_n[k] = cnt;
+            }
+            Box left;
+            int ln = 0;
+            for (int k = 0; k < NB - 1; ++k) {
+                left.add(bin_box[k]);
+                ln += bin_n[k];
+                if (ln == 0 || right_n[k + 1] == 0) continue;
+                const double cost = area(left) * ln + right_area[k + 1] * right_n[k + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = k; }
+            }
+        }
+        int mid;
+        if (best_axis < 0) {
+            if (n <= 4) return leaf_link(begin, n);
+            mid = begin + n / 2;  // identical centroids: split by index
+        } else {
+            const Box whole = range_box(begin, end);
+            // leaf cost: every item test is an f64 primitive intersection (expensive) -> weight 3 vs 1 per node
+            const double leaf_cost = 3.0 * n;
+            const double split_cost = 1.0 + 3.0 * best_cost / std::max(area(whole), 1e-300);
+            if (n <= 4 && leaf_cost <= split_cost) return leaf_link(begin, n);
+            const double ext = cb.hi[best_axis] - cb.lo[best_axis];
+            auto it = std::partition(order.begin() + begin, order.begin() + end, [&](int32_t item) {
+                const Box& b = boxes[(size_t)item];
+                const double c = 0.5 * (b.lo[best_axis] + b.hi[best_axis]);
+                int k = (int)((c - cb.lo[best_axis]) / ext * NB);
+                k = std::min(std::max(k, 0), NB - 1);
+                return k <= best_bin;
+            });
+            mid = (int)(it - order.begin());
+            if (mid == begin || mid == end) mid = begin + n / 2;
+        }
+        const int32_t self = (int32_t)nodes.size();
+        nodes.emplace_back();
+        const Box lb = range_box(begin, mid), rb = range_box(mid, end);
+        const int32_t l = build(begin, mid, level + 1);
+        const int32_t r = build(mid, end, level + 1);
+        BvhNode& nd = nodes[(size_t)self];
+        std::memset(&nd, 0, sizeof nd);
+        store_box(nd.lo0, nd.hi0, lb);
+        store_box(nd.lo1, nd.hi1, rb);
+        nd.c0 = l;
+        nd.c1 = r;
+        return self;
+    }
+};
+
+template <class T>
+int32_t dedupe(std::map<std::string, int32_t>& index, std::vector<T>& store, const T& value) {
+    std::string key((const char*)&value, sizeof(T));
+    auto it = index.find(key);
+    if (it != index.end()) return it->second;
+    store.push_back(value);
+    const int32_t id = (int32_t)store.size() - 1;
+    index.emplace(std::move(key), id);
+    return id;
+}
+
+}  // namespace
+
+std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
+    out = HostScene{};
+    if (d.abi_version != RTC_ABI_VERSION) return "abi_version mismatch";
+    if (d.n_prims < 0 || d.n_nodes < 1 || d.n_children < 0 || d.n_materials < 0 || d.n_patterns < 0 || d.n_lights < 0)
+        return "negative array length (or no root node)";
+    if (d.n_lights > rtcdev::MAX_LIGHTS) return "too many lights (max " + std::to_string(rtcdev::MAX_LIGHTS) + ")";
+    if ((d.n_prims && !d.prims) || !d.nodes || (d.n_children && !d.children) || (d.n_materials && !d.materials) ||
+        (d.n_patterns && !d.patterns) || (d.n_lights && !d.lights))
+        return "null array pointer";
+
+    // ---- patterns ----
+    for (int i = 0; i < d.n_patterns; ++i) {
+        const rtc_pattern& p = d.patterns[i];
+        if (p.kind < RTC_PAT_DEBUG || p.kind > RTC_PAT_STRIPES) return "pattern " + std::to_string(i) + ": unknown kind";
+        const bool jitter = p.kind == RTC_PAT_JITTER_COLOR || p.kind == RTC_PAT_JITTER_POINT;
+        const bool mixture = p.kind >= RTC_PAT_BLEND;
+        // children must precede their parent (post-order), which also rules out cycles
+        if ((jitter || mixture) && (p.left < 0 || p.left >= i)) return "pattern " + std::to_string(i) + ": bad left/inner index";
+        if (mixture && (p.right < 0 || p.right >= i)) return "pattern " + std::to_string(i) + ": bad right index";
+        if (mixture && !affine(p.transform_inv)) return "pattern " + std::to_string(i) + ": transform is not affine";
+        if (jitter && p.noise_kind != RTC_NOISE_SIMPLEX && p.noise_kind != RTC_NOISE_FRACTAL) return "pattern: unknown noise kind";
+        if (jitter && p.octaves < 0) return "pattern: negative octaves";
+        rtcdev::Pattern q{};
+        q.kind = p.kind; q.left = p.left; q.right = p.right; q.noise_kind = p.noise_kind; q.octaves = p.octaves;
+        q.noise_scale = p.noise_scale;
+        for (int k = 0; k < 3; ++k) q.color[k] = p.color[k];
+        for (int k = 0; k < 16; ++k) q.m[k] = p.transform_inv[k];
+        out.patterns.push_back(q);
+    }
+    {  // evaluation-frame depth: Blend / Gradient / RingGradient / ColorJitter keep a frame while a child is evaluated
+        std::vector<int> frames((size_t)d.n_patterns, 0);
+        for (int i = 0; i < d.n_patterns; ++i) {
+            const rtc_pattern& p = d.patterns[i];
+            int child = 0;
+            if (p.kind == RTC_PAT_JITTER_COLOR || p.kind == RTC_PAT_JITTER_POINT) child = frames[(size_t)p.left];
+            else if (p.kind >= RTC_PAT_BLEND) child = std::max(frames[(size_t)p.left], frames[(size_t)p.right]);
+            const bool needs = p.kind == RTC_PAT_BLEND || p.kind == RTC_PAT_GRADIENT || p.kind == RTC_PAT_RING_GRADIENT || p.kind == RTC_PAT_JITTER_COLOR;
+            frames[(size_t)i] = child + (needs ? 1 : 0);
+            if (frames[(size_t)i] > rtcdev::MAX_PATTERN_FRAMES) return "pattern nesting too deep for the device evaluator";
+        }
+    }
+    // ---- materials ----
+    for (int i = 0; i < d.n_materials; ++i) {
+        const rtc_material& m = d.materials[i];
+        if (m.pattern < 0 || m.pattern >= d.n_patterns) return "material " + std::to_string(i) + ": bad pattern index";
+        rtcdev::Material q{};
+        q.ambient = m.ambient; q.diffuse = m.diffuse; q.specular = m.specular; q.shininess = m.shininess;
+        q.reflective = m.reflective; q.transparency = m.transparency; q.refractive_index = m.refractive_index;
+        q.pattern = m.pattern;
+        if (d.patterns[m.pattern].kind == RTC_PAT_PLAIN) {
+            q.flags = 1;
+            for (int k = 0; k < 3; ++k) q.plain[k] = d.patterns[m.pattern].color[k];
+        }
+        out.materials.push_back(q);
+        out.max_children = std::max(out.max_children, (int)(m.reflective != 0.0) + (int)(m.transparency != 0.0));
+    }
+    for (int i = 0; i < d.n_lights; ++i) {
+        rtcdev::Light l{};
+        for (int k = 0; k < 3; ++k) { l.intensity[k] = d.lights[i].intensity[k]; l.origin[k] = d.lights[i].origin[k]; }
+        out.lights.push_back(l);
+    }
+
+    // ---- primitives ----
+    std::map<std::string, int32_t> xf_index, mi_index;
+    std::vector<Box> prim_box((size_t)d.n_prims);
+    for (int i = 0; i < d.n_prims; ++i) {
+        const rtc_prim& p = d.prims[i];
+        if (p.kind < RTC_SPHERE || p.kind > RTC_SMOOTH_TRIANGLE) return "prim " + std::to_string(i) + ": unknown kind";
+        if (p.material < 0 || p.material >= d.n_materials) return "prim " + std::to_string(i) + ": bad material index";
+        if (!affine(p.transform_inv) || !affine(p.material_inv)) return "prim " + std::to_string(i) + ": non-affine matrix";
+        if (!all_finite(p.transform_inv, 16) || !all_finite(p.transform_inv_tsp, 16) || !all_finite(p.material_inv, 16))
+            return "prim " + std::to_string(i) + ": non-finite matrix";
+        rtcdev::Xform xf{};
+        for (int k = 0; k < 12; ++k) xf.inv[k] = p.transform_inv[k];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) xf.tsp[r * 3 + c] = p.transform_inv_tsp[r * 4 + c];
+        rtcdev::MatInv mi{};
+        for (int k = 0; k < 16; ++k) mi.m[k] = p.material_inv[k];
+        rtcdev::Prim q{};
+        q.kind_flags = p.kind | (p.casts_shadow ? 0x100 : 0) | (p.closed ? 0x200 : 0);
+        q.material = p.material;
+        q.xform = dedupe(xf_index, out.xforms, xf);
+        q.matinv = dedupe(mi_index, out.matinvs, mi);
+        q.geom = -1;
+        if (p.kind == RTC_TRIANGLE || p.kind == RTC_SMOOTH_TRIANGLE) {
+            q.geom = (int32_t)(out.tri_pe.size() / 10);
+            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.p1[k]);
+            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.e1[k]);
+            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.e2[k]);
+            out.tri_pe.push_back(0.0);
+            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n1[k]);
+            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n2[k]);
+            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n3[k]);
+            out.tri_n.push_back(0.0);
+        } else if (p.kind == RTC_CYLINDER || p.kind == RTC_CONE) {
+            q.geom = (int32_t)(out.ranges.size() / 2);
+            out.ranges.push_back(p.min);
+            out.ranges.push_back(p.max);
+        }
+        if (!p.casts_shadow) out.all_cast_shadow = 0;
+        out.prims.push_back(q);
+        prim_box[(size_t)i] = prim_bounds(p);
+    }
+
+    // ---- group tree: gates, CSG roots, items --------------------------------------------------
+    std::vector<int> visited_node((size_t)d.n_nodes, 0), visited_prim((size_t)d.n_prims, 0);
+    std::vector<Box> item_boxes;   // per BVH item
+    std::vector<int32_t> item_ids; // per BVH item: prim index or ~csg index
+    int next_prim = 0;             // primitives must appear in depth-first order
+    std::string err;
+
+    // Returns the bounds of the subtree; fills prim range [pb, pe).
+    std::function<Box(int, uint32_t, int, int, int&, int&)> walk;
+    // csg_root: index into out.csg_roots of the enclosing top-level CSG item, or -1.
+    walk = [&](int ni, uint32_t mask, int csg_root, int csg_depth, int& pb, int& pe) -> Box {
+        Box sub;
+        pb = next_prim;
+        pe = next_prim;
+        if (!err.empty()) return sub;
+        if (ni < 0 || ni >= d.n_nodes || visited_node[(size_t)ni]) { err = "group tree: bad or repeated node index"; return sub; }
+        visited_node[(size_t)ni] = 1;
+        const rtc_node& nd = d.nodes[ni];
+        if (nd.kind < RTC_UNION || nd.kind > RTC_AGGREGATION) { err = "group: unknown kind"; return sub; }
+        if (nd.first_child < 0 || nd.n_children < 0 || nd.first_child + nd.n_children > d.n_children) { err = "group: child range out of bounds"; return sub; }
+        const bool is_csg = nd.kind != RTC_AGGREGATION;
+        if (is_csg && nd.n_children != 2) { err = "CSG group needs exactly two children (src/shape.rs:80-83)"; return sub; }
+        if (ni == 0 && is_csg) { err = "the root node must be an aggregation"; return sub; }
+
+        // gate of this group (the virtual root has none: src/world.rs:21-23)
+        int gate_slot = -1;
+        if (ni != 0) {
+            int constraining = 0;
+            bool finite6 = true;
+            for (int k = 0; k < 3; ++k) {
+                const double lo = nd.bbox_min[k], hi = nd.bbox_max[k];
+                if (lo != lo || hi != hi) { err = "group box holds NaN"; return sub; }
+                const bool free_axis = (lo == -INF && hi == INF) || (lo == INF && hi == -INF);
+                if (!free_axis) constraining++;
+                if (!std::isfinite(lo) || !std::isfinite(hi)) finite6 = false;
+            }
+            if (constraining <= 1) {
+                out.n_gates_always_pass++;  // the slab test cannot fail ("group boxes")
+            } else {
+                gate_slot = (int)out.gates.size();  // provisional: dropped again below if provably conservative
+                rtcdev::Gate g{};
+                for (int k = 0; k < 3; ++k) { g.lo[k] = nd.bbox_min[k]; g.hi[k] = nd.bbox_max[k]; }
+                out.gates.push_back(g);
+                (void)finite6;
+            }
+        }
+        const uint32_t child_mask = gate_slot >= 0 && gate_slot < 32 ? (mask | (1u << gate_slot)) : mask;
+        if (gate_slot >= 32) { err = "more than 32 group boxes need exact evaluation"; return sub; }
+
+        int my_root = csg_root;
+        int my_depth = csg_depth;
+        if (is_csg) {
+            if (csg_root < 0) {
+                my_root = (int)out.csg_roots.size();
+                rtcdev::CsgRoot r{};
+                r.first_op = (int32_t)out.csg_ops.size();
+                out.csg_roots.push_back(r);
+            }
+            my_depth = csg_depth + 1;
+            if (my_depth > rtcdev::MAX_CSG_MARKS) { err = "CSG nesting too deep"; return sub; }
+            out.csg_ops.push_back({rtcdev::OP_BEGIN, 0, 0, 0});
+        }
+        int left_b = 0, left_e = 0;
+        const size_t first_prim_slot = out.prims.size();
+        (void)first_prim_slot;
+        for (int c = 0; c < nd.n_children; ++c) {
+            const int32_t ch = d.children[nd.first_child + c];
+            int cb = next_prim, ce = next_prim;
+            if (ch >= 0) {
+                if (ch != next_prim || ch >= d.n_prims || visited_prim[(size_t)ch]) { err = "primitives must be listed in depth-first order, each exactly once"; return sub; }
+                visited_prim[(size_t)ch] = 1;
+                next_prim++;
+                ce = next_prim;
+                out.prims[(size_t)ch].gate_mask = child_mask;
+                sub.add(prim_box[(size_t)ch]);
+                if (my_root >= 0) {
+                    out.csg_ops.push_back({rtcdev::OP_PRIM, ch, 0, 0});
+                } else if (prim_box[(size_t)ch].bounded) {
+                    item_boxes.push_back(prim_box[(size_t)ch]);
+                    item_ids.push_back(ch);
+                } else {
+                    out.unbounded.push_back(ch);
+                }
+            } else {
+                Box b = walk(~ch, child_mask, my_root, my_depth, cb, ce);
+                if (!err.empty()) return sub;
+                sub.add(b);
+            }
+            if (c == 0) { left_b = cb; left_e = ce; }
+        }
+        pe = next_prim;
+        if (is_csg) {
+            out.csg_ops.push_back({rtcdev::OP_END, nd.kind, left_b, left_e});
+            if (csg_root < 0) {  // this node is a top-level CSG item
+                rtcdev::CsgRoot& r = out.csg_roots[(size_t)my_root];
+                r.n_ops = (int32_t)out.csg_ops.size() - r.first_op;
+                r.prim_begin = pb;
+                r.prim_end = pe;
+                if (sub.bounded && !sub.empty()) {
+                    item_boxes.push_back(sub);
+                    item_ids.push_back(~my_root);
+                } else if (pe > pb) {
+                    out.unbounded.push_back(~my_root);
+                }
+            }
+        }
+        // a finite box that encloses everything below it can only reject rays that miss all of it: skip it
+        if (gate_slot >= 0) {
+            bool conservative = sub.bounded;
+            for (int k = 0; k < 3 && conservative; ++k) {
+                const double lo = nd.bbox_min[k], hi = nd.bbox_max[k];
+                if (!std::isfinite(lo) || !std::isfinite(hi)) { conservative = false; break; }
+                if (sub.empty()) continue;
+                const double tol = 4e-9 * std::max({1.0, std::fabs(sub.lo[k]), std::fabs(sub.hi[k])});
+                if (lo > sub.lo[k] + tol || hi < sub.hi[k] - tol) conservative = false;
+            }
+            if (conservative && gate_slot == (int)out.gates.size() - 1) {
+                // no deeper gate took a later slot: release this one
+                out.gates.pop_back();
+                for (int p = pb; p < pe; ++p) out.prims[(size_t)p].gate_mask &= ~(1u << gate_slot);
+                out.n_gates_conservative++;
+            } else if (conservative) {
+                for (int p = pb; p < pe; ++p) out.prims[(size_t)p].gate_mask &= ~(1u << gate_slot);
+                // slot stays allocated but unused by any primitive; harmless
+                out.n_gates_conservative++;
+            } else {
+                out.n_gates_exact++;
+            }
+        }
+        return sub;
+    };
+    int pb = 0, pe = 0;
+    walk(0, 0u, -1, 0, pb, pe);
+    if (!err.empty()) return err;
+    if (next_prim != d.n_prims) return "some primitives are not reachable from the root node";
+
+    // ---- BVH over the bounded items -------------------------------------------------------------
+    out.n_bvh_items = (int32_t)item_ids.size();
+    if (!item_ids.empty()) {
+        Box root;
+        for (auto& b : item_boxes) root.add(b);
+        double S = 0.0;
+        for (int k = 0; k < 3; ++k) S = std::max({S, std::fabs(root.lo[k]), std::fabs(root.hi[k])});
+        // fp32 traversal error bound is ~9 * 2^-24 * S (DESIGN.md "conservative fp32 culling"); pad with margin
+        const double pad = 4e-6 * std::max(S, 1e-30);
+        Builder bld{item_boxes, {}, {}, pad};
+        bld.order.resize(item_ids.size());
+        for (size_t i = 0; i < item_ids.size(); ++i) bld.order[i] = (int32_t)i;
+        out.bvh_root = bld.build(0, (int)item_ids.size(), 0);
+        out.bvh = std::move(bld.nodes);
+        out.bvh_depth = bld.depth;
+        if (out.bvh_depth + 2 > rtcdev::BVH_STACK) return "BVH deeper than the traversal stack";
+        out.leaf_items.resize(item_ids.size());
+        for (size_t i = 0; i < item_ids.size(); ++i) out.leaf_items[i] = item_ids[(size_t)bld.order[i]];
+        for (int k = 0; k < 3; ++k) { out.root_lo[k] = root.lo[k] - pad; out.root_hi[k] = root.hi[k] + pad; }
+    }
+    if (out.bvh.empty()) out.bvh.emplace_back();  // keep device pointers non-null
+    return "";
+}
+
+}  // namespace rtchost
