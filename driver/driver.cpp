@@ -94,6 +94,19 @@ int drv_render_device(void* h, const rtc_opts* opts, double** dev, uint64_t* n, 
     return 0;
 }
 
+// One end-to-end step = the body of Image::par_render on an already-flattened World: upload (rtc_scene_create),
+// render into the caller's host buffer (rtc_render: kernels + device->host copy), release (rtc_scene_destroy).
+int drv_e2e_step(void* h, int device, const rtc_opts* opts, double* out_rgb, rtc_stats* stats, char* err, int errlen) {
+    Session* s = (Session*)h;
+    const rtc_scene_desc d = s->flat->desc();
+    rtc_scene* scene = nullptr;
+    if (rtc_scene_create(&d, device, &scene) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+    const int rc = rtc_render(scene, &s->camera, opts, out_rgb, stats);
+    if (rc != 0) set_err(err, errlen, rtc_last_error());
+    rtc_scene_destroy(scene);
+    return rc;
+}
+
 // Image::par_render + Image::ppm through the public host API (the path a bin would take): returns the PPM text length.
 int64_t drv_par_render_ppm(const char* name, const char* data_dir, int hsize, int vsize, int device, char* out, int64_t out_cap, char* err, int errlen) {
     try {

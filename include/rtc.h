@@ -197,6 +197,14 @@ int64_t rtc_scene_stat(const rtc_scene* scene, int key);
  * scene would be accepted; stats (optional, 16 entries indexed by rtc_stat_key) are filled on success. */
 int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16);
 
+/* Page-locked host memory for out_rgb (optional: any host buffer works, pinned ones copy at full PCIe rate). */
+void* rtc_alloc_host(uint64_t bytes);
+void rtc_free_host(void* p);
+
+/* Measured roofline denominators on the current device: TFLOP/s (two flops per multiply-add pair) or GB/s. */
+enum rtc_microbench_kind { RTC_MB_FP64_FMA = 0, RTC_MB_FP64_MUL_ADD = 1, RTC_MB_FP32_FMA = 2, RTC_MB_FP32_MUL_ADD = 3, RTC_MB_L2_READ = 4 };
+int rtc_microbench(int what, double* result);
+
 /* Thread-local message for the last non-zero status. */
 const char* rtc_last_error(void);
 

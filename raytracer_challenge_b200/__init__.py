@@ -15,6 +15,9 @@ from .binding import (  # noqa: F401
     quantize,
     shard_pixels,
     device_count,
+    pinned_array,
+    free_pinned,
+    microbench,
     SCENES,
     DATA_DIR,
 )

@@ -80,8 +80,40 @@ def load_rtc():
         lib.rtc_scene_destroy.argtypes = [C.c_void_p]
         lib.rtc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.rtc_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.rtc_alloc_host.restype = C.c_void_p
+        lib.rtc_alloc_host.argtypes = [C.c_uint64]
+        lib.rtc_free_host.argtypes = [C.c_void_p]
+        lib.rtc_microbench.argtypes = [C.c_int, C.c_void_p]
         _rtc = lib
     return _rtc
+
+
+def pinned_array(shape, dtype=np.float64):
+    """numpy array backed by page-locked host memory (rtc_alloc_host); keeps its allocation alive."""
+    lib = load_rtc()
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    ptr = lib.rtc_alloc_host(n)
+    if not ptr:
+        raise RtcError(lib.rtc_last_error().decode())
+    buf = (C.c_char * n).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+    return arr, ptr
+
+
+def free_pinned(ptr):
+    load_rtc().rtc_free_host(ptr)
+
+
+def microbench():
+    """Measured FP64/FP32 issue rates (TFLOP/s) and L2 read bandwidth (GB/s) on the current device."""
+    lib = load_rtc()
+    out = {}
+    for key, what in (("fp64_fma_tflops", 0), ("fp64_mul_add_tflops", 1), ("fp32_fma_tflops", 2), ("fp32_mul_add_tflops", 3), ("l2_read_gbs", 4)):
+        v = C.c_double()
+        if lib.rtc_microbench(what, C.byref(v)) != 0:
+            raise RtcError("rtc_microbench failed")
+        out[key] = v.value
+    return out
 
 
 def load_driver():

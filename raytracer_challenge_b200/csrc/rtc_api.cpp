@@ -88,6 +88,18 @@ int rtc_device_count(void) {
     return n;
 }
 
+void* rtc_alloc_host(uint64_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        g_error = "rtc_alloc_host: cudaHostAlloc failed";
+        return nullptr;
+    }
+    return p;
+}
+void rtc_free_host(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
 void rtc_quantize(const double* rgb, uint8_t* out, uint64_t n) {
     // Color::clamp, src/color.rs:42-46: min(1).max(0) * 255, round half away from zero, saturating cast
     for (uint64_t i = 0; i < n; ++i) {

@@ -1,0 +1,25 @@
+"""Quick device-side timing of the named scenes (kernel ms, rays, Mrays/s).  Usage: perf_probe.py [scene WxH]..."""
+import sys, os, time, json
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import raytracer_challenge_b200 as R
+
+cases = sys.argv[1:] or ["teapot:3840x2160", "glass_air_bubble:1920x1080", "benchmark:3840x2160", "hexagon:3840x2160", "csg_noise:1920x1080"]
+if "--microbench" in cases:
+    cases.remove("--microbench")
+    print(json.dumps(R.microbench()))
+for c in cases:
+    name, res = c.split(":")
+    w, h = map(int, res.split("x"))
+    t0 = time.time()
+    s = R.Session(name, w, h, device=0)
+    t_open = time.time() - t0
+    best = None
+    for i in range(4):
+        _, n, st = s.render_device(R.Opts())
+        if best is None or st.ms_kernels < best.ms_kernels:
+            best = st
+    out, st2 = s.render(R.Opts())
+    print(json.dumps({"scene": name, "res": res, "open_s": round(t_open, 3), "ms_kernels": round(best.ms_kernels, 3), "rays": best.rays,
+                      "mrays_s": round(best.rays / best.ms_kernels / 1e3, 1), "rays_ref": best.rays_ref, "launches": best.kernel_launches,
+                      "e2e_ms_total": round(st2.ms_total, 2), "d2h_ms": round(st2.ms_d2h, 2), "build": s.build_stats}))
+    s.close()
