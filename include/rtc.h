@@ -147,7 +147,7 @@ typedef struct rtc_stats {
     double ms_total;         /* rtc_render entry -> last pixel in host memory */
     double ms_kernels;       /* CUDA-event time of all kernels of this call */
     double ms_trace_shade;   /* CUDA-event time of the wavefront kernels only */
-    double ms_d2h;           /* device -> host copy */
+    double ms_d2h;           /* reserved (0): rtc_render copies each finished batch out while later batches are traced */
     int32_t overflow;        /* non-zero: an on-chip list overflowed; result invalid (call fails) */
     int32_t reserved;
 } rtc_stats;
@@ -168,8 +168,9 @@ void rtc_scene_destroy(rtc_scene* scene);
  * Replaces the body of Image::par_render (src/image.rs:65-81).  0 = ok. */
 int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* out_rgb, rtc_stats* stats);
 
-/* Same, but leaves the result in device memory owned by the scene (valid until the next render
- * or destroy); *out_dev_rgb receives the device pointer (f64 triples), *out_pixels the count. */
+/* Same, but leaves the result in device memory owned by the library's per-device render context (valid until
+ * the next render on that device or rtc_release_device_memory); *out_dev_rgb receives the device pointer (f64
+ * triples), *out_pixels the count. */
 int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double** out_dev_rgb,
                       uint64_t* out_pixels, rtc_stats* stats);
 
@@ -189,13 +190,17 @@ void rtc_quantize(const double* rgb, uint8_t* out, uint64_t n);
 enum rtc_stat_key {
     RTC_STAT_PRIMS = 0, RTC_STAT_BVH_NODES = 1, RTC_STAT_BVH_DEPTH = 2, RTC_STAT_UNBOUNDED = 3,
     RTC_STAT_GATES_EXACT = 4, RTC_STAT_GATES_CONSERVATIVE = 5, RTC_STAT_GATES_ALWAYS_PASS = 6,
-    RTC_STAT_CSG_ROOTS = 7, RTC_STAT_XFORMS = 8, RTC_STAT_FEATURES = 9, RTC_STAT_BVH_ITEMS = 10
+    RTC_STAT_CSG_ROOTS = 7, RTC_STAT_XFORMS = 8, RTC_STAT_FEATURES = 9, RTC_STAT_BVH_ITEMS = 10, RTC_STAT_DEVICE_BYTES = 11
 };
 int64_t rtc_scene_stat(const rtc_scene* scene, int key);
 
 /* Runs the host half of scene upload only (validation, flattening, BVH build) — no GPU needed.  0 = the
  * scene would be accepted; stats (optional, 16 entries indexed by rtc_stat_key) are filled on success. */
 int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16);
+
+/* The library keeps its render scratch (ray queues, hit lists, frame buffer) per device across scenes, so that
+ * create-render-destroy per frame (what Image::par_render does) does not reallocate it.  This frees it. */
+void rtc_release_device_memory(int device);
 
 /* Page-locked host memory for out_rgb (optional: any host buffer works, pinned ones copy at full PCIe rate). */
 void* rtc_alloc_host(uint64_t bytes);

@@ -195,26 +195,74 @@ __device__ __forceinline__ void load_tri(const double* __restrict__ rec, V3& a, 
     c = mk(q3.x, q3.y, q4.x);
 }
 
-// All crossings of primitive `p` with the WORLD ray (src/shape.rs:414-417 + :862-885).
-__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, Roots& out) {
-    out.n = 0;
-    const double* m = sc.xforms[p.xform].inv;
+// World ray -> object space (Ray::transform, src/ray.rs:14-19), cached per transform id: consecutive items that
+// share a transform (all triangles of a mesh do) reuse the transformed ray, bit-identical to recomputing it.
+struct ObjRay {
+    int xform;
     Ray r;
-    r.o = xf_point(m, world.o);
-    r.d = xf_dir(m, world.d);
-    const int kind = p.kind_flags & 0xff;
+};
+__device__ __forceinline__ void load_xform_inv(const Scene& sc, int xform, double* __restrict__ m) {
+    const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv);  // 192-byte records, 16-byte aligned
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const double2 v = __ldg(q + k);
+        m[2 * k] = v.x;
+        m[2 * k + 1] = v.y;
+    }
+}
+__device__ __forceinline__ const Ray& object_ray(const Scene& sc, const Ray& world, int xform, ObjRay& c) {
+    if (xform != c.xform) {
+        double m[12];
+        load_xform_inv(sc, xform, m);
+        c.r.o = xf_point(m, world.o);
+        c.r.d = xf_dir(m, world.d);
+        c.xform = xform;
+    }
+    return c.r;
+}
+
+// All crossings of one primitive with the object-space ray r (src/shape.rs:862-885).  Out of line on purpose: the
+// seven intersectors with their f64 divisions and square roots are ~2 000 instructions, and every kernel that can
+// meet an arbitrary primitive shares this one copy (the hot kinds are inlined at their call sites instead).
+// tri_rec: the primitive's (p1, e1, e2) record if it is a triangle.
+__device__ __noinline__ void roots_generic(const Scene& sc, int kind_flags, int geom, const double* __restrict__ tri_rec, const Ray& r, Roots& out) {
+    const int kind = kind_flags & 0xff;
     switch (kind) {
         case 0: isect_sphere(r, out); break;
         case 1: isect_plane(r, out); break;
         case 2: isect_cube(r, out); break;
-        case 3: isect_cylinder(r, sc.ranges[2 * p.geom], sc.ranges[2 * p.geom + 1], (p.kind_flags & 0x200) != 0, out); break;
-        case 4: isect_cone(r, sc.ranges[2 * p.geom], sc.ranges[2 * p.geom + 1], (p.kind_flags & 0x200) != 0, out); break;
+        case 3: isect_cylinder(r, __ldg(sc.ranges + 2 * geom), __ldg(sc.ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
+        case 4: isect_cone(r, __ldg(sc.ranges + 2 * geom), __ldg(sc.ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
         default: {
             V3 p1, e1, e2;
-            load_tri(sc.tri_pe + 10 * (size_t)p.geom, p1, e1, e2);
+            load_tri(tri_rec, p1, e1, e2);
             isect_triangle(r, p1, e1, e2, out);
         }
     }
+}
+
+// HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6).
+template <int HOT>
+__device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int xform, int geom, const double* __restrict__ tri_rec,
+                                           const Ray& world, ObjRay& cache, Roots& out) {
+    out.n = 0;
+    const Ray& r = object_ray(sc, world, xform, cache);
+    const int kind = kind_flags & 0xff;
+    if ((HOT & 0x60) && kind >= 5) {
+        V3 p1, e1, e2;
+        load_tri(tri_rec, p1, e1, e2);
+        isect_triangle(r, p1, e1, e2, out);
+    } else if ((HOT & 0x01) && kind == 0) {
+        isect_sphere(r, out);
+    } else if ((HOT & 0x02) && kind == 1) {
+        isect_plane(r, out);
+    } else {
+        roots_generic(sc, kind_flags, geom, tri_rec, r, out);
+    }
+}
+template <int HOT>
+__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, ObjRay& cache, Roots& out) {
+    prim_roots<HOT>(sc, p.kind_flags, p.xform, p.geom, sc.tri_pe + 10 * (size_t)(p.geom < 0 ? 0 : p.geom), world, cache, out);
 }
 
 // src/shape.rs:419-427 + :887-946 — world normal at a world point (not yet flipped towards the eye)

@@ -75,6 +75,16 @@ struct BvhNode {
     int32_t pad0, pad1;
 };
 
+// One BVH item in LEAF ORDER: everything the traversal needs to test it without touching prims[].
+// Triangles additionally have their (p1, e1, e2) record at the same slot of Scene::leaf_tri, so the items of
+// one leaf are contiguous in memory and a leaf visit is two independent loads instead of a dependent chain.
+struct LeafItem {
+    int32_t id;          // >= 0 primitive index, < 0: ~csg_root index
+    int32_t kind_flags;  // as Prim::kind_flags (unused for CSG roots)
+    int32_t xform;
+    int32_t geom;        // cylinder / cone: slot in ranges
+};  // 16 B
+
 // CSG evaluation program of one top-level CSG item (post-order over its subtree).
 //   OP_PRIM  a = primitive index
 //   OP_BEGIN                     (push list length)
@@ -100,7 +110,8 @@ struct Scene {
     const Light* lights;
     const Gate* gates;
     const BvhNode* bvh;
-    const int32_t* leaf_items;  // >= 0 primitive index, < 0: ~csg_root index
+    const LeafItem* leaf_items; // BVH items in leaf order
+    const double* leaf_tri;     // 10 doubles per BVH item (triangles only: p1, e1, e2, pad), leaf order
     const int32_t* unbounded;   // items tested for every ray (planes, cones, infinite cylinders, CSG holding one)
     const CsgOp* csg_ops;
     const CsgRoot* csg_roots;

@@ -8,6 +8,9 @@
 // of those the ray really crosses and the result equals the brute-force scan.  Accepted primitives are
 // intersected in f64 with the reference's own arithmetic.  Ties in t resolve to the lower primitive index
 // (= depth-first order = what the reference's stable sort yields).
+//
+// Each query is instantiated once per kernel (the kernels of render_kernels.cu hold one traversal each), which
+// keeps the instruction footprint of a kernel small: profiles/README.md, "Reading of r01a".
 #pragma once
 #include "device_math.cuh"
 
@@ -24,6 +27,21 @@ struct Cross {
     int pad;
 };
 
+__device__ __forceinline__ Prim load_prim(const Scene& sc, int id) {
+    const int4* q = reinterpret_cast<const int4*>(sc.prims + id);
+    const int4 a = __ldg(q), b = __ldg(q + 1);
+    Prim p;
+    p.kind_flags = a.x; p.material = a.y; p.xform = a.z; p.matinv = a.w;
+    p.geom = b.x; p.gate_mask = (uint32_t)b.y; p.pad0 = 0; p.pad1 = 0;
+    return p;
+}
+__device__ __forceinline__ LeafItem load_leaf(const Scene& sc, int slot) {
+    const int4 a = __ldg(reinterpret_cast<const int4*>(sc.leaf_items + slot));
+    LeafItem li;
+    li.id = a.x; li.kind_flags = a.y; li.xform = a.z; li.geom = a.w;
+    return li;
+}
+
 __device__ __forceinline__ bool allows_intersection(int kind, bool left_hit, bool in_left, bool in_right) {  // src/shape.rs:169-178
     if (kind == 0) return (left_hit && !in_right) || (!left_hit && !in_left);
     if (kind == 1) return (left_hit && in_right) || (!left_hit && in_left);
@@ -38,24 +56,48 @@ __device__ __forceinline__ uint32_t gates_passed(const Scene& sc, const Ray& ray
             if (box_gate(sc.gates[g], ray)) m |= 1u << g;
     return m;
 }
+
+// Shared state of one query: the world ray, the object-space ray cache and the group-box gates it passed.
 template <int FEAT>
-__device__ __forceinline__ bool gate_ok(const Prim& p, uint32_t passed) {
-    return !(FEAT & FEAT_GATES) || (p.gate_mask & ~passed) == 0u;
-}
+struct Query {
+    const Scene& sc;
+    const Ray& ray;
+    uint32_t passed;
+    ObjRay cache;
+    int* overflow;
+    __device__ __forceinline__ Query(const Scene& s, const Ray& r, int* ovf) : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), overflow(ovf) {
+        cache.xform = -1;
+    }
+    __device__ __forceinline__ bool gate_ok(int prim_id) const {
+        if (!(FEAT & FEAT_GATES)) return true;
+        return (__ldg(&sc.prims[prim_id].gate_mask) & ~passed) == 0u;
+    }
+    // crossings of primitive `id` (by index: unbounded list, CSG programs, brute force)
+    __device__ __forceinline__ void roots_of_prim(int id, Roots& r) {
+        r.n = 0;
+        const Prim p = load_prim(sc, id);
+        if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
+        prim_roots<0x02>(sc, p, ray, cache, r);  // planes are the usual always-tested primitive
+    }
+    // crossings of a BVH leaf item that is a primitive
+    __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
+        r.n = 0;
+        if (!gate_ok(li.id)) return;
+        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, r);  // triangles, spheres
+    }
+};
 
 // Group::intersect for a CSG subtree (src/shape.rs:230-269): gather, stable-sort by t, filter, recursively.
 // Returns the number of surviving crossings in `list` (sorted by t), or -1 on overflow.
 template <int FEAT>
-__device__ __noinline__ int csg_eval(const Scene& sc, const CsgRoot& root, const Ray& ray, uint32_t passed, Cross* list) {
+__device__ __noinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cross* list) {
     int marks[MAX_CSG_MARKS];
     int nm = 0, n = 0;
     for (int k = 0; k < root.n_ops; ++k) {
-        const CsgOp op = sc.csg_ops[root.first_op + k];
+        const CsgOp op = q.sc.csg_ops[root.first_op + k];
         if (op.op == OP_PRIM) {
-            const Prim p = sc.prims[op.a];
-            if (!gate_ok<FEAT>(p, passed)) continue;
             Roots r;
-            prim_roots(sc, p, ray, r);
+            q.roots_of_prim(op.a, r);
             if (n + r.n > MAX_CSG_LIST) return -1;
             for (int j = 0; j < r.n; ++j) { list[n].t = r.t[j]; list[n].prim = op.a; n++; }
         } else if (op.op == OP_BEGIN) {
@@ -130,13 +172,17 @@ __device__ __forceinline__ bool slab(const Walk& w, float lx, float ly, float lz
     return t0 <= t1;
 }
 
-// Visitor protocol:  bool V::item(int id)   -> true stops the walk;   double V::tmax()  -> current upper bound on t.
+// upper end of the admissible interval relative to the re-origin, rounded up (conservative)
+__device__ __forceinline__ float walk_thi(double tmax, double te) { return __double2float_ru(__dsub_ru(tmax, te)); }
+
+// Visitor protocol:  bool V::leaf(int slot) -> true stops the walk;  double V::tmax() -> current upper bound on t
+// (re-read only after a leaf was visited: it cannot change in between).
 template <class V>
 __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v) {
     if (sc.n_bvh_items == 0) return;
     if (brute) {
         for (int i = 0; i < sc.n_bvh_items; ++i)
-            if (v.item(sc.leaf_items[i])) return;
+            if (v.leaf(i)) return;
         return;
     }
     Walk w;
@@ -144,11 +190,11 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
     int stack[BVH_STACK];
     int sp = 0;
     int link = sc.bvh_root;
+    float thi = walk_thi(v.tmax(), w.te);
     for (;;) {
         if (link >= 0) {
             const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
             const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-            const float thi = __double2float_ru(__dsub_ru(v.tmax(), w.te));
             float n0, n1;
             const bool h0 = slab(w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
             const bool h1 = slab(w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
@@ -165,7 +211,8 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
             const int enc = ~link;
             const int first = enc >> 2, count = (enc & 3) + 1;
             for (int i = 0; i < count; ++i)
-                if (v.item(sc.leaf_items[first + i])) return;
+                if (v.leaf(first + i)) return;
+            thi = walk_thi(v.tmax(), w.te);
         }
         if (sp == 0) return;
         link = stack[--sp];
@@ -175,50 +222,60 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
 // ---- closest hit ---------------------------------------------------------------------------------
 template <int FEAT>
 struct ClosestVisitor {
-    const Scene& sc;
-    const Ray& ray;
-    uint32_t passed;
+    Query<FEAT> q;
     Hit best;
     double limit;   // exclusive upper bound on t (shadow queries on scenes with non-casting shapes), else +inf
-    int* overflow;
+    __device__ __forceinline__ ClosestVisitor(const Scene& sc, const Ray& ray, double lim, int* ovf) : q(sc, ray, ovf), limit(lim) {
+        best.t = 0.0; best.prim = -1; best.u = 0.0; best.v = 0.0;
+    }
     __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : limit; }
     __device__ __forceinline__ void offer(double t, int prim, double u, double v) {
         if (t >= 0.0 && t < limit && (best.prim < 0 || t < best.t || (t == best.t && prim < best.prim))) {
             best.t = t; best.prim = prim; best.u = u; best.v = v;
         }
     }
-    __device__ __forceinline__ bool item(int id) {
-        if (!(FEAT & FEAT_CSG) || id >= 0) {
-            const Prim p = sc.prims[id];
-            if (!gate_ok<FEAT>(p, passed)) return false;
-            Roots r;
-            prim_roots(sc, p, ray, r);
-            for (int k = 0; k < r.n; ++k) offer(r.t[k], id, r.u, r.v);
-        } else {
-            Cross list[MAX_CSG_LIST];
-            const int n = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
-            if (n < 0) { *overflow = 1; return true; }
-            for (int k = 0; k < n; ++k)
-                if (list[k].t >= 0.0) {  // list is sorted: the first non-negative entry is this item's hit
-                    double u = 0.0, v = 0.0;
-                    const Prim p = sc.prims[list[k].prim];
-                    if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
-                        Roots r;
-                        prim_roots(sc, p, ray, r);
-                        u = r.u; v = r.v;
-                    }
-                    offer(list[k].t, list[k].prim, u, v);
-                    break;
+    __device__ __forceinline__ void offer_roots(const Roots& r, int id) {
+        for (int k = 0; k < r.n; ++k) offer(r.t[k], id, r.u, r.v);
+    }
+    __device__ __noinline__ bool csg(int root) {
+        Cross list[MAX_CSG_LIST];
+        const int n = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
+        if (n < 0) { *q.overflow = 1; return true; }
+        for (int k = 0; k < n; ++k)
+            if (list[k].t >= 0.0) {  // list is sorted: the first non-negative entry is this item's hit
+                double u = 0.0, v = 0.0;
+                const Prim p = load_prim(q.sc, list[k].prim);
+                if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
+                    Roots r;
+                    prim_roots<0>(q.sc, p, q.ray, q.cache, r);
+                    u = r.u; v = r.v;
                 }
-        }
+                offer(list[k].t, list[k].prim, u, v);
+                break;
+            }
+        return false;
+    }
+    __device__ __forceinline__ bool item(int id) {  // unbounded list entry
+        if ((FEAT & FEAT_CSG) && id < 0) return csg(~id);
+        Roots r;
+        q.roots_of_prim(id, r);
+        offer_roots(r, id);
+        return false;
+    }
+    __device__ __forceinline__ bool leaf(int slot) {
+        const LeafItem li = load_leaf(q.sc, slot);
+        if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
+        Roots r;
+        q.roots_of_leaf(li, slot, r);
+        offer_roots(r, li.id);
         return false;
     }
 };
 
 template <int FEAT>
 __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, int* overflow) {
-    ClosestVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), Hit{0.0, -1, 0.0, 0.0}, limit, overflow};
-    for (int i = 0; i < sc.n_unbounded; ++i) v.item(sc.unbounded[i]);
+    ClosestVisitor<FEAT> v(sc, ray, limit, overflow);
+    for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
     walk_bvh(sc, ray, 0, brute, v);
     return v.best;
 }
@@ -226,87 +283,99 @@ __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, doub
 // ---- shadow query: World::is_shadowed (src/world.rs:26-48) -------------------------------------------
 template <int FEAT>
 struct AnyVisitor {
-    const Scene& sc;
-    const Ray& ray;
-    uint32_t passed;
+    Query<FEAT> q;
     double dist;
     bool found;
-    int* overflow;
+    __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, int* ovf) : q(sc, ray, ovf), dist(d), found(false) {}
     __device__ __forceinline__ double tmax() const { return dist; }
-    __device__ __forceinline__ bool item(int id) {
-        if (!(FEAT & FEAT_CSG) || id >= 0) {
-            const Prim p = sc.prims[id];
-            if (!gate_ok<FEAT>(p, passed)) return false;
-            Roots r;
-            prim_roots(sc, p, ray, r);
-            for (int k = 0; k < r.n; ++k)
-                if (r.t[k] >= 0.0 && r.t[k] < dist) { found = true; return true; }
-        } else {
-            Cross list[MAX_CSG_LIST];
-            const int n = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
-            if (n < 0) { *overflow = 1; return true; }
-            for (int k = 0; k < n; ++k)
-                if (list[k].t >= 0.0 && list[k].t < dist) { found = true; return true; }
-        }
+    __device__ __forceinline__ bool test(const Roots& r) {
+        for (int k = 0; k < r.n; ++k)
+            if (r.t[k] >= 0.0 && r.t[k] < dist) { found = true; return true; }
         return false;
+    }
+    __device__ __noinline__ bool csg(int root) {
+        Cross list[MAX_CSG_LIST];
+        const int n = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
+        if (n < 0) { *q.overflow = 1; return true; }
+        for (int k = 0; k < n; ++k)
+            if (list[k].t >= 0.0 && list[k].t < dist) { found = true; return true; }
+        return false;
+    }
+    __device__ __forceinline__ bool item(int id) {
+        if ((FEAT & FEAT_CSG) && id < 0) return csg(~id);
+        Roots r;
+        q.roots_of_prim(id, r);
+        return test(r);
+    }
+    __device__ __forceinline__ bool leaf(int slot) {
+        const LeafItem li = load_leaf(q.sc, slot);
+        if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
+        Roots r;
+        q.roots_of_leaf(li, slot, r);
+        return test(r);
     }
 };
 
 // shadowed <=> the nearest crossing with t >= 0 belongs to a casting shape and has t < distance.
+// Only instantiated for scenes where every primitive casts shadows: then "nearest t < dist" <=> "any t in
+// [0, dist)" and the walk may stop at the first such crossing.  (Scenes with non-casting shapes use closest_hit.)
 template <int FEAT>
-__device__ __forceinline__ bool is_shadowed(const Scene& sc, const Ray& ray, double dist, bool brute, int* overflow) {
-    if (sc.all_cast_shadow) {  // then "nearest t < dist" <=> "any t in [0, dist)": stop at the first one
-        AnyVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), dist, false, overflow};
-        for (int i = 0; i < sc.n_unbounded; ++i)
-            if (v.item(sc.unbounded[i])) return v.found;
-        walk_bvh(sc, ray, 0, brute, v);
-        return v.found;
-    }
-    const Hit h = closest_hit<FEAT>(sc, ray, dist, brute, overflow);
-    return h.prim >= 0 && (sc.prims[h.prim].kind_flags & 0x100) != 0;
+__device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, int* overflow) {
+    AnyVisitor<FEAT> v(sc, ray, dist, overflow);
+    for (int i = 0; i < sc.n_unbounded; ++i)
+        if (v.item(__ldg(sc.unbounded + i))) return v.found;
+    walk_bvh(sc, ray, 0, brute, v);
+    return v.found;
 }
 
 // ---- n1 / n2: replay of the container walk of Intersection::prepare_state (src/intersection.rs:70-103) ----
 template <int FEAT>
 struct CollectVisitor {
-    const Scene& sc;
-    const Ray& ray;
-    uint32_t passed;
+    Query<FEAT> q;
     double thit;
     Cross* out;
     int n;
-    int* overflow;
+    __device__ __forceinline__ CollectVisitor(const Scene& sc, const Ray& ray, double th, Cross* o, int* ovf) : q(sc, ray, ovf), thit(th), out(o), n(0) {}
     __device__ __forceinline__ double tmax() const { return thit; }
     __device__ __forceinline__ bool push(double t, int prim) {
         if (!(t <= thit)) return false;
-        if (n >= MAX_CROSSINGS) { *overflow = 1; return true; }
+        if (n >= MAX_CROSSINGS) { *q.overflow = 1; return true; }
         out[n].t = t; out[n].prim = prim; n++;
         return false;
     }
-    __device__ __forceinline__ bool item(int id) {
-        if (!(FEAT & FEAT_CSG) || id >= 0) {
-            const Prim p = sc.prims[id];
-            if (!gate_ok<FEAT>(p, passed)) return false;
-            Roots r;
-            prim_roots(sc, p, ray, r);
-            for (int k = 0; k < r.n; ++k)
-                if (push(r.t[k], id)) return true;
-        } else {
-            Cross list[MAX_CSG_LIST];
-            const int m = csg_eval<FEAT>(sc, sc.csg_roots[~id], ray, passed, list);
-            if (m < 0) { *overflow = 1; return true; }
-            for (int k = 0; k < m; ++k)
-                if (push(list[k].t, list[k].prim)) return true;
-        }
+    __device__ __forceinline__ bool push_roots(const Roots& r, int id) {
+        for (int k = 0; k < r.n; ++k)
+            if (push(r.t[k], id)) return true;
         return false;
+    }
+    __device__ __noinline__ bool csg(int root) {
+        Cross list[MAX_CSG_LIST];
+        const int m = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
+        if (m < 0) { *q.overflow = 1; return true; }
+        for (int k = 0; k < m; ++k)
+            if (push(list[k].t, list[k].prim)) return true;
+        return false;
+    }
+    __device__ __forceinline__ bool item(int id) {
+        if ((FEAT & FEAT_CSG) && id < 0) return csg(~id);
+        Roots r;
+        q.roots_of_prim(id, r);
+        return push_roots(r, id);
+    }
+    __device__ __forceinline__ bool leaf(int slot) {
+        const LeafItem li = load_leaf(q.sc, slot);
+        if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
+        Roots r;
+        q.roots_of_leaf(li, slot, r);
+        return push_roots(r, li.id);
     }
 };
 
 template <int FEAT>
-__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, const Hit& hit, bool brute, double& n1, double& n2, int* overflow) {
+__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, double hit_t, int hit_prim, bool brute, double& n1, double& n2, int* overflow) {
     Cross xs[MAX_CROSSINGS];
-    CollectVisitor<FEAT> v{sc, ray, gates_passed<FEAT>(sc, ray), hit.t, xs, 0, overflow};
-    for (int i = 0; i < sc.n_unbounded; ++i) v.item(sc.unbounded[i]);
+    CollectVisitor<FEAT> v(sc, ray, hit_t, xs, overflow);
+    for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
     walk_bvh(sc, ray, 1, brute, v);
     const int n = v.n;
     for (int i = 1; i < n; ++i) {  // order of the reference's sorted list: by t, ties in depth-first primitive order
@@ -320,7 +389,7 @@ __device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray,
     n1 = 1.0;
     n2 = 1.0;
     for (int i = 0; i < n; ++i) {
-        const bool is_hit = xs[i].t == hit.t && xs[i].prim == hit.prim;  // Intersection::eq, src/intersection.rs:135-139
+        const bool is_hit = xs[i].t == hit_t && xs[i].prim == hit_prim;  // Intersection::eq, src/intersection.rs:135-139
         if (is_hit) n1 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
         int at = -1;
         for (int k = 0; k < no; ++k)

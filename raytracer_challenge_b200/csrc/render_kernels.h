@@ -22,9 +22,14 @@ struct FrameParams {
     int32_t pad;
 };
 
-// Ray queue: structure-of-arrays of 16-byte chunks, so a warp's loads/stores are four fully coalesced
-// 512-byte transactions per ray record (64 B per ray):
-//   q0 = (origin.x, origin.y)  q1 = (origin.z, dir.x)  q2 = (dir.y, dir.z)  q3 = (throughput, fuel<<32 | sample)
+// One bounce level of one batch.  All arrays are structure-of-arrays of 16-byte chunks, so a warp's loads and
+// stores are fully coalesced 512-byte transactions.
+//   ray queue (64 B per ray):  q0 = (origin.x, origin.y)  q1 = (origin.z, dir.x)  q2 = (dir.y, dir.z)
+//                              q3 = (throughput, fuel<<32 | sample)
+//   hit list (compacted: one entry per ray that hit something; 36 / 52 B per hit):
+//                              hit_ray = index of the ray in the level's input,  hit0 = (t, primitive index)
+//                              hit1 = (u, v)   hit2 = (n1, n2) [scenes with transparent materials only]
+//   shadow[li * n_hits + h]    1 = light li is occluded at hit h
 struct LevelParams {
     const double2 *in_q0, *in_q1, *in_q2, *in_q3;
     double2 *out_q0, *out_q1, *out_q2, *out_q3;
@@ -33,13 +38,20 @@ struct LevelParams {
     uint64_t in_capacity, out_capacity;
     uint64_t first_sample;  // primary level: first sample ordinal of this batch
     uint64_t n_primary;     // primary level: samples in this batch
-    double* accum;          // 3 doubles per sample of the batch
-    unsigned long long* stats;  // [0] rays in, [1] shadow, [2] reflected pushed, [3] refracted pushed, [4] R_ref
+    uint32_t* hit_ray;
+    double2 *hit0, *hit1, *hit2;
+    unsigned long long* hit_count;
+    uint8_t* shadow;
+    double* accum;              // 3 doubles per sample of the batch
+    unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed
     int* overflow;
 };
 
 void upload_perm(const uint8_t* perm512);
-void launch_level(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+// The three kernels of one level, in launch order.
+void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+void launch_shadow(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+void launch_shade(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major);
 
 }  // namespace rtcdev

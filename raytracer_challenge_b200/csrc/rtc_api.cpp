@@ -5,7 +5,10 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -39,39 +42,90 @@ const uint8_t kPerm[256] = {
     81,  51,  145, 235, 249, 14,  239, 107, 49,  192, 214, 31,  181, 199, 106, 157, 184, 84,  204, 176, 115, 121, 50,  45,  127, 4,
     150, 254, 138, 236, 205, 93,  222, 114, 67,  29,  24,  72,  243, 141, 128, 195, 78,  66,  215, 61,  156, 180};
 
-template <class T>
-cudaError_t upload(const std::vector<T>& host, T** dev) {
-    *dev = nullptr;
-    const size_t bytes = std::max<size_t>(host.size(), 1) * sizeof(T);
-    cudaError_t e = cudaMalloc((void**)dev, bytes);
-    if (e != cudaSuccess) return e;
-    if (!host.empty()) e = cudaMemcpy(*dev, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice);
-    return e;
-}
+constexpr int MAX_PIPES = 4;
+constexpr int MAX_DEVICES = 64;
+constexpr int COUNTERS_PER_BATCH = 64;  // [0..15] queue counts per level, [16..31] hit counts per level, [32..34] stats
 
-struct Buffers {  // per-scene render scratch, grown on demand and reused across renders
+// Scratch of one pipeline (= one CUDA stream working through batches): ray queues (ping-pong), hit list, shadow
+// bytes, sample accumulators.
+struct Pipe {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
     double2* q[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
-    uint64_t q_capacity = 0;
+    uint32_t* hit_ray = nullptr;
+    double2* hit[3] = {nullptr, nullptr, nullptr};
+    uint8_t* shadow = nullptr;
     double* accum = nullptr;
-    uint64_t accum_samples = 0;
+    uint64_t q_capacity = 0, shadow_bytes = 0, accum_samples = 0;
+    bool hit2 = false;
+};
+
+// Per-device render context: streams, events and scratch memory.  It outlives scenes, so that the drop-in call
+// sequence of Image::par_render (create scene, render once, destroy scene) does not pay for gigabytes of
+// cudaMalloc / cudaFree per frame.  One render at a time per device (mutex); released by rtc_release_device_memory.
+struct DeviceCtx {
+    std::mutex mu;
+    bool ready = false;
+    int device = 0;
+    int sm_count = 0;
+    Pipe pipe[MAX_PIPES];
+    cudaEvent_t ev[2] = {nullptr, nullptr};
     double* out = nullptr;
     uint64_t out_pixels = 0;
-    unsigned long long* counters = nullptr;  // [0..15] queue counts, [16..23] stats
+    unsigned long long* counters = nullptr;
+    unsigned long long* counters_host = nullptr;  // pinned mirror
+    uint64_t counter_batches = 0;
     int* overflow = nullptr;
+    bool perm_uploaded = false;
 };
+DeviceCtx g_ctx[MAX_DEVICES];
+
+void free_pipe(Pipe& p) {
+    for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 4; ++b) { cudaFree(p.q[a][b]); p.q[a][b] = nullptr; }
+    cudaFree(p.hit_ray); p.hit_ray = nullptr;
+    for (auto& h : p.hit) { cudaFree(h); h = nullptr; }
+    cudaFree(p.shadow); p.shadow = nullptr;
+    cudaFree(p.accum); p.accum = nullptr;
+    p.q_capacity = p.shadow_bytes = p.accum_samples = 0;
+    p.hit2 = false;
+}
+
+int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the device
+    if (c.ready) return 0;
+    c.device = device;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    c.sm_count = prop.multiProcessorCount;
+    for (Pipe& p : c.pipe) {
+        CU(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
+    }
+    for (auto& e : c.ev) CU(cudaEventCreate(&e));
+    CU(cudaMalloc((void**)&c.overflow, sizeof(int)));
+    uint8_t perm[512];
+    for (int i = 0; i < 512; ++i) perm[i] = kPerm[i & 255];
+    rtcdev::upload_perm(perm);
+    CU(cudaGetLastError());
+    c.ready = true;
+    return 0;
+}
+
+int env_int(const char* name, int fallback, int lo, int hi) {
+    const char* v = std::getenv(name);
+    if (!v || !*v) return fallback;
+    const long x = std::strtol(v, nullptr, 10);
+    return (int)std::min<long>(std::max<long>(x, lo), hi);
+}
 
 }  // namespace
 
 struct rtc_scene {
     int device = 0;
-    int sm_count = 0;
     int feat = 0;
     rtchost::HostScene host;
     rtcdev::Scene dev{};
-    std::vector<void*> allocations;
-    Buffers buf;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    void* arena = nullptr;  // one device allocation holding every scene array
 };
 
 extern "C" {
@@ -149,6 +203,7 @@ static int64_t host_stat(const rtchost::HostScene& h, int key) {
             return (transparent ? rtcdev::FEAT_TRANSPARENT : 0) | (!h.csg_roots.empty() ? rtcdev::FEAT_CSG : 0) |
                    (!h.gates.empty() ? rtcdev::FEAT_GATES : 0);
         }
+        case RTC_STAT_DEVICE_BYTES: return h.device_bytes;
         default: return -1;
     }
 }
@@ -168,17 +223,22 @@ int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16) {
 void rtc_scene_destroy(rtc_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    for (void* p : s->allocations) cudaFree(p);
-    for (int a = 0; a < 2; ++a)
-        for (int b = 0; b < 4; ++b) cudaFree(s->buf.q[a][b]);
-    cudaFree(s->buf.accum);
-    cudaFree(s->buf.out);
-    cudaFree(s->buf.counters);
-    cudaFree(s->buf.overflow);
-    for (auto& e : s->ev)
-        if (e) cudaEventDestroy(e);
-    if (s->stream) cudaStreamDestroy(s->stream);
+    cudaFree(s->arena);
     delete s;
+}
+
+void rtc_release_device_memory(int device) {
+    if (device < 0 || device >= MAX_DEVICES) return;
+    DeviceCtx& c = g_ctx[device];
+    std::lock_guard<std::mutex> lock(c.mu);
+    if (!c.ready) return;
+    cudaSetDevice(device);
+    cudaDeviceSynchronize();
+    for (Pipe& p : c.pipe) free_pipe(p);
+    cudaFree(c.out); c.out = nullptr; c.out_pixels = 0;
+    cudaFree(c.counters); c.counters = nullptr;
+    cudaFreeHost(c.counters_host); c.counters_host = nullptr;
+    c.counter_batches = 0;
 }
 
 int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
@@ -187,49 +247,57 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     int n_dev = 0;
     CU(cudaGetDeviceCount(&n_dev));
     if (n_dev <= 0) return fail("rtc_scene_create: no CUDA device (this library has no CPU fallback)");
-    if (device < 0 || device >= n_dev) return fail("rtc_scene_create: device ordinal out of range");
-    rtc_scene* s = new rtc_scene;
+    if (device < 0 || device >= n_dev || device >= MAX_DEVICES) return fail("rtc_scene_create: device ordinal out of range");
+    std::unique_ptr<rtc_scene> s(new rtc_scene);
     s->device = device;
     const std::string err = rtchost::build_host_scene(*desc, s->host);
-    if (!err.empty()) {
-        delete s;
-        return fail("rtc_scene_create: " + err);
+    if (!err.empty()) return fail("rtc_scene_create: " + err);
+    CU(cudaSetDevice(device));
+    {
+        DeviceCtx& c = g_ctx[device];
+        std::lock_guard<std::mutex> lock(c.mu);
+        if (int rc = ctx_init(c, device)) return rc;
     }
-    auto bail = [&](const std::string& m) {
-        rtc_scene_destroy(s);
-        return fail(m);
-    };
-    if (cudaSetDevice(device) != cudaSuccess) return bail("cudaSetDevice failed");
-    cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail("cudaGetDeviceProperties failed");
-    s->sm_count = prop.multiProcessorCount;
 
-    const rtchost::HostScene& h = s->host;
+    // Pack every array into one staging blob (256-byte aligned sections): one cudaMalloc + one copy.
+    rtchost::HostScene& h = s->host;
     rtcdev::Scene& d = s->dev;
-#define UP(field, vec, type)                                                                  \
-    {                                                                                         \
-        type* p_ = nullptr;                                                                   \
-        cudaError_t e_ = upload(vec, &p_);                                                    \
-        if (p_) s->allocations.push_back(p_);                                                 \
-        if (e_ != cudaSuccess) return bail(std::string("upload " #field ": ") + cudaGetErrorString(e_)); \
-        d.field = p_;                                                                         \
+    std::vector<unsigned char> blob;
+    auto place = [&](const void* src, size_t bytes) -> size_t {
+        const size_t off = (blob.size() + 255) & ~(size_t)255;
+        blob.resize(off + std::max<size_t>(bytes, 16));
+        if (bytes) std::memcpy(blob.data() + off, src, bytes);
+        return off;
+    };
+#define PLACE(vec) place((vec).data(), (vec).size() * sizeof((vec)[0]))
+    const size_t o_prims = PLACE(h.prims), o_xforms = PLACE(h.xforms), o_matinvs = PLACE(h.matinvs), o_tri_pe = PLACE(h.tri_pe),
+                 o_tri_n = PLACE(h.tri_n), o_ranges = PLACE(h.ranges), o_materials = PLACE(h.materials), o_patterns = PLACE(h.patterns),
+                 o_lights = PLACE(h.lights), o_gates = PLACE(h.gates), o_bvh = PLACE(h.bvh), o_leaf_items = PLACE(h.leaf_items),
+                 o_leaf_tri = PLACE(h.leaf_tri), o_unbounded = PLACE(h.unbounded), o_csg_ops = PLACE(h.csg_ops), o_csg_roots = PLACE(h.csg_roots);
+#undef PLACE
+    h.device_bytes = (int64_t)blob.size();
+    if (cudaMalloc(&s->arena, blob.size()) != cudaSuccess) return fail("rtc_scene_create: cudaMalloc of the scene arena failed");
+    if (cudaMemcpy(s->arena, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaFree(s->arena);
+        return fail(std::string("rtc_scene_create: scene upload failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
-    UP(prims, h.prims, rtcdev::Prim)
-    UP(xforms, h.xforms, rtcdev::Xform)
-    UP(matinvs, h.matinvs, rtcdev::MatInv)
-    UP(tri_pe, h.tri_pe, double)
-    UP(tri_n, h.tri_n, double)
-    UP(ranges, h.ranges, double)
-    UP(materials, h.materials, rtcdev::Material)
-    UP(patterns, h.patterns, rtcdev::Pattern)
-    UP(lights, h.lights, rtcdev::Light)
-    UP(gates, h.gates, rtcdev::Gate)
-    UP(bvh, h.bvh, rtcdev::BvhNode)
-    UP(leaf_items, h.leaf_items, int32_t)
-    UP(unbounded, h.unbounded, int32_t)
-    UP(csg_ops, h.csg_ops, rtcdev::CsgOp)
-    UP(csg_roots, h.csg_roots, rtcdev::CsgRoot)
-#undef UP
+    unsigned char* base = (unsigned char*)s->arena;
+    d.prims = (const rtcdev::Prim*)(base + o_prims);
+    d.xforms = (const rtcdev::Xform*)(base + o_xforms);
+    d.matinvs = (const rtcdev::MatInv*)(base + o_matinvs);
+    d.tri_pe = (const double*)(base + o_tri_pe);
+    d.tri_n = (const double*)(base + o_tri_n);
+    d.ranges = (const double*)(base + o_ranges);
+    d.materials = (const rtcdev::Material*)(base + o_materials);
+    d.patterns = (const rtcdev::Pattern*)(base + o_patterns);
+    d.lights = (const rtcdev::Light*)(base + o_lights);
+    d.gates = (const rtcdev::Gate*)(base + o_gates);
+    d.bvh = (const rtcdev::BvhNode*)(base + o_bvh);
+    d.leaf_items = (const rtcdev::LeafItem*)(base + o_leaf_items);
+    d.leaf_tri = (const double*)(base + o_leaf_tri);
+    d.unbounded = (const int32_t*)(base + o_unbounded);
+    d.csg_ops = (const rtcdev::CsgOp*)(base + o_csg_ops);
+    d.csg_roots = (const rtcdev::CsgRoot*)(base + o_csg_roots);
     d.n_prims = (int32_t)h.prims.size();
     d.n_lights = (int32_t)h.lights.size();
     d.n_gates = (int32_t)h.gates.size();
@@ -240,54 +308,42 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     d.all_cast_shadow = h.all_cast_shadow;
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
-
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
-
-    uint8_t perm[512];
-    for (int i = 0; i < 512; ++i) perm[i] = kPerm[i & 255];
-    rtcdev::upload_perm(perm);
-    if (cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) != cudaSuccess) return bail("cudaStreamCreate failed");
-    for (auto& e : s->ev)
-        if (cudaEventCreate(&e) != cudaSuccess) return bail("cudaEventCreate failed");
-    if (cudaMalloc((void**)&s->buf.counters, 32 * sizeof(unsigned long long)) != cudaSuccess) return bail("cudaMalloc counters failed");
-    if (cudaMalloc((void**)&s->buf.overflow, sizeof(int)) != cudaSuccess) return bail("cudaMalloc flag failed");
-    if (cudaDeviceSynchronize() != cudaSuccess) return bail(std::string("scene upload: ") + cudaGetErrorString(cudaGetLastError()));
-    *out = s;
+    *out = s.release();
     return 0;
 }
 
-static int ensure_buffers(rtc_scene* s, uint64_t q_capacity, uint64_t accum_samples, uint64_t out_pixels) {
-    Buffers& b = s->buf;
-    if (q_capacity > b.q_capacity) {
+static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t shadow_bytes, uint64_t accum_samples, bool hit2) {
+    if (q_capacity > p.q_capacity || (hit2 && !p.hit2)) {
+        const uint64_t acc = p.accum_samples, sh = p.shadow_bytes;
+        double* keep_accum = p.accum; uint8_t* keep_shadow = p.shadow;
+        p.accum = nullptr; p.shadow = nullptr;
+        free_pipe(p);
+        p.accum = keep_accum; p.accum_samples = acc; p.shadow = keep_shadow; p.shadow_bytes = sh;
         for (int a = 0; a < 2; ++a)
-            for (int c = 0; c < 4; ++c) {
-                cudaFree(b.q[a][c]);
-                b.q[a][c] = nullptr;
-            }
-        b.q_capacity = 0;
-        for (int a = 0; a < 2; ++a)
-            for (int c = 0; c < 4; ++c) CU(cudaMalloc((void**)&b.q[a][c], q_capacity * sizeof(double2)));
-        b.q_capacity = q_capacity;
+            for (int c = 0; c < 4; ++c) CU(cudaMalloc((void**)&p.q[a][c], q_capacity * sizeof(double2)));
+        CU(cudaMalloc((void**)&p.hit_ray, q_capacity * sizeof(uint32_t)));
+        for (int c = 0; c < (hit2 ? 3 : 2); ++c) CU(cudaMalloc((void**)&p.hit[c], q_capacity * sizeof(double2)));
+        p.q_capacity = q_capacity;
+        p.hit2 = hit2;
     }
-    if (accum_samples > b.accum_samples) {
-        cudaFree(b.accum);
-        b.accum = nullptr;
-        b.accum_samples = 0;
-        CU(cudaMalloc((void**)&b.accum, accum_samples * 3 * sizeof(double)));
-        b.accum_samples = accum_samples;
+    if (shadow_bytes > p.shadow_bytes) {
+        cudaFree(p.shadow); p.shadow = nullptr; p.shadow_bytes = 0;
+        CU(cudaMalloc((void**)&p.shadow, shadow_bytes));
+        p.shadow_bytes = shadow_bytes;
     }
-    if (out_pixels > b.out_pixels) {
-        cudaFree(b.out);
-        b.out = nullptr;
-        b.out_pixels = 0;
-        CU(cudaMalloc((void**)&b.out, out_pixels * 3 * sizeof(double)));
-        b.out_pixels = out_pixels;
+    if (accum_samples > p.accum_samples) {
+        cudaFree(p.accum); p.accum = nullptr; p.accum_samples = 0;
+        CU(cudaMalloc((void**)&p.accum, accum_samples * 3 * sizeof(double)));
+        p.accum_samples = accum_samples;
     }
     return 0;
 }
 
-int rtc_render_device(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in, double** out_dev_rgb, uint64_t* out_pixels,
-                      rtc_stats* stats) {
+// The body shared by rtc_render (host_out != null: each finished batch is copied to the host while later batches
+// are still being traced) and rtc_render_device (host_out == null).
+static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in, double* host_out, double** out_dev_rgb,
+                       uint64_t* out_pixels, rtc_stats* stats) {
     if (!s || !cam) return fail("rtc_render: null argument");
     rtc_opts o{};
     if (o_in) o = *o_in;
@@ -301,15 +357,18 @@ int rtc_render_device(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in,
     if (o.fuel > 12) return fail("rtc_render: fuel > 12 not supported");
     if (o.shard_index < 0 || o.shard_index >= o.shard_count) return fail("rtc_render: shard_index out of range");
     if (cam->hsize <= 0 || cam->vsize <= 0) return fail("rtc_render: empty camera image");
+    if ((int64_t)o.spp_x * o.spp_y > 4096) return fail("rtc_render: more than 4096 samples per pixel");
     const bool whole = o.win_w <= 0 || o.win_h <= 0;
     const int32_t wx0 = whole ? 0 : o.win_x0, wy0 = whole ? 0 : o.win_y0;
     const int32_t ww = whole ? cam->hsize : o.win_w, wh = whole ? cam->vsize : o.win_h;
     if (wx0 < 0 || wy0 < 0 || (int64_t)wx0 + ww > cam->hsize || (int64_t)wy0 + wh > cam->vsize) return fail("rtc_render: window outside the image");
-    if ((int64_t)ww * wh >= 0xffffffffll) return fail("rtc_render: window too large");
     for (int i = 12; i < 16; ++i)  // last row equals (0,0,0,1) only up to the rounding of the reference's inverse
         if (!(std::fabs(cam->transform_inv[i] - (i == 15 ? 1.0 : 0.0)) <= 1e-9)) return fail("rtc_render: camera transform is not affine");
 
     CU(cudaSetDevice(s->device));
+    DeviceCtx& ctx = g_ctx[s->device];
+    std::lock_guard<std::mutex> lock(ctx.mu);
+    if (int rc = ctx_init(ctx, s->device)) return rc;
     const auto t_begin = std::chrono::steady_clock::now();
 
     rtcdev::FrameParams f{};
@@ -327,106 +386,162 @@ int rtc_render_device(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in,
     f.flags = o.flags;
 
     const uint64_t per_tile = (uint64_t)o.tile_w * o.tile_h;
+    const uint64_t all_slots = (uint64_t)f.tiles_x * f.tiles_y * per_tile;  // padded pixel slots of the whole window
+    if (all_slots * (uint64_t)f.spp >= 0x7fffffffull) return fail("rtc_render: window too large (pixel slots x samples must stay below 2^31)");
     const uint64_t n_slots = rtc_shard_pixels(ww, wh, o.tile_w, o.tile_h, o.shard_index, o.shard_count, nullptr);  // incl. tile padding
     const bool row_major = o.shard_count == 1;
     const uint64_t n_out = row_major ? (uint64_t)ww * wh : n_slots;
+    const int L = s->dev.n_lights;
 
-    // Batch size: whole tiles; queues sized for the worst-case fan-out (binary tree only if some material both
-    // reflects and refracts), capped so both ping-pong queues stay within ~4 GiB.
+    // Batches: whole tiles (row-major output: whole tile ROWS, so a batch is a contiguous band of the image and can
+    // be copied out on its own).  Queues are sized for the worst-case fan-out: a binary tree only if some material
+    // both reflects and refracts.
     const int fan = s->dev.max_children >= 2 ? 2 : 1;
     uint64_t worst = 1;
     for (int k = 0; k < o.fuel && fan == 2; ++k) worst *= 2;
-    const uint64_t max_records = (uint64_t)32 << 20;  // 32 Mi records * 64 B = 2 GiB per queue
-    uint64_t batch_samples = std::max<uint64_t>(max_records / worst, per_tile * f.spp);
-    batch_samples = std::min<uint64_t>(batch_samples, (uint64_t)8 << 20);
-    uint64_t batch_pixels = std::max<uint64_t>(batch_samples / f.spp / per_tile, 1) * per_tile;
-    batch_pixels = std::min(batch_pixels, std::max<uint64_t>(n_slots, per_tile));
+    const uint64_t unit = row_major ? (uint64_t)f.tiles_x * per_tile : per_tile;  // batch granularity in pixel slots
+    const uint64_t target_samples = (uint64_t)env_int("RTC_BATCH_SAMPLES", 2 << 20, 1024, 1 << 28);
+    const uint64_t max_records = (uint64_t)24 << 20;  // records per queue
+    uint64_t batch_samples = std::min(target_samples, std::max<uint64_t>(max_records / worst, 1));
+    uint64_t batch_pixels = std::max<uint64_t>(batch_samples / f.spp / unit, 1) * unit;
+    batch_pixels = std::min(batch_pixels, std::max<uint64_t>((n_slots + unit - 1) / unit, 1) * unit);
     batch_samples = batch_pixels * f.spp;
-    if (batch_samples >= 0xffffffffull) return fail("rtc_render: batch too large");
     const uint64_t q_cap = batch_samples * worst;
-    if (int rc = ensure_buffers(s, q_cap, batch_samples, n_out)) return rc;
-    Buffers& b = s->buf;
+    if (q_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
+    const uint64_t n_batches = std::max<uint64_t>((n_slots + batch_pixels - 1) / batch_pixels, 1);
+    const int n_pipes = (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 3, 1, MAX_PIPES), n_batches);
+    const bool hit2 = (s->feat & rtcdev::FEAT_TRANSPARENT) != 0;
+    for (int p = 0; p < n_pipes; ++p)
+        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, q_cap * (uint64_t)std::max(L, 1), batch_samples, hit2)) return rc;
+    if (n_out > ctx.out_pixels) {
+        cudaFree(ctx.out); ctx.out = nullptr; ctx.out_pixels = 0;
+        CU(cudaMalloc((void**)&ctx.out, std::max<uint64_t>(n_out, 1) * 3 * sizeof(double)));
+        ctx.out_pixels = n_out;
+    }
+    if (n_batches > ctx.counter_batches) {
+        cudaFree(ctx.counters); ctx.counters = nullptr;
+        cudaFreeHost(ctx.counters_host); ctx.counters_host = nullptr;
+        ctx.counter_batches = 0;
+        const uint64_t nb = std::max<uint64_t>(n_batches, 64);
+        CU(cudaMalloc((void**)&ctx.counters, nb * COUNTERS_PER_BATCH * sizeof(unsigned long long)));
+        CU(cudaHostAlloc((void**)&ctx.counters_host, nb * COUNTERS_PER_BATCH * sizeof(unsigned long long) + 64, cudaHostAllocDefault));
+        ctx.counter_batches = nb;
+    }
 
-    cudaStream_t st = s->stream;
-    CU(cudaMemsetAsync(b.counters, 0, 32 * sizeof(unsigned long long), st));
-    CU(cudaMemsetAsync(b.overflow, 0, sizeof(int), st));
-    CU(cudaEventRecord(s->ev[0], st));
-    const int grid = s->sm_count * 8;
+    cudaStream_t st0 = ctx.pipe[0].stream;
+    const size_t counter_bytes = n_batches * COUNTERS_PER_BATCH * sizeof(unsigned long long);
+    CU(cudaMemsetAsync(ctx.counters, 0, counter_bytes, st0));
+    CU(cudaMemsetAsync(ctx.overflow, 0, sizeof(int), st0));
+    CU(cudaEventRecord(ctx.ev[0], st0));
+    for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
+    const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 8, 1, 32);
     uint64_t launches = 0;
-    for (uint64_t first = 0; first < n_slots; first += batch_pixels) {
-        const uint64_t npix = std::min(batch_pixels, n_slots - first);
-        CU(cudaMemsetAsync(b.accum, 0, npix * f.spp * 3 * sizeof(double), st));
-        CU(cudaMemsetAsync(b.counters, 0, 16 * sizeof(unsigned long long), st));
+    for (uint64_t b = 0; b < n_batches; ++b) {
+        Pipe& p = ctx.pipe[b % (uint64_t)n_pipes];
+        cudaStream_t st = p.stream;
+        const uint64_t first = b * batch_pixels;
+        const uint64_t npix = std::min(batch_pixels, n_slots > first ? n_slots - first : 0);
+        if (!npix) break;
+        unsigned long long* cnt = ctx.counters + b * COUNTERS_PER_BATCH;
+        CU(cudaMemsetAsync(p.accum, 0, npix * f.spp * 3 * sizeof(double), st));
         for (int level = 0; level <= o.fuel; ++level) {
             rtcdev::LevelParams lv{};
             const int in = level & 1, outq = in ^ 1;
-            lv.in_q0 = b.q[in][0]; lv.in_q1 = b.q[in][1]; lv.in_q2 = b.q[in][2]; lv.in_q3 = b.q[in][3];
-            lv.out_q0 = b.q[outq][0]; lv.out_q1 = b.q[outq][1]; lv.out_q2 = b.q[outq][2]; lv.out_q3 = b.q[outq][3];
-            lv.in_count = b.counters + level;
-            lv.out_count = b.counters + level + 1;
-            lv.in_capacity = b.q_capacity;
-            lv.out_capacity = b.q_capacity;
+            lv.in_q0 = p.q[in][0]; lv.in_q1 = p.q[in][1]; lv.in_q2 = p.q[in][2]; lv.in_q3 = p.q[in][3];
+            lv.out_q0 = p.q[outq][0]; lv.out_q1 = p.q[outq][1]; lv.out_q2 = p.q[outq][2]; lv.out_q3 = p.q[outq][3];
+            lv.in_count = cnt + level;
+            lv.out_count = cnt + level + 1;
+            lv.in_capacity = p.q_capacity;
+            lv.out_capacity = p.q_capacity;
             lv.first_sample = first * f.spp;
             lv.n_primary = npix * f.spp;
-            lv.accum = b.accum;
-            lv.stats = b.counters + 16;
-            lv.overflow = b.overflow;
-            rtcdev::launch_level(s->feat, level == 0, grid, st, s->dev, f, lv);
-            launches++;
+            lv.hit_ray = p.hit_ray;
+            lv.hit0 = p.hit[0]; lv.hit1 = p.hit[1]; lv.hit2 = p.hit[2];
+            lv.hit_count = cnt + 16 + level;
+            lv.shadow = p.shadow;
+            lv.accum = p.accum;
+            lv.stats = cnt + 32;
+            lv.overflow = ctx.overflow;
+            int grid = grid_full;
+            if (level == 0) grid = (int)std::min<uint64_t>((uint64_t)grid_full, (lv.n_primary + RTC_BLOCK - 1) / RTC_BLOCK);
+            rtcdev::launch_trace(s->feat, level == 0, grid, st, s->dev, f, lv);
+            rtcdev::launch_shadow(s->feat, level == 0, grid_full, st, s->dev, f, lv);
+            rtcdev::launch_shade(s->feat, level == 0, grid, st, s->dev, f, lv);
+            launches += L > 0 ? 3 : 2;
         }
-        rtcdev::launch_resolve(st, f, b.accum, first, npix, b.out, row_major ? 1 : 0);
+        rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
         launches++;
+        if (host_out) {  // this batch's pixels are final: copy them out while the other pipelines keep tracing
+            uint64_t off_px, len_px;
+            if (row_major) {
+                const uint64_t row0 = first / unit * (uint64_t)o.tile_h;
+                const uint64_t row1 = std::min<uint64_t>((first + npix) / unit * (uint64_t)o.tile_h, (uint64_t)wh);
+                off_px = row0 * (uint64_t)ww;
+                len_px = (row1 - row0) * (uint64_t)ww;
+            } else {
+                off_px = first;
+                len_px = npix;
+            }
+            if (len_px) CU(cudaMemcpyAsync(host_out + 3 * off_px, ctx.out + 3 * off_px, len_px * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        }
     }
-    CU(cudaEventRecord(s->ev[1], st));
     CU(cudaGetLastError());
-    unsigned long long h_counters[32];
-    int h_overflow = 0;
-    CU(cudaMemcpyAsync(h_counters, b.counters, sizeof h_counters, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(&h_overflow, b.overflow, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    for (int p = 1; p < n_pipes; ++p) {
+        CU(cudaEventRecord(ctx.pipe[p].done, ctx.pipe[p].stream));
+        CU(cudaStreamWaitEvent(st0, ctx.pipe[p].done, 0));
+    }
+    CU(cudaEventRecord(ctx.ev[1], st0));
+    int* h_overflow = (int*)(ctx.counters_host + n_batches * COUNTERS_PER_BATCH);
+    CU(cudaMemcpyAsync(ctx.counters_host, ctx.counters, counter_bytes, cudaMemcpyDeviceToHost, st0));
+    CU(cudaMemcpyAsync(h_overflow, ctx.overflow, sizeof(int), cudaMemcpyDeviceToHost, st0));
+    CU(cudaStreamSynchronize(st0));
     float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]));
+    CU(cudaEventElapsedTime(&ms, ctx.ev[0], ctx.ev[1]));
+    const int overflow = *h_overflow;
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
-        const uint64_t pushed_refl = h_counters[18], pushed_refr = h_counters[19];
-        stats->rays_primary = h_counters[16] - std::min<uint64_t>(h_counters[16], pushed_refl + pushed_refr);
-        stats->rays_shadow = h_counters[17];
-        stats->rays_reflected = pushed_refl;
-        stats->rays_refracted = pushed_refr;
-        stats->rays_ref = h_counters[20];
+        // R_ref: the reference re-traces every secondary sub-tree once per light, so a ray at
+        // bounce level k exists L^k times there, and each of its hits issues L shadow queries.
+        double mult = 1.0;
+        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0;
+        double ref = 0.0;
+        for (uint64_t b = 0; b < n_batches; ++b) {
+            const unsigned long long* c = ctx.counters_host + b * COUNTERS_PER_BATCH;
+            primary += c[32]; refl += c[33]; refr += c[34];
+            mult = 1.0;
+            for (int level = 0; level <= o.fuel; ++level) {
+                const uint64_t n_in = level == 0 ? c[32] : std::min<uint64_t>(c[level], q_cap);
+                const uint64_t hits = c[16 + level];
+                shadow += hits * (uint64_t)L;
+                ref += mult * ((double)n_in + (double)hits * L);
+                mult *= (double)L;
+            }
+        }
+        stats->rays_primary = primary;
+        stats->rays_shadow = shadow;
+        stats->rays_reflected = refl;
+        stats->rays_refracted = refr;
+        stats->rays_ref = (uint64_t)ref;
         stats->kernel_launches = launches;
         stats->pixels = n_out;
         stats->ms_kernels = ms;
         stats->ms_trace_shade = ms;
-        stats->overflow = h_overflow;
+        stats->overflow = overflow;
         stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
     }
-    if (h_overflow) return fail(h_overflow == 2 ? "rtc_render: ray queue overflow" : "rtc_render: on-chip crossing list overflow (scene too deep for the device evaluator)");
-    if (out_dev_rgb) *out_dev_rgb = b.out;
+    if (overflow) return fail(overflow == 2 ? "rtc_render: ray queue overflow" : "rtc_render: on-chip crossing list overflow (scene too deep for the device evaluator)");
+    if (out_dev_rgb) *out_dev_rgb = ctx.out;
     if (out_pixels) *out_pixels = n_out;
     return 0;
 }
 
+int rtc_render_device(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o, double** out_dev_rgb, uint64_t* out_pixels, rtc_stats* stats) {
+    return render_impl(s, cam, o, nullptr, out_dev_rgb, out_pixels, stats);
+}
+
 int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o, double* out_rgb, rtc_stats* stats) {
     if (!out_rgb) return fail("rtc_render: null output buffer");
-    const auto t_begin = std::chrono::steady_clock::now();
-    double* dev = nullptr;
-    uint64_t n = 0;
-    rtc_stats local{};
-    if (int rc = rtc_render_device(s, cam, o, &dev, &n, &local)) {
-        if (stats) *stats = local;
-        return rc;
-    }
-    CU(cudaEventRecord(s->ev[2], s->stream));
-    CU(cudaMemcpyAsync(out_rgb, dev, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
-    CU(cudaEventRecord(s->ev[3], s->stream));
-    CU(cudaStreamSynchronize(s->stream));
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, s->ev[2], s->ev[3]));
-    local.ms_d2h = ms;
-    local.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
-    if (stats) *stats = local;
-    return 0;
+    return render_impl(s, cam, o, out_rgb, nullptr, nullptr, stats);
 }
 
 }  // extern "C"

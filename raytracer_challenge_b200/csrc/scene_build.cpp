@@ -488,7 +488,20 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         out.bvh_depth = bld.depth;
         if (out.bvh_depth + 2 > rtcdev::BVH_STACK) return "BVH deeper than the traversal stack";
         out.leaf_items.resize(item_ids.size());
-        for (size_t i = 0; i < item_ids.size(); ++i) out.leaf_items[i] = item_ids[(size_t)bld.order[i]];
+        out.leaf_tri.assign(item_ids.size() * 10, 0.0);
+        for (size_t i = 0; i < item_ids.size(); ++i) {
+            const int32_t id = item_ids[(size_t)bld.order[i]];
+            rtcdev::LeafItem li{id, 0, 0, -1};
+            if (id >= 0) {
+                const rtcdev::Prim& p = out.prims[(size_t)id];
+                li.kind_flags = p.kind_flags;
+                li.xform = p.xform;
+                li.geom = p.geom;
+                if ((p.kind_flags & 0xff) >= RTC_TRIANGLE)
+                    for (int k = 0; k < 10; ++k) out.leaf_tri[i * 10 + (size_t)k] = out.tri_pe[(size_t)p.geom * 10 + (size_t)k];
+            }
+            out.leaf_items[i] = li;
+        }
         for (int k = 0; k < 3; ++k) { out.root_lo[k] = root.lo[k] - pad; out.root_hi[k] = root.hi[k] + pad; }
     }
     if (out.bvh.empty()) out.bvh.emplace_back();  // keep device pointers non-null

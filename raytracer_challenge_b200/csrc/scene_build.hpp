@@ -23,7 +23,9 @@ struct HostScene {
     std::vector<rtcdev::Light> lights;
     std::vector<rtcdev::Gate> gates;
     std::vector<rtcdev::BvhNode> bvh;
-    std::vector<int32_t> leaf_items, unbounded;
+    std::vector<rtcdev::LeafItem> leaf_items;
+    std::vector<double> leaf_tri;
+    std::vector<int32_t> unbounded;
     std::vector<rtcdev::CsgOp> csg_ops;
     std::vector<rtcdev::CsgRoot> csg_roots;
     int32_t bvh_root = 0;
@@ -34,6 +36,7 @@ struct HostScene {
     // build statistics (reported by tests / DESIGN.md)
     int32_t n_gates_always_pass = 0, n_gates_conservative = 0, n_gates_exact = 0;
     int32_t bvh_depth = 0;
+    int64_t device_bytes = 0;  // size of the uploaded scene arena (set by rtc_scene_create)
 };
 
 // Returns "" on success, otherwise a description of why the scene was rejected.

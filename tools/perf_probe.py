@@ -3,10 +3,12 @@ import sys, os, time, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import raytracer_challenge_b200 as R
 
-cases = sys.argv[1:] or ["teapot:3840x2160", "glass_air_bubble:1920x1080", "benchmark:3840x2160", "hexagon:3840x2160", "csg_noise:1920x1080"]
+DEFAULT = ["teapot:3840x2160", "glass_air_bubble:1920x1080", "benchmark:3840x2160", "hexagon:3840x2160", "csg_noise:1920x1080"]
+cases = sys.argv[1:]
 if "--microbench" in cases:
     cases.remove("--microbench")
     print(json.dumps(R.microbench()))
+cases = cases or DEFAULT
 for c in cases:
     name, res = c.split(":")
     w, h = map(int, res.split("x"))
