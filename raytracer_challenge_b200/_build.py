@@ -18,7 +18,7 @@ OBJ = os.path.join(ROOT, "build", "obj")
 NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # -fmad=false: no multiply-add contraction, so f64 results are bit-identical to the reference's scalar code
-DEVICE_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH
+DEVICE_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH + os.environ.get("RTC_NVCC_EXTRA", "").split()
 HOST_FLAGS = ["-std=c++17", "-O2", "-Xcompiler", "-fPIC,-Wall", "-Wno-deprecated-gpu-targets"] + ARCH
 
 

@@ -126,7 +126,7 @@ __device__ __forceinline__ Surface surface_at(const Scene& sc, const Prim& prim,
 
 // ---- kernel 1: closest hit -> compacted hit list ---------------------------------------------------------------
 template <int FEAT, bool PRIMARY>
-__global__ void __launch_bounds__(RTC_BLOCK) trace_closest(const Scene sc, const FrameParams f, const LevelParams lv) {
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest(const Scene sc, const FrameParams f, const LevelParams lv) {
     const bool brute = (f.flags & 1u) != 0;
     const uint32_t n_in = level_rays<PRIMARY>(lv);
     const unsigned lane = threadIdx.x & 31u;
@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(RTC_BLOCK) trace_closest(const Scene sc, const
 
 // ---- kernel 2: World::is_shadowed for every (hit, light) ------------------------------------------------------
 template <int FEAT, bool PRIMARY, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK) trace_shadow(const Scene sc, const FrameParams f, const LevelParams lv) {
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_shadow(const Scene sc, const FrameParams f, const LevelParams lv) {
     const bool brute = (f.flags & 1u) != 0;
     const uint32_t n_hits = (uint32_t)*lv.hit_count;
     const uint32_t L = (uint32_t)sc.n_lights;
@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(RTC_BLOCK) trace_shadow(const Scene sc, const 
 
 // ---- kernel 3: shading + children -----------------------------------------------------------------------------
 template <bool TRANSPARENT, bool PRIMARY>
-__global__ void __launch_bounds__(RTC_BLOCK) shade(const Scene sc, const FrameParams f, const LevelParams lv) {
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADE_MIN_BLOCKS) shade(const Scene sc, const FrameParams f, const LevelParams lv) {
     __shared__ uint8_t s_perm[512];
     for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
     __syncthreads();

@@ -6,6 +6,13 @@
 #include "device_scene.h"
 
 #define RTC_BLOCK 128
+// resident blocks per SM the compiler must allow for (register cap = 65536 / (128 * blocks))
+#ifndef RTC_TRACE_MIN_BLOCKS
+#define RTC_TRACE_MIN_BLOCKS 5
+#endif
+#ifndef RTC_SHADE_MIN_BLOCKS
+#define RTC_SHADE_MIN_BLOCKS 4
+#endif
 
 namespace rtcdev {
 

@@ -409,7 +409,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     const uint64_t q_cap = batch_samples * worst;
     if (q_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
     const uint64_t n_batches = std::max<uint64_t>((n_slots + batch_pixels - 1) / batch_pixels, 1);
-    const int n_pipes = (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 3, 1, MAX_PIPES), n_batches);
+    const int n_pipes = (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
     const bool hit2 = (s->feat & rtcdev::FEAT_TRANSPARENT) != 0;
     for (int p = 0; p < n_pipes; ++p)
         if (int rc = ensure_pipe(ctx.pipe[p], q_cap, q_cap * (uint64_t)std::max(L, 1), batch_samples, hit2)) return rc;
@@ -434,7 +434,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     CU(cudaMemsetAsync(ctx.overflow, 0, sizeof(int), st0));
     CU(cudaEventRecord(ctx.ev[0], st0));
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
-    const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 8, 1, 32);
+    const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
     uint64_t launches = 0;
     for (uint64_t b = 0; b < n_batches; ++b) {
         Pipe& p = ctx.pipe[b % (uint64_t)n_pipes];
