@@ -107,13 +107,31 @@ int drv_e2e_step(void* h, int device, const rtc_opts* opts, double* out_rgb, rtc
     return rc;
 }
 
+// The single-process multi-GPU form (rtc_render_multi) through the host API: Image::par_render over the first
+// n_devices devices (0 = all).  out_rgb: hsize*vsize*3 doubles.
+int drv_par_render_multi(const char* name, const char* data_dir, int hsize, int vsize, int n_devices, double* out_rgb, rtc_stats* stats, char* err, int errlen) {
+    try {
+        if (data_dir && *data_dir) scenes::data_dir() = data_dir;
+        auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
+        rtc::RenderOptions ro;
+        for (int i = 0; i < n_devices; ++i) ro.devices.push_back(i);
+        rtc::Image img = rtc::Image::par_render(sc.camera, sc.world, ro);
+        for (size_t i = 0; i < img.pixels.size(); ++i) { out_rgb[3 * i] = img.pixels[i].r; out_rgb[3 * i + 1] = img.pixels[i].g; out_rgb[3 * i + 2] = img.pixels[i].b; }
+        if (stats) *stats = img.stats;
+        return 0;
+    } catch (const std::exception& e) {
+        set_err(err, errlen, e.what());
+        return 1;
+    }
+}
+
 // Image::par_render + Image::ppm through the public host API (the path a bin would take): returns the PPM text length.
 int64_t drv_par_render_ppm(const char* name, const char* data_dir, int hsize, int vsize, int device, char* out, int64_t out_cap, char* err, int errlen) {
     try {
         if (data_dir && *data_dir) scenes::data_dir() = data_dir;
         auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
         rtc::RenderOptions ro;
-        ro.device = device;
+        if (device >= 0) ro.devices = {device};  // device < 0: shard over every visible device
         rtc::Image img = rtc::Image::par_render(sc.camera, sc.world, ro);
         const std::string ppm = img.ppm();
         if ((int64_t)ppm.size() <= out_cap) std::memcpy(out, ppm.data(), ppm.size());

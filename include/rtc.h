@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define RTC_ABI_VERSION 1
+#define RTC_ABI_VERSION 2
 
 /* Geometry kinds: src/shape.rs:465-498 */
 enum rtc_prim_kind {
@@ -128,6 +128,10 @@ typedef struct rtc_camera {
 } rtc_camera;
 
 #define RTC_FLAG_BRUTE_FORCE 1u /* test every primitive for every ray (no BVH culling); validation only */
+#define RTC_FLAG_SCATTER_ROWS 4u /* sharded render with full-width tiles (tile_w == window width): out_rgb is the FULL row-major
+                                  * window buffer and the shard's pixel rows are written at their row-major positions (the other
+                                  * rows are left untouched), so N shards fill one shared host image with N parallel copies */
+#define RTC_FLAG_PROFILE 2u     /* one pipeline, CUDA events around every launch: fills rtc_stats.ms_trace/ms_shadow/ms_shade */
 
 typedef struct rtc_opts {
     int32_t fuel;          /* src/config.rs:2 (FUEL = 5) */
@@ -150,6 +154,13 @@ typedef struct rtc_stats {
     double ms_d2h;           /* reserved (0): rtc_render copies each finished batch out while later batches are traced */
     int32_t overflow;        /* non-zero: an on-chip list overflowed; result invalid (call fails) */
     int32_t reserved;
+    /* work actually done by the traversal kernels (inputs of the roofline model) */
+    uint64_t surface_hits;    /* rays that hit something = shaded surface points */
+    uint64_t bvh_node_visits; /* each visit = two fp32 slab tests */
+    uint64_t triangle_tests, primitive_tests; /* exact f64 intersections: triangles / every other kind */
+    uint64_t ray_transforms;  /* world -> object ray transforms (src/ray.rs:14-19) actually computed */
+    /* RTC_FLAG_PROFILE only: CUDA-event time per kernel class, launches serialised on one stream */
+    double ms_trace, ms_shadow, ms_shade;
 } rtc_stats;
 
 typedef struct rtc_scene rtc_scene;
@@ -168,7 +179,15 @@ void rtc_scene_destroy(rtc_scene* scene);
  * Replaces the body of Image::par_render (src/image.rs:65-81).  0 = ok. */
 int rtc_render(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* out_rgb, rtc_stats* stats);
 
-/* Same, but leaves the result in device memory owned by the library's per-device render context (valid until
+/* One frame on n GPUs of this box from ONE host thread (the form Image::par_render needs): scenes[i] are uploads of
+ * the same scene on n distinct devices; bands of tile_h pixel rows are dealt round-robin to the devices, each device
+ * renders its bands on its own worker thread and copies them straight to their row-major place in out_rgb over its
+ * own PCIe link (RTC_FLAG_SCATTER_ROWS).  No collective is involved: pixels are independent (src/image.rs:66-74).
+ * stats: ray counts summed over devices, ms_kernels = the slowest device. */
+int rtc_render_multi(rtc_scene* const* scenes, int n, const rtc_camera* camera, const rtc_opts* opts, double* out_rgb,
+                     rtc_stats* stats);
+
+/* Same as rtc_render, but leaves the result in device memory owned by the library's per-device render context (valid until
  * the next render on that device or rtc_release_device_memory); *out_dev_rgb receives the device pointer (f64
  * triples), *out_pixels the count. */
 int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double** out_dev_rgb,
@@ -205,6 +224,9 @@ void rtc_release_device_memory(int device);
 /* Page-locked host memory for out_rgb (optional: any host buffer works, pinned ones copy at full PCIe rate). */
 void* rtc_alloc_host(uint64_t bytes);
 void rtc_free_host(void* p);
+/* Page-locks / unlocks memory the caller already owns (e.g. a shared-memory frame several processes render into). */
+int rtc_host_register(void* p, uint64_t bytes);
+int rtc_host_unregister(void* p);
 
 /* Measured roofline denominators on the current device: TFLOP/s (two flops per multiply-add pair) or GB/s. */
 enum rtc_microbench_kind { RTC_MB_FP64_FMA = 0, RTC_MB_FP64_MUL_ADD = 1, RTC_MB_FP32_FMA = 2, RTC_MB_FP32_MUL_ADD = 3, RTC_MB_L2_READ = 4 };

@@ -18,6 +18,10 @@ from .binding import (  # noqa: F401
     pinned_array,
     free_pinned,
     microbench,
+    par_render_multi,
+    FLAG_BRUTE_FORCE,
+    FLAG_PROFILE,
+    FLAG_SCATTER_ROWS,
     SCENES,
     DATA_DIR,
 )

@@ -37,7 +37,10 @@ class Stats(C.Structure):  # rtc_stats
     _fields_ = [("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_reflected", C.c_uint64),
                 ("rays_refracted", C.c_uint64), ("rays_ref", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("pixels", C.c_uint64), ("ms_total", C.c_double), ("ms_kernels", C.c_double),
-                ("ms_trace_shade", C.c_double), ("ms_d2h", C.c_double), ("overflow", C.c_int32), ("reserved", C.c_int32)]
+                ("ms_trace_shade", C.c_double), ("ms_d2h", C.c_double), ("overflow", C.c_int32), ("reserved", C.c_int32),
+                ("surface_hits", C.c_uint64), ("bvh_node_visits", C.c_uint64), ("triangle_tests", C.c_uint64),
+                ("primitive_tests", C.c_uint64), ("ray_transforms", C.c_uint64),
+                ("ms_trace", C.c_double), ("ms_shadow", C.c_double), ("ms_shade", C.c_double)]
 
     @property
     def rays(self):
@@ -48,7 +51,21 @@ class Stats(C.Structure):  # rtc_stats
 
 
 STAT_KEYS = ["prims", "bvh_nodes", "bvh_depth", "unbounded", "gates_exact", "gates_conservative", "gates_always_pass",
-             "csg_roots", "xforms", "features", "bvh_items"]
+             "csg_roots", "xforms", "features", "bvh_items", "device_bytes"]
+
+FLAG_BRUTE_FORCE, FLAG_PROFILE, FLAG_SCATTER_ROWS = 1, 2, 4
+
+
+def par_render_multi(name, hsize, vsize, n_devices=0, data_dir=None):
+    """Image::par_render of the host builder API over n_devices GPUs in ONE process (rtc_render_multi).  Returns (image, Stats)."""
+    lib = load_driver()
+    out = np.empty((vsize, hsize, 3), dtype=np.float64)
+    stats = Stats()
+    err = C.create_string_buffer(1024)
+    rc = lib.drv_par_render_multi(name.encode(), (data_dir or DATA_DIR).encode(), hsize, vsize, n_devices, out.ctypes.data, C.byref(stats), err, 1024)
+    if rc != 0:
+        raise RtcError(err.value.decode())
+    return out, stats
 
 
 def lib_paths():
@@ -83,6 +100,8 @@ def load_rtc():
         lib.rtc_alloc_host.restype = C.c_void_p
         lib.rtc_alloc_host.argtypes = [C.c_uint64]
         lib.rtc_free_host.argtypes = [C.c_void_p]
+        lib.rtc_host_register.argtypes = [C.c_void_p, C.c_uint64]
+        lib.rtc_host_unregister.argtypes = [C.c_void_p]
         lib.rtc_microbench.argtypes = [C.c_int, C.c_void_p]
         _rtc = lib
     return _rtc
@@ -130,6 +149,8 @@ def load_driver():
         lib.drv_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
         lib.drv_par_render_ppm.restype = C.c_int64
         lib.drv_par_render_ppm.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
+        lib.drv_par_render_multi.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        lib.drv_e2e_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
         lib.drv_scene.restype = C.c_void_p
         lib.drv_scene.argtypes = [C.c_void_p]
         lib.drv_camera.restype = C.c_void_p

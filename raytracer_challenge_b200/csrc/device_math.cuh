@@ -201,6 +201,11 @@ struct ObjRay {
     int xform;
     Ray r;
 };
+// Work actually done by a thread's queries (feeds the algorithmic FLOP / byte model of the roofline):
+// BVH node visits (two slab tests each), triangle tests, other primitive tests, ray transforms.
+struct Tally {
+    uint32_t nodes, tris, prims, xforms;
+};
 __device__ __forceinline__ void load_xform_inv(const Scene& sc, int xform, double* __restrict__ m) {
     const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv);  // 192-byte records, 16-byte aligned
 #pragma unroll
@@ -210,8 +215,9 @@ __device__ __forceinline__ void load_xform_inv(const Scene& sc, int xform, doubl
         m[2 * k + 1] = v.y;
     }
 }
-__device__ __forceinline__ const Ray& object_ray(const Scene& sc, const Ray& world, int xform, ObjRay& c) {
+__device__ __forceinline__ const Ray& object_ray(const Scene& sc, const Ray& world, int xform, ObjRay& c, Tally& tally) {
     if (xform != c.xform) {
+        tally.xforms++;
         double m[12];
         load_xform_inv(sc, xform, m);
         c.r.o = xf_point(m, world.o);
@@ -244,10 +250,11 @@ __device__ __noinline__ void roots_generic(const Scene& sc, int kind_flags, int 
 // HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6).
 template <int HOT>
 __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int xform, int geom, const double* __restrict__ tri_rec,
-                                           const Ray& world, ObjRay& cache, Roots& out) {
+                                           const Ray& world, ObjRay& cache, Tally& tally, Roots& out) {
     out.n = 0;
-    const Ray& r = object_ray(sc, world, xform, cache);
+    const Ray& r = object_ray(sc, world, xform, cache, tally);
     const int kind = kind_flags & 0xff;
+    if (kind >= 5) tally.tris++; else tally.prims++;
     if ((HOT & 0x60) && kind >= 5) {
         V3 p1, e1, e2;
         load_tri(tri_rec, p1, e1, e2);
@@ -261,8 +268,8 @@ __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int 
     }
 }
 template <int HOT>
-__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, ObjRay& cache, Roots& out) {
-    prim_roots<HOT>(sc, p.kind_flags, p.xform, p.geom, sc.tri_pe + 10 * (size_t)(p.geom < 0 ? 0 : p.geom), world, cache, out);
+__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, ObjRay& cache, Tally& tally, Roots& out) {
+    prim_roots<HOT>(sc, p.kind_flags, p.xform, p.geom, sc.tri_pe + 10 * (size_t)(p.geom < 0 ? 0 : p.geom), world, cache, tally, out);
 }
 
 // src/shape.rs:419-427 + :887-946 — world normal at a world point (not yet flipped towards the eye)

@@ -64,8 +64,9 @@ struct Query {
     const Ray& ray;
     uint32_t passed;
     ObjRay cache;
+    Tally& tally;
     int* overflow;
-    __device__ __forceinline__ Query(const Scene& s, const Ray& r, int* ovf) : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), overflow(ovf) {
+    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf) : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), overflow(ovf) {
         cache.xform = -1;
     }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
@@ -77,13 +78,13 @@ struct Query {
         r.n = 0;
         const Prim p = load_prim(sc, id);
         if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
-        prim_roots<0x02>(sc, p, ray, cache, r);  // planes are the usual always-tested primitive
+        prim_roots<0x02>(sc, p, ray, cache, tally, r);  // planes are the usual always-tested primitive
     }
     // crossings of a BVH leaf item that is a primitive
     __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
         r.n = 0;
         if (!gate_ok(li.id)) return;
-        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, r);  // triangles, spheres
+        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, tally, r);  // triangles, spheres
     }
 };
 
@@ -178,7 +179,7 @@ __device__ __forceinline__ float walk_thi(double tmax, double te) { return __dou
 // Visitor protocol:  bool V::leaf(int slot) -> true stops the walk;  double V::tmax() -> current upper bound on t
 // (re-read only after a leaf was visited: it cannot change in between).
 template <class V>
-__device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v) {
+__device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v, Tally& tally) {
     if (sc.n_bvh_items == 0) return;
     if (brute) {
         for (int i = 0; i < sc.n_bvh_items; ++i)
@@ -193,6 +194,7 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
     float thi = walk_thi(v.tmax(), w.te);
     for (;;) {
         if (link >= 0) {
+            tally.nodes++;
             const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
             const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
             float n0, n1;
@@ -225,7 +227,7 @@ struct ClosestVisitor {
     Query<FEAT> q;
     Hit best;
     double limit;   // exclusive upper bound on t (shadow queries on scenes with non-casting shapes), else +inf
-    __device__ __forceinline__ ClosestVisitor(const Scene& sc, const Ray& ray, double lim, int* ovf) : q(sc, ray, ovf), limit(lim) {
+    __device__ __forceinline__ ClosestVisitor(const Scene& sc, const Ray& ray, double lim, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), limit(lim) {
         best.t = 0.0; best.prim = -1; best.u = 0.0; best.v = 0.0;
     }
     __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : limit; }
@@ -247,7 +249,7 @@ struct ClosestVisitor {
                 const Prim p = load_prim(q.sc, list[k].prim);
                 if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
                     Roots r;
-                    prim_roots<0>(q.sc, p, q.ray, q.cache, r);
+                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.tally, r);
                     u = r.u; v = r.v;
                 }
                 offer(list[k].t, list[k].prim, u, v);
@@ -273,10 +275,10 @@ struct ClosestVisitor {
 };
 
 template <int FEAT>
-__device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, int* overflow) {
-    ClosestVisitor<FEAT> v(sc, ray, limit, overflow);
+__device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, Tally& tally, int* overflow) {
+    ClosestVisitor<FEAT> v(sc, ray, limit, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
-    walk_bvh(sc, ray, 0, brute, v);
+    walk_bvh(sc, ray, 0, brute, v, tally);
     return v.best;
 }
 
@@ -286,7 +288,7 @@ struct AnyVisitor {
     Query<FEAT> q;
     double dist;
     bool found;
-    __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, int* ovf) : q(sc, ray, ovf), dist(d), found(false) {}
+    __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), dist(d), found(false) {}
     __device__ __forceinline__ double tmax() const { return dist; }
     __device__ __forceinline__ bool test(const Roots& r) {
         for (int k = 0; k < r.n; ++k)
@@ -320,11 +322,11 @@ struct AnyVisitor {
 // Only instantiated for scenes where every primitive casts shadows: then "nearest t < dist" <=> "any t in
 // [0, dist)" and the walk may stop at the first such crossing.  (Scenes with non-casting shapes use closest_hit.)
 template <int FEAT>
-__device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, int* overflow) {
-    AnyVisitor<FEAT> v(sc, ray, dist, overflow);
+__device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, Tally& tally, int* overflow) {
+    AnyVisitor<FEAT> v(sc, ray, dist, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i)
         if (v.item(__ldg(sc.unbounded + i))) return v.found;
-    walk_bvh(sc, ray, 0, brute, v);
+    walk_bvh(sc, ray, 0, brute, v, tally);
     return v.found;
 }
 
@@ -335,7 +337,7 @@ struct CollectVisitor {
     double thit;
     Cross* out;
     int n;
-    __device__ __forceinline__ CollectVisitor(const Scene& sc, const Ray& ray, double th, Cross* o, int* ovf) : q(sc, ray, ovf), thit(th), out(o), n(0) {}
+    __device__ __forceinline__ CollectVisitor(const Scene& sc, const Ray& ray, double th, Cross* o, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), thit(th), out(o), n(0) {}
     __device__ __forceinline__ double tmax() const { return thit; }
     __device__ __forceinline__ bool push(double t, int prim) {
         if (!(t <= thit)) return false;
@@ -372,11 +374,11 @@ struct CollectVisitor {
 };
 
 template <int FEAT>
-__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, double hit_t, int hit_prim, bool brute, double& n1, double& n2, int* overflow) {
+__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, double hit_t, int hit_prim, bool brute, double& n1, double& n2, Tally& tally, int* overflow) {
     Cross xs[MAX_CROSSINGS];
-    CollectVisitor<FEAT> v(sc, ray, hit_t, xs, overflow);
+    CollectVisitor<FEAT> v(sc, ray, hit_t, xs, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
-    walk_bvh(sc, ray, 1, brute, v);
+    walk_bvh(sc, ray, 1, brute, v, tally);
     const int n = v.n;
     for (int i = 1; i < n; ++i) {  // order of the reference's sorted list: by t, ties in depth-first primitive order
         const Cross c = xs[i];

@@ -110,6 +110,17 @@ __device__ __forceinline__ uint32_t level_rays(const LevelParams& lv) {
     return (uint32_t)(n < lv.in_capacity ? n : lv.in_capacity);
 }
 
+// Adds a thread's tally to the batch counters: warp reduce, one atomic per counter per warp.
+__device__ __forceinline__ void flush_tally(const Tally& t, unsigned long long* stats, unsigned lane) {
+    uint32_t v[4] = {t.nodes, t.tris, t.prims, t.xforms};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        unsigned long long x = v[k];
+        for (int off = 16; off; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+        if (lane == 0 && x) atomicAdd(stats + 3 + k, x);
+    }
+}
+
 // Geometric half of Intersection::prepare_state (src/intersection.rs:50-68)
 struct Surface {
     V3 point, eye, normal, over_point;
@@ -134,6 +145,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
     // every lane of a warp runs the same number of iterations so the warp-aggregated push stays convergent
     const uint32_t n_round = (n_in + 31u) & ~31u;
     uint32_t c_active = 0;
+    Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
         Ray ray;
         double w;
@@ -145,11 +157,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
         double n1 = 1.0, n2 = 1.0;
         if (active) {
             c_active++;
-            hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, lv.overflow);
+            hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
             if ((FEAT & FEAT_TRANSPARENT) && hit.prim >= 0) {
                 const int material = __ldg(&sc.prims[hit.prim].material);
                 if (sc.materials[material].transparency != 0.0)
-                    refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, lv.overflow);
+                    refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, tally, lv.overflow);
             }
         }
         const bool is_hit = active && hit.prim >= 0;
@@ -167,6 +179,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
             }
         }
     }
+    flush_tally(tally, lv.stats, lane);
     if (PRIMARY) {
         for (int off = 16; off; off >>= 1) c_active += __shfl_down_sync(0xffffffffu, c_active, off);
         if (lane == 0 && c_active) atomicAdd(lv.stats + 0, (unsigned long long)c_active);
@@ -181,6 +194,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_shadow(
     const uint32_t L = (uint32_t)sc.n_lights;
     const uint32_t total = n_hits * L;  // < 2^32: checked by the host (queue capacity * lights)
     const uint32_t stride = gridDim.x * blockDim.x;
+    Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         const uint32_t li = i / n_hits;
         const uint32_t h = i - li * n_hits;
@@ -201,13 +215,14 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_shadow(
         sray.d = normalize(to_light);
         bool shadowed;
         if (ANYHIT) {
-            shadowed = any_hit<FEAT>(sc, sray, distance, brute, lv.overflow);
+            shadowed = any_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
         } else {  // some shape does not cast shadows: the nearest crossing decides (src/world.rs:43-47)
-            const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, lv.overflow);
+            const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
             shadowed = sh.prim >= 0 && (__ldg(&sc.prims[sh.prim].kind_flags) & 0x100) != 0;
         }
         lv.shadow[i] = shadowed ? 1 : 0;
     }
+    flush_tally(tally, lv.stats, threadIdx.x & 31u);
 }
 
 // ---- kernel 3: shading + children -----------------------------------------------------------------------------

@@ -10,6 +10,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rtc.h"
@@ -76,7 +77,7 @@ struct DeviceCtx {
     unsigned long long* counters_host = nullptr;  // pinned mirror
     uint64_t counter_batches = 0;
     int* overflow = nullptr;
-    bool perm_uploaded = false;
+    std::vector<cudaEvent_t> prof_events;  // RTC_FLAG_PROFILE: one event per launch boundary
 };
 DeviceCtx g_ctx[MAX_DEVICES];
 
@@ -152,6 +153,16 @@ void* rtc_alloc_host(uint64_t bytes) {
 }
 void rtc_free_host(void* p) {
     if (p) cudaFreeHost(p);
+}
+int rtc_host_register(void* p, uint64_t bytes) {
+    if (!p || !bytes) return fail("rtc_host_register: null argument");
+    CU(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return 0;
+}
+int rtc_host_unregister(void* p) {
+    if (!p) return fail("rtc_host_unregister: null argument");
+    CU(cudaHostUnregister(p));
+    return 0;
 }
 
 void rtc_quantize(const double* rgb, uint8_t* out, uint64_t n) {
@@ -390,6 +401,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     if (all_slots * (uint64_t)f.spp >= 0x7fffffffull) return fail("rtc_render: window too large (pixel slots x samples must stay below 2^31)");
     const uint64_t n_slots = rtc_shard_pixels(ww, wh, o.tile_w, o.tile_h, o.shard_index, o.shard_count, nullptr);  // incl. tile padding
     const bool row_major = o.shard_count == 1;
+    const bool scatter_rows = !row_major && (o.flags & RTC_FLAG_SCATTER_ROWS) != 0;
+    if (scatter_rows && o.tile_w != ww) return fail("rtc_render: RTC_FLAG_SCATTER_ROWS needs full-width tiles (tile_w == window width)");
     const uint64_t n_out = row_major ? (uint64_t)ww * wh : n_slots;
     const int L = s->dev.n_lights;
 
@@ -409,7 +422,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     const uint64_t q_cap = batch_samples * worst;
     if (q_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
     const uint64_t n_batches = std::max<uint64_t>((n_slots + batch_pixels - 1) / batch_pixels, 1);
-    const int n_pipes = (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
+    const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
+    const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
     const bool hit2 = (s->feat & rtcdev::FEAT_TRANSPARENT) != 0;
     for (int p = 0; p < n_pipes; ++p)
         if (int rc = ensure_pipe(ctx.pipe[p], q_cap, q_cap * (uint64_t)std::max(L, 1), batch_samples, hit2)) return rc;
@@ -436,6 +450,18 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
     uint64_t launches = 0;
+    size_t n_prof = 0;  // profile mode: event k is recorded after launch k-1 (classes cycle trace, shadow, shade)
+    auto prof_mark = [&](cudaStream_t st) -> int {
+        if (!profile) return 0;
+        if (n_prof == ctx.prof_events.size()) {
+            cudaEvent_t e;
+            CU(cudaEventCreate(&e));
+            ctx.prof_events.push_back(e);
+        }
+        CU(cudaEventRecord(ctx.prof_events[n_prof++], st));
+        return 0;
+    };
+    std::vector<int> prof_class;  // class of the interval that ENDS at event k (0 trace, 1 shadow, 2 shade, -1 other)
     for (uint64_t b = 0; b < n_batches; ++b) {
         Pipe& p = ctx.pipe[b % (uint64_t)n_pipes];
         cudaStream_t st = p.stream;
@@ -464,9 +490,13 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
             lv.overflow = ctx.overflow;
             int grid = grid_full;
             if (level == 0) grid = (int)std::min<uint64_t>((uint64_t)grid_full, (lv.n_primary + RTC_BLOCK - 1) / RTC_BLOCK);
+            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(-1); }
             rtcdev::launch_trace(s->feat, level == 0, grid, st, s->dev, f, lv);
+            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
             rtcdev::launch_shadow(s->feat, level == 0, grid_full, st, s->dev, f, lv);
+            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
             rtcdev::launch_shade(s->feat, level == 0, grid, st, s->dev, f, lv);
+            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
             launches += L > 0 ? 3 : 2;
         }
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
@@ -478,6 +508,25 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
                 const uint64_t row1 = std::min<uint64_t>((first + npix) / unit * (uint64_t)o.tile_h, (uint64_t)wh);
                 off_px = row0 * (uint64_t)ww;
                 len_px = (row1 - row0) * (uint64_t)ww;
+            } else if (scatter_rows) {
+                // tiles are full-width rows of tile_h pixel rows: owned tile row k of this shard is global tile row
+                // shard_index + k * shard_count, i.e. one strided 2-D copy puts the batch where it belongs in the frame
+                const uint64_t k0 = first / per_tile, k1 = (first + npix) / per_tile;  // owned tile rows [k0, k1)
+                const uint64_t row_bytes = (uint64_t)ww * 3 * sizeof(double);
+                auto global_y = [&](uint64_t k) { return ((uint64_t)o.shard_index + k * (uint64_t)o.shard_count) * (uint64_t)o.tile_h; };
+                // only the last tile row of the frame can hold fewer than tile_h pixel rows
+                const bool partial_last = k1 > k0 && global_y(k1 - 1) + (uint64_t)o.tile_h > (uint64_t)wh;
+                const uint64_t n_full = (k1 - k0) - (partial_last ? 1 : 0);
+                if (n_full)
+                    CU(cudaMemcpy2DAsync(host_out + 3 * global_y(k0) * (uint64_t)ww, (uint64_t)o.shard_count * (uint64_t)o.tile_h * row_bytes,
+                                         ctx.out + 3 * k0 * per_tile, per_tile * 3 * sizeof(double), (uint64_t)o.tile_h * row_bytes, n_full,
+                                         cudaMemcpyDeviceToHost, st));
+                if (partial_last) {
+                    const uint64_t y0 = global_y(k1 - 1);
+                    CU(cudaMemcpyAsync(host_out + 3 * y0 * (uint64_t)ww, ctx.out + 3 * (k1 - 1) * per_tile, ((uint64_t)wh - y0) * row_bytes,
+                                       cudaMemcpyDeviceToHost, st));
+                }
+                continue;
             } else {
                 off_px = first;
                 len_px = npix;
@@ -503,16 +552,18 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         // R_ref: the reference re-traces every secondary sub-tree once per light, so a ray at
         // bounce level k exists L^k times there, and each of its hits issues L shadow queries.
         double mult = 1.0;
-        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0;
+        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0, hits_all = 0, tally[4] = {0, 0, 0, 0};
         double ref = 0.0;
         for (uint64_t b = 0; b < n_batches; ++b) {
             const unsigned long long* c = ctx.counters_host + b * COUNTERS_PER_BATCH;
             primary += c[32]; refl += c[33]; refr += c[34];
+            for (int k = 0; k < 4; ++k) tally[k] += c[35 + k];
             mult = 1.0;
             for (int level = 0; level <= o.fuel; ++level) {
                 const uint64_t n_in = level == 0 ? c[32] : std::min<uint64_t>(c[level], q_cap);
                 const uint64_t hits = c[16 + level];
                 shadow += hits * (uint64_t)L;
+                hits_all += hits;
                 ref += mult * ((double)n_in + (double)hits * L);
                 mult *= (double)L;
             }
@@ -527,6 +578,16 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         stats->ms_kernels = ms;
         stats->ms_trace_shade = ms;
         stats->overflow = overflow;
+        stats->surface_hits = hits_all;
+        stats->bvh_node_visits = tally[0];
+        stats->triangle_tests = tally[1];
+        stats->primitive_tests = tally[2];
+        stats->ray_transforms = tally[3];
+        for (size_t k = 1; k < n_prof; ++k) {
+            float t = 0.f;
+            if (prof_class[k] < 0 || cudaEventElapsedTime(&t, ctx.prof_events[k - 1], ctx.prof_events[k]) != cudaSuccess) continue;
+            (prof_class[k] == 0 ? stats->ms_trace : prof_class[k] == 1 ? stats->ms_shadow : stats->ms_shade) += t;
+        }
         stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
     }
     if (overflow) return fail(overflow == 2 ? "rtc_render: ray queue overflow" : "rtc_render: on-chip crossing list overflow (scene too deep for the device evaluator)");
@@ -542,6 +603,57 @@ int rtc_render_device(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o, do
 int rtc_render(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o, double* out_rgb, rtc_stats* stats) {
     if (!out_rgb) return fail("rtc_render: null output buffer");
     return render_impl(s, cam, o, out_rgb, nullptr, nullptr, stats);
+}
+
+int rtc_render_multi(rtc_scene* const* scenes, int n, const rtc_camera* cam, const rtc_opts* o_in, double* out_rgb, rtc_stats* stats) {
+    if (!scenes || n <= 0 || !cam || !out_rgb) return fail("rtc_render_multi: null argument");
+    for (int i = 0; i < n; ++i) {
+        if (!scenes[i]) return fail("rtc_render_multi: null scene");
+        for (int j = 0; j < i; ++j)
+            if (scenes[j]->device == scenes[i]->device) return fail("rtc_render_multi: two scenes live on the same device");
+    }
+    if (n == 1) return rtc_render(scenes[0], cam, o_in, out_rgb, stats);
+    rtc_opts base{};
+    if (o_in) base = *o_in;
+    else base.fuel = 5;
+    if (base.shard_count > 1) return fail("rtc_render_multi: the call shards the frame itself; pass shard_count <= 1");
+    const bool whole = base.win_w <= 0 || base.win_h <= 0;
+    base.tile_w = whole ? cam->hsize : base.win_w;  // full-width tiles: a shard owns every n-th band of tile_h pixel rows
+    if (base.tile_h <= 0) base.tile_h = 4;
+    base.shard_count = n;
+    base.flags |= RTC_FLAG_SCATTER_ROWS;
+    const auto t_begin = std::chrono::steady_clock::now();
+    std::vector<rtc_stats> st((size_t)n);
+    std::vector<std::string> errs((size_t)n);
+    std::vector<int> rcs((size_t)n, 0);
+    std::vector<std::thread> threads;
+    for (int i = 0; i < n; ++i)
+        threads.emplace_back([&, i] {
+            rtc_opts o = base;
+            o.shard_index = i;
+            rcs[(size_t)i] = render_impl(scenes[i], cam, &o, out_rgb, nullptr, nullptr, &st[(size_t)i]);
+            if (rcs[(size_t)i]) errs[(size_t)i] = g_error;  // g_error is thread-local
+        });
+    for (auto& t : threads) t.join();
+    for (int i = 0; i < n; ++i)
+        if (rcs[(size_t)i]) return fail("rtc_render_multi: device " + std::to_string(scenes[i]->device) + ": " + errs[(size_t)i]);
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        for (const rtc_stats& a : st) {
+            stats->rays_primary += a.rays_primary; stats->rays_shadow += a.rays_shadow;
+            stats->rays_reflected += a.rays_reflected; stats->rays_refracted += a.rays_refracted;
+            stats->rays_ref += a.rays_ref; stats->kernel_launches += a.kernel_launches;
+            stats->surface_hits += a.surface_hits; stats->bvh_node_visits += a.bvh_node_visits;
+            stats->triangle_tests += a.triangle_tests; stats->primitive_tests += a.primitive_tests;
+            stats->ray_transforms += a.ray_transforms;
+            stats->ms_kernels = std::max(stats->ms_kernels, a.ms_kernels);  // devices run concurrently: the slowest one counts
+            stats->ms_trace_shade = std::max(stats->ms_trace_shade, a.ms_trace_shade);
+        }
+        const bool whole_w = o_in == nullptr || o_in->win_w <= 0 || o_in->win_h <= 0;
+        stats->pixels = whole_w ? (uint64_t)cam->hsize * cam->vsize : (uint64_t)o_in->win_w * o_in->win_h;
+        stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+    }
+    return 0;
 }
 
 }  // extern "C"

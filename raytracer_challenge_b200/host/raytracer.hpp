@@ -658,8 +658,8 @@ class FlatScene {
 
 // ---- Image (src/image.rs) -----------------------------------------------------------------
 struct RenderOptions {
-    int device = 0;      // CUDA device ordinal
-    rtc_opts opts{};     // fuel / supersampling / shard / window
+    std::vector<int> devices;  // CUDA device ordinals to shard the frame over; empty = every visible device
+    rtc_opts opts{};           // fuel / supersampling / window (sharding is chosen by par_render itself)
     RenderOptions() { opts.fuel = FUEL; opts.spp_x = 1; opts.spp_y = 1; opts.shard_count = 1; }
 };
 
@@ -669,29 +669,48 @@ class Image {
     std::vector<Color> pixels;
     rtc_stats stats{};
 
-    // Image::par_render(camera, world) (src/image.rs:65-81): flatten -> upload -> CUDA wavefront -> download.
-    // Infallible in the reference; here every failure (no device, CUDA error, overflow) throws.
+    // Image::par_render(camera, world) (src/image.rs:65-81): flatten -> upload to every device -> CUDA wavefront on
+    // each device's share of the rows -> rows land in one host image.  Infallible in the reference; here every
+    // failure (no device, CUDA error, overflow) throws.
     static Image par_render(const Camera& camera, const World& world, const RenderOptions& ro = RenderOptions{}) {
         FlatScene flat(world);
         const rtc_scene_desc d = flat.desc();
-        rtc_scene* scene = nullptr;
-        if (rtc_scene_create(&d, ro.device, &scene) != 0) throw std::runtime_error(std::string("rtc_scene_create: ") + rtc_last_error());
+        std::vector<int> devices = ro.devices;
+        if (devices.empty()) {
+            const int n = rtc_device_count();
+            if (n <= 0) throw std::runtime_error(std::string("Image::par_render: no CUDA device: ") + rtc_last_error());
+            for (int i = 0; i < n; ++i) devices.push_back(i);
+        }
+        std::vector<rtc_scene*> scenes;
+        auto release = [&] { for (rtc_scene* sc : scenes) rtc_scene_destroy(sc); };
+        for (int dev : devices) {
+            rtc_scene* sc = nullptr;
+            if (rtc_scene_create(&d, dev, &sc) != 0) {
+                const std::string err = rtc_last_error();
+                release();
+                throw std::runtime_error("rtc_scene_create: " + err);
+            }
+            scenes.push_back(sc);
+        }
         const rtc_camera cam = camera.to_c();
         Image img;
         const bool windowed = ro.opts.win_w > 0 && ro.opts.win_h > 0;
         img.hsize = windowed ? (size_t)ro.opts.win_w : camera.hsize;
         img.vsize = windowed ? (size_t)ro.opts.win_h : camera.vsize;
-        const uint64_t n = ro.opts.shard_count <= 1
-                               ? (uint64_t)img.hsize * img.vsize
-                               : rtc_shard_pixels((int32_t)img.hsize, (int32_t)img.vsize, ro.opts.tile_w, ro.opts.tile_h,
-                                                  ro.opts.shard_index, ro.opts.shard_count, nullptr);
-        std::vector<double> buf((size_t)n * 3);
-        const int rc = rtc_render(scene, &cam, &ro.opts, buf.data(), &img.stats);
+        const size_t n = img.hsize * img.vsize;
+        // page-locked staging buffer: the device -> host copies run at full PCIe rate and overlap the kernels
+        double* buf = (double*)rtc_alloc_host((uint64_t)n * 3 * sizeof(double));
+        if (!buf) { release(); throw std::runtime_error(std::string("rtc_alloc_host: ") + rtc_last_error()); }
+        rtc_opts o = ro.opts;
+        o.shard_index = 0;
+        o.shard_count = 1;
+        const int rc = rtc_render_multi(scenes.data(), (int)scenes.size(), &cam, &o, buf, &img.stats);
         const std::string err = rc ? rtc_last_error() : "";
-        rtc_scene_destroy(scene);
-        if (rc != 0) throw std::runtime_error("rtc_render: " + err);
-        img.pixels.resize((size_t)n);
-        for (size_t i = 0; i < (size_t)n; ++i) img.pixels[i] = Color{buf[3 * i], buf[3 * i + 1], buf[3 * i + 2]};
+        release();
+        if (rc != 0) { rtc_free_host(buf); throw std::runtime_error("rtc_render: " + err); }
+        img.pixels.resize(n);
+        for (size_t i = 0; i < n; ++i) img.pixels[i] = Color{buf[3 * i], buf[3 * i + 1], buf[3 * i + 2]};
+        rtc_free_host(buf);
         return img;
     }
     Color read(size_t x, size_t y) const { return pixels[y * hsize + x]; }

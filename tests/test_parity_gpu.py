@@ -39,3 +39,172 @@ def test_known_answer_pixel(built):
     with R.Session("default_world", 11, 11, device=0) as s:
         img, _ = s.render()
     assert np.allclose(img[5, 5], [0.38066, 0.47583, 0.28550], atol=1e-5)
+
+
+# ---- the reference's own rendered images (fixtures: tests/golden/make_golden.py) -------------------------------
+import json
+import os
+
+from common import ROOT, oracle_quantize
+
+_GOLDEN = os.path.join(ROOT, "tests", "golden")
+with open(os.path.join(_GOLDEN, "ref_png_crops.json")) as _f:
+    _MANIFEST = json.load(_f)
+
+
+@pytest.mark.parametrize("entry", _MANIFEST, ids=lambda e: e["key"])
+def test_cuda_matches_reference_png_window(built, entry):
+    """The bin's scene at the bin's native resolution through the C ABI vs the reference's own output image."""
+    crops = np.load(os.path.join(_GOLDEN, "ref_png_crops.npz"))
+    want = crops[entry["key"]].astype(np.int32)
+    with R.Session(entry["scene"], entry["hsize"], entry["vsize"], device=0) as s:
+        img, _ = s.render(R.Opts(window=tuple(entry["window"])))
+    d = np.abs(oracle_quantize(img).astype(np.int32) - want).max(axis=-1)
+    assert (d <= 1).mean() >= 0.999 and d.max() <= 2, {"max": int(d.max()), "n_diff": int((d > 0).sum())}
+
+
+# ---- sharding, windows, supersampling, profiling: same pixels whichever way they are produced -------------------
+def same_pixels(name, a, b):
+    """Bit-identical, except for scenes whose materials both reflect and refract: there several path-tree nodes of one
+    pixel sit in the same bounce level and their f64 atomic adds commute only up to the last bit."""
+    if name in ("glass_air_bubble", "csg_noise") or name.startswith("fuzz"):
+        return np.allclose(a, b, rtol=0.0, atol=1e-12, equal_nan=False)
+    return np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("name,w,h,world,tile", [("glass_air_bubble", 61, 37, 3, (0, 0)), ("teapot_low", 64, 36, 2, (64, 4)),
+                                                 ("csg_noise", 50, 30, 4, (50, 4)), ("benchmark", 33, 19, 8, (8, 4))])
+def test_shards_reassemble_to_the_whole_frame(built, name, w, h, world, tile):
+    with R.Session(name, w, h, device=0) as s:
+        whole, _ = s.render(R.Opts())
+        frame = np.full((h * w, 3), np.nan)
+        for r in range(world):
+            part, st = s.render(R.Opts(shard=(r, world), tile=tile))
+            idx = R.shard_pixels(w, h, r, world, tile)
+            real = idx != 0xFFFFFFFF
+            frame[idx[real]] = part[real]
+            assert st.rays_primary == int(real.sum())
+    assert same_pixels(name, frame.reshape(h, w, 3), whole)
+
+
+@pytest.mark.parametrize("name,w,h,world", [("teapot_low", 64, 38, 2), ("glass_air_bubble", 48, 27, 3), ("three_spheres", 40, 10, 8)])
+def test_scatter_rows_fills_one_shared_frame(built, name, w, h, world):
+    """RTC_FLAG_SCATTER_ROWS: every shard writes its bands of rows at their row-major place of ONE host image."""
+    from raytracer_challenge_b200 import sharding
+
+    with R.Session(name, w, h, device=0) as s:
+        whole, _ = s.render(R.Opts())
+        frame = np.full((h, w, 3), np.nan)
+        for r in range(world):
+            s.render(sharding.band_opts(w, r, world), out=frame)
+    assert same_pixels(name, frame, whole)
+
+
+def test_par_render_multi_one_process(built):
+    """Image::par_render of the host builder API (rtc_render_multi underneath) over every visible device."""
+    w, h = 96, 54
+    ref, _, _ = oracle_render("teapot_low", w, h)
+    img, st = R.par_render_multi("teapot_low", w, h, n_devices=0)
+    assert compare_images(img, ref)["ok"]
+    assert st.rays_primary == w * h
+    with R.Session("teapot_low", w, h, device=0) as s:
+        one, _ = s.render(R.Opts())
+    assert np.array_equal(img, one)
+
+
+def test_window_equals_crop(built):
+    with R.Session("glass_air_bubble", 80, 60, device=0) as s:
+        whole, _ = s.render(R.Opts())
+        win, _ = s.render(R.Opts(window=(13, 7, 31, 22)))
+    assert same_pixels("glass_air_bubble", whole[7:29, 13:44], win)
+
+
+@pytest.mark.parametrize("name,spp", [("three_spheres", (2, 2)), ("csg_noise", (4, 4)), ("glass_air_bubble", (3, 2))])
+def test_supersampling_matches_oracle(built, name, spp):
+    w, h = 48, 27
+    ref, counts, _ = oracle_render(name, w, h, spp=spp)
+    with R.Session(name, w, h, device=0) as s:
+        img, st = s.render(R.Opts(spp=spp))
+    rep = compare_images(img, ref)
+    assert rep["ok"] and rep["max_abs_f64"] < 1e-9, rep
+    assert st.rays_primary == w * h * spp[0] * spp[1]
+    assert st.rays_ref == int(counts.sum())
+
+
+@pytest.mark.parametrize("fuel", [0, 1, 3])
+def test_fuel_matches_oracle(built, fuel):
+    ref, counts, _ = oracle_render("glass_air_bubble", 64, 64, fuel=fuel)
+    with R.Session("glass_air_bubble", 64, 64, device=0) as s:
+        img, st = s.render(R.Opts(fuel=fuel))
+    assert compare_images(img, ref)["ok"]
+    assert st.rays_ref == int(counts.sum())
+
+
+def test_profile_flag_and_work_tallies(built):
+    with R.Session("teapot_low", 128, 72, device=0) as s:
+        a, sa = s.render(R.Opts())
+        b, sb = s.render(R.Opts(flags=R.FLAG_PROFILE))
+    assert np.array_equal(a, b)
+    assert sb.ms_trace > 0 and sb.ms_shadow > 0 and sb.ms_shade > 0
+    assert sa.ms_trace == 0
+    for st in (sa, sb):
+        assert st.surface_hits > 0 and st.bvh_node_visits > 0 and st.triangle_tests > 0 and st.ray_transforms > 0
+        assert st.rays_shadow == st.surface_hits * 2  # two lights (src/bin/chapter15_teapot.rs)
+    assert (sa.bvh_node_visits, sa.triangle_tests) == (sb.bvh_node_visits, sb.triangle_tests)
+
+
+def test_repeated_renders_are_identical_and_batches_do_not_matter(built, monkeypatch):
+    with R.Session("teapot_low", 160, 90, device=0) as s:
+        a, _ = s.render(R.Opts())
+        monkeypatch.setenv("RTC_BATCH_SAMPLES", "1024")
+        monkeypatch.setenv("RTC_PIPES", "3")
+        b, st = s.render(R.Opts())
+        assert st.kernel_launches > 19 * 4
+    assert np.array_equal(a, b)
+
+
+def test_ppm_through_the_host_api(built):
+    """Image::par_render + Image::ppm (src/image.rs:93-112): header, <= 5 pixels per text line, rows restart lines."""
+    import ctypes as C
+
+    lib = R.load_driver()
+    w, h = 11, 11
+    cap = 1 << 16
+    buf = C.create_string_buffer(cap)
+    err = C.create_string_buffer(1024)
+    n = lib.drv_par_render_ppm(b"default_world", R.DATA_DIR.encode(), w, h, 0, buf, cap, err, 1024)
+    assert n > 0, err.value
+    text = buf.raw[:n].decode()
+    lines = text.split("\n")
+    assert lines[0] == "P3" and lines[1] == "11 11" and lines[2] == "255" and text.endswith("\n")
+    body = lines[3:-1]
+    assert len(body) == 11 * 3  # 11 pixels per row -> 5 + 5 + 1
+    assert [len(l.split()) for l in body[:3]] == [15, 15, 3]
+    vals = np.array(" ".join(body).split(), dtype=np.int64).reshape(h, w, 3)
+    ref, _, _ = oracle_render("default_world", w, h)
+    assert np.array_equal(vals, oracle_quantize(ref))
+
+
+# ---- full-size properties (BASELINE.json sizes; the brute-force oracle cannot finish these in seconds) -----------
+def test_full_size_teapot_properties(built):
+    """3840x2160 teapot, fuel 5: (a) the frame assembled from 8 band shards equals the unsharded frame bit for bit;
+    (b) a window rendered alone equals the crop; (c) an oracle-checked window inside the full frame; (d) ray counts obey
+    the identities of SURVEY.md §8(d): shadow = hits * L, R_ref >= R_uniq."""
+    from raytracer_challenge_b200 import sharding
+
+    w, h = 3840, 2160
+    with R.Session("teapot", w, h, device=0) as s:
+        whole, st = s.render(R.Opts())
+        frame = np.full((h, w, 3), np.nan)
+        for r in range(8):
+            s.render(sharding.band_opts(w, r, 8), out=frame)
+        assert np.array_equal(frame, whole)
+        win, _ = s.render(R.Opts(window=(1900, 1000, 64, 32)))
+        assert np.array_equal(whole[1000:1032, 1900:1964], win)
+    ref, _, _ = oracle_render("teapot", w, h, window=(1900, 1000, 24, 12))
+    rep = compare_images(whole[1000:1012, 1900:1924], ref)
+    assert rep["ok"] and rep["max_abs_f64"] < 1e-9, rep
+    assert st.rays_primary == w * h
+    assert st.rays_shadow == 2 * st.surface_hits
+    assert st.rays_ref >= st.rays
+    assert np.isfinite(whole).all()
