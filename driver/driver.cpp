@@ -1,6 +1,9 @@
 // Harness glue (not part of the C ABI): builds the named scenes of scenes/scenes.hpp through the product's host
 // builder API (raytracer_challenge_b200/host/raytracer.hpp), flattens them and drives include/rtc.h.
 // Loaded from Python (ctypes) by tests/, bench.py and __graft_entry__.py.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -100,10 +103,18 @@ int drv_e2e_step(void* h, int device, const rtc_opts* opts, double* out_rgb, rtc
     Session* s = (Session*)h;
     const rtc_scene_desc d = s->flat->desc();
     rtc_scene* scene = nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
     if (rtc_scene_create(&d, device, &scene) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }
+    const auto t1 = std::chrono::steady_clock::now();
     const int rc = rtc_render(scene, &s->camera, opts, out_rgb, stats);
     if (rc != 0) set_err(err, errlen, rtc_last_error());
+    const auto t2 = std::chrono::steady_clock::now();
     rtc_scene_destroy(scene);
+    const auto t3 = std::chrono::steady_clock::now();
+    if (std::getenv("RTC_E2E_TRACE")) {
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        std::fprintf(stderr, "e2e step: create %.3f ms, render %.3f ms (kernels %.3f), destroy %.3f ms\n", ms(t0, t1), ms(t1, t2), stats ? stats->ms_kernels : 0.0, ms(t2, t3));
+    }
     return rc;
 }
 

@@ -247,13 +247,33 @@ __device__ __noinline__ void roots_generic(const Scene& sc, int kind_flags, int 
     }
 }
 
+// A plane only reads the y components of the object-space ray (src/shape.rs:622-633), i.e. row 1 of the transform:
+// two dot products instead of the full Ray::transform, with the same expression order as xf_point / xf_dir, so o.y
+// and d.y are bit-identical.  skip_negative: the caller only wants crossings with t >= 0 (closest hit, shadow), so
+// the division is skipped when the signs of o.y and d.y already say t < 0.
+__device__ __forceinline__ void plane_roots(const Scene& sc, int xform, const Ray& world, bool skip_negative, Roots& out) {
+    const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv + 4);
+    const double2 a = __ldg(q), b = __ldg(q + 1);
+    const double oy = a.x * world.o.x + a.y * world.o.y + b.x * world.o.z + b.y;
+    const double dy = a.x * world.d.x + a.y * world.d.y + b.x * world.d.z;
+    if (approx0(dy)) return;
+    if (skip_negative && ((oy > 0.0 && dy > 0.0) || (oy < 0.0 && dy < 0.0))) return;  // -oy / dy < 0
+    out.t[0] = -oy / dy;
+    out.n = 1;
+}
+
 // HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6).
 template <int HOT>
 __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int xform, int geom, const double* __restrict__ tri_rec,
-                                           const Ray& world, ObjRay& cache, Tally& tally, Roots& out) {
+                                           const Ray& world, ObjRay& cache, Tally& tally, bool skip_negative, Roots& out) {
     out.n = 0;
-    const Ray& r = object_ray(sc, world, xform, cache, tally);
     const int kind = kind_flags & 0xff;
+    if ((HOT & 0x02) && kind == 1) {
+        tally.prims++;
+        plane_roots(sc, xform, world, skip_negative, out);
+        return;
+    }
+    const Ray& r = object_ray(sc, world, xform, cache, tally);
     if (kind >= 5) tally.tris++; else tally.prims++;
     if ((HOT & 0x60) && kind >= 5) {
         V3 p1, e1, e2;
@@ -261,15 +281,13 @@ __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int 
         isect_triangle(r, p1, e1, e2, out);
     } else if ((HOT & 0x01) && kind == 0) {
         isect_sphere(r, out);
-    } else if ((HOT & 0x02) && kind == 1) {
-        isect_plane(r, out);
     } else {
         roots_generic(sc, kind_flags, geom, tri_rec, r, out);
     }
 }
 template <int HOT>
-__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, ObjRay& cache, Tally& tally, Roots& out) {
-    prim_roots<HOT>(sc, p.kind_flags, p.xform, p.geom, sc.tri_pe + 10 * (size_t)(p.geom < 0 ? 0 : p.geom), world, cache, tally, out);
+__device__ __forceinline__ void prim_roots(const Scene& sc, const Prim& p, const Ray& world, ObjRay& cache, Tally& tally, bool skip_negative, Roots& out) {
+    prim_roots<HOT>(sc, p.kind_flags, p.xform, p.geom, sc.tri_pe + 10 * (size_t)(p.geom < 0 ? 0 : p.geom), world, cache, tally, skip_negative, out);
 }
 
 // src/shape.rs:419-427 + :887-946 — world normal at a world point (not yet flipped towards the eye)

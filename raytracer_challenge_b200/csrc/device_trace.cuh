@@ -66,7 +66,9 @@ struct Query {
     ObjRay cache;
     Tally& tally;
     int* overflow;
-    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf) : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), overflow(ovf) {
+    bool skip_negative;  // the query only wants crossings with t >= 0 (set by the closest-hit and shadow visitors)
+    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg)
+        : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), overflow(ovf), skip_negative(skip_neg) {
         cache.xform = -1;
     }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
@@ -78,13 +80,13 @@ struct Query {
         r.n = 0;
         const Prim p = load_prim(sc, id);
         if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
-        prim_roots<0x02>(sc, p, ray, cache, tally, r);  // planes are the usual always-tested primitive
+        prim_roots<0x02>(sc, p, ray, cache, tally, skip_negative, r);  // planes are the usual always-tested primitive
     }
     // crossings of a BVH leaf item that is a primitive
     __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
         r.n = 0;
         if (!gate_ok(li.id)) return;
-        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, tally, r);  // triangles, spheres
+        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, tally, skip_negative, r);  // triangles, spheres
     }
 };
 
@@ -227,7 +229,7 @@ struct ClosestVisitor {
     Query<FEAT> q;
     Hit best;
     double limit;   // exclusive upper bound on t (shadow queries on scenes with non-casting shapes), else +inf
-    __device__ __forceinline__ ClosestVisitor(const Scene& sc, const Ray& ray, double lim, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), limit(lim) {
+    __device__ __forceinline__ ClosestVisitor(const Scene& sc, const Ray& ray, double lim, Tally& tl, int* ovf) : q(sc, ray, tl, ovf, !(FEAT & FEAT_CSG)), limit(lim) {
         best.t = 0.0; best.prim = -1; best.u = 0.0; best.v = 0.0;
     }
     __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : limit; }
@@ -249,7 +251,7 @@ struct ClosestVisitor {
                 const Prim p = load_prim(q.sc, list[k].prim);
                 if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
                     Roots r;
-                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.tally, r);
+                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.tally, false, r);
                     u = r.u; v = r.v;
                 }
                 offer(list[k].t, list[k].prim, u, v);
@@ -288,7 +290,7 @@ struct AnyVisitor {
     Query<FEAT> q;
     double dist;
     bool found;
-    __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), dist(d), found(false) {}
+    __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, Tally& tl, int* ovf) : q(sc, ray, tl, ovf, !(FEAT & FEAT_CSG)), dist(d), found(false) {}
     __device__ __forceinline__ double tmax() const { return dist; }
     __device__ __forceinline__ bool test(const Roots& r) {
         for (int k = 0; k < r.n; ++k)
@@ -337,7 +339,7 @@ struct CollectVisitor {
     double thit;
     Cross* out;
     int n;
-    __device__ __forceinline__ CollectVisitor(const Scene& sc, const Ray& ray, double th, Cross* o, Tally& tl, int* ovf) : q(sc, ray, tl, ovf), thit(th), out(o), n(0) {}
+    __device__ __forceinline__ CollectVisitor(const Scene& sc, const Ray& ray, double th, Cross* o, Tally& tl, int* ovf) : q(sc, ray, tl, ovf, false), thit(th), out(o), n(0) {}
     __device__ __forceinline__ double tmax() const { return thit; }
     __device__ __forceinline__ bool push(double t, int prim) {
         if (!(t <= thit)) return false;

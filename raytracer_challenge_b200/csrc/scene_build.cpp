@@ -1,6 +1,8 @@
 #include "scene_build.hpp"
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cmath>
 #include <cstring>
 #include <functional>
@@ -113,11 +115,25 @@ float f32_up(double x) {
 
 // ---- binned-SAH BVH2 over item boxes ------------------------------------------------------
 struct Builder {
-    const std::vector<Box>& boxes;  // per item
-    std::vector<int32_t> order;     // item permutation; leaves reference ranges of it
-    std::vector<BvhNode> nodes;
+    struct Item {  // box + centroid of one BVH item, kept in leaf order (partitioned in place: sequential passes)
+        Box box;
+        double c[3];
+        int32_t index;
+    };
+    std::vector<Item> items;
+    std::vector<BvhNode> nodes;  // build(): slot mid - 1 of the node that splits at `mid` (sparse); compact(): final
     double pad;
-    int depth = 0;
+    std::atomic<int> depth{0};
+    Builder(const std::vector<Box>& boxes, double pad_) : pad(pad_) {
+        items.resize(boxes.size());
+        for (size_t i = 0; i < boxes.size(); ++i) {
+            Item& it = items[i];
+            it.box = boxes[i];
+            for (int k = 0; k < 3; ++k) it.c[k] = 0.5 * (it.box.lo[k] + it.box.hi[k]);
+            it.index = (int32_t)i;
+        }
+        nodes.resize(boxes.size());
+    }
 
     static double area(const Box& b) {
         if (b.empty()) return 0.0;
@@ -126,7 +142,7 @@ struct Builder {
     }
     Box range_box(int begin, int end) const {
         Box b;
-        for (int i = begin; i < end; ++i) b.add(boxes[(size_t)order[(size_t)i]]);
+        for (int i = begin; i < end; ++i) b.add(items[(size_t)i].box);
         return b;
     }
     void store_box(float lo[3], float hi[3], const Box& b) const {
@@ -134,80 +150,89 @@ struct Builder {
     }
     static int32_t leaf_link(int begin, int count) { return ~((begin << 2) | (count - 1)); }
 
-    // returns the link for range [begin, end)
-    int32_t build(int begin, int end, int level) {
-        depth = std::max(depth, level);
+    // Binned-SAH split of items [begin, end) whose union is `whole`; returns the link for the range.
+    // Subtrees over disjoint item ranges are independent, so the top levels fork threads.  A node's slot is derived
+    // from its split position (unique per inner node), which makes the result independent of thread timing;
+    // compact() then renumbers the nodes in depth-first order, the layout a sequential build would produce.
+    int32_t build(int begin, int end, int level, const Box& whole) {
+        for (int seen = depth.load(); level > seen && !depth.compare_exchange_weak(seen, level);) {}
         const int n = end - begin;
         if (n <= 1) return leaf_link(begin, n);
-        // split candidates on the centroid bounds
-        Box cb;
-        for (int i = begin; i < end; ++i) {
-            const Box& b = boxes[(size_t)order[(size_t)i]];
-            const double c[3] = {0.5 * (b.lo[0] + b.hi[0]), 0.5 * (b.lo[1] + b.hi[1]), 0.5 * (b.lo[2] + b.hi[2])};
-            cb.add(c);
+        const int NB = std::min(16, std::max(4, n));  // few items: few bins (the per-node fixed cost is what small nodes pay)
+        Box cb;  // centroid bounds: the split candidates
+        for (int i = begin; i < end; ++i) cb.add(items[(size_t)i].c);
+        double ext[3], scale[3];
+        for (int a = 0; a < 3; ++a) {
+            ext[a] = cb.hi[a] - cb.lo[a];
+            scale[a] = ext[a] > 0.0 ? (double)NB / ext[a] : 0.0;
         }
-        constexpr int NB = 16;
+        auto bin_of = [&](const Item& it, int a) {
+            const int k = (int)((it.c[a] - cb.lo[a]) * scale[a]);
+            return std::min(std::max(k, 0), NB - 1);
+        };
+        Box bin_box[3][16];
+        int bin_n[3][16] = {};
+        for (int i = begin; i < end; ++i) {  // one pass fills the bins of all three axes
+            const Item& it = items[(size_t)i];
+            for (int a = 0; a < 3; ++a) {
+                if (!(ext[a] > 0.0)) continue;
+                const int k = bin_of(it, a);
+                bin_box[a][k].add(it.box);
+                bin_n[a][k]++;
+            }
+        }
         double best_cost = INF;
         int best_axis = -1, best_bin = -1;
-        for (int axis = 0; axis < 3; ++axis) {
-            const double ext = cb.hi[axis] - cb.lo[axis];
-            if (!(ext > 0.0)) continue;
-            Box bin_box[NB];
-            int bin_n[NB] = {0};
-            for (int i = begin; i < end; ++i) {
-                const Box& b = boxes[(size_t)order[(size_t)i]];
-                const double c = 0.5 * (b.lo[axis] + b.hi[axis]);
-                int k = (int)((c - cb.lo[axis]) / ext * NB);
-                k = std::min(std::max(k, 0), NB - 1);
-                bin_box[k].add(b);
-                bin_n[k]++;
-            }
-            double right_area[NB];
-            int right_n[NB];
+        Box best_left, best_right;
+        for (int a = 0; a < 3; ++a) {
+            if (!(ext[a] > 0.0)) continue;
+            Box right_box[16];
+            int right_n[16];
             Box acc;
             int cnt = 0;
             for (int k = NB - 1; k > 0; --k) {
-                acc.add(bin_box[k]);
-                cnt += bin_n[k];
-                right_area[k] = area(acc);
+                acc.add(bin_box[a][k]);
+                cnt += bin_n[a][k];
+                right_box[k] = acc;
                 right_n[k] = cnt;
             }
             Box left;
             int ln = 0;
             for (int k = 0; k < NB - 1; ++k) {
-                left.add(bin_box[k]);
-                ln += bin_n[k];
+                left.add(bin_box[a][k]);
+                ln += bin_n[a][k];
                 if (ln == 0 || right_n[k + 1] == 0) continue;
-                const double cost = area(left) * ln + right_area[k + 1] * right_n[k + 1];
-                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = k; }
+                const double cost = area(left) * ln + area(right_box[k + 1]) * right_n[k + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; best_left = left; best_right = right_box[k + 1]; }
             }
         }
         int mid;
+        Box lb, rb;
         if (best_axis < 0) {
             if (n <= 4) return leaf_link(begin, n);
             mid = begin + n / 2;  // identical centroids: split by index
+            lb = range_box(begin, mid);
+            rb = range_box(mid, end);
         } else {
-            const Box whole = range_box(begin, end);
             // leaf cost: every item test is an f64 primitive intersection (expensive) -> weight 3 vs 1 per node
             const double leaf_cost = 3.0 * n;
             const double split_cost = 1.0 + 3.0 * best_cost / std::max(area(whole), 1e-300);
             if (n <= 4 && leaf_cost <= split_cost) return leaf_link(begin, n);
-            const double ext = cb.hi[best_axis] - cb.lo[best_axis];
-            auto it = std::partition(order.begin() + begin, order.begin() + end, [&](int32_t item) {
-                const Box& b = boxes[(size_t)item];
-                const double c = 0.5 * (b.lo[best_axis] + b.hi[best_axis]);
-                int k = (int)((c - cb.lo[best_axis]) / ext * NB);
-                k = std::min(std::max(k, 0), NB - 1);
-                return k <= best_bin;
-            });
-            mid = (int)(it - order.begin());
-            if (mid == begin || mid == end) mid = begin + n / 2;
+            auto it = std::partition(items.begin() + begin, items.begin() + end, [&](const Item& x) { return bin_of(x, best_axis) <= best_bin; });
+            mid = (int)(it - items.begin());
+            lb = best_left;
+            rb = best_right;
         }
-        const int32_t self = (int32_t)nodes.size();
-        nodes.emplace_back();
-        const Box lb = range_box(begin, mid), rb = range_box(mid, end);
-        const int32_t l = build(begin, mid, level + 1);
-        const int32_t r = build(mid, end, level + 1);
+        const int32_t self = mid - 1;
+        int32_t l, r;
+        if (level < 4 && n >= 1024) {
+            std::thread left([&] { l = build(begin, mid, level + 1, lb); });
+            r = build(mid, end, level + 1, rb);
+            left.join();
+        } else {
+            l = build(begin, mid, level + 1, lb);
+            r = build(mid, end, level + 1, rb);
+        }
         BvhNode& nd = nodes[(size_t)self];
         std::memset(&nd, 0, sizeof nd);
         store_box(nd.lo0, nd.hi0, lb);
@@ -215,6 +240,33 @@ struct Builder {
         nd.c0 = l;
         nd.c1 = r;
         return self;
+    }
+    // depth-first renumbering of the sparse slots into a dense array; returns the new root link
+    int32_t compact(int32_t root) {
+        if (root < 0) { nodes.clear(); return root; }
+        std::vector<BvhNode> dense;
+        std::vector<std::pair<int32_t, int32_t>> stack;  // (sparse slot, dense index)
+        dense.emplace_back();
+        stack.push_back({root, 0});
+        while (!stack.empty()) {
+            const auto [slot, at] = stack.back();
+            stack.pop_back();
+            BvhNode nd = nodes[(size_t)slot];
+            // children are numbered when their parent is written: left first, so the left subtree follows its parent
+            int32_t kids[2] = {nd.c0, nd.c1};
+            int32_t dense_kids[2];
+            for (int k = 0; k < 2; ++k) {
+                if (kids[k] >= 0) { dense_kids[k] = (int32_t)dense.size(); dense.emplace_back(); }
+                else dense_kids[k] = kids[k];
+            }
+            if (kids[1] >= 0) stack.push_back({kids[1], dense_kids[1]});
+            if (kids[0] >= 0) stack.push_back({kids[0], dense_kids[0]});
+            nd.c0 = dense_kids[0];
+            nd.c1 = dense_kids[1];
+            dense[(size_t)at] = nd;
+        }
+        nodes.swap(dense);
+        return 0;
     }
 };
 
@@ -480,17 +532,15 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         for (int k = 0; k < 3; ++k) S = std::max({S, std::fabs(root.lo[k]), std::fabs(root.hi[k])});
         // fp32 traversal error bound is ~9 * 2^-24 * S (DESIGN.md "conservative fp32 culling"); pad with margin
         const double pad = 4e-6 * std::max(S, 1e-30);
-        Builder bld{item_boxes, {}, {}, pad};
-        bld.order.resize(item_ids.size());
-        for (size_t i = 0; i < item_ids.size(); ++i) bld.order[i] = (int32_t)i;
-        out.bvh_root = bld.build(0, (int)item_ids.size(), 0);
+        Builder bld(item_boxes, pad);
+        out.bvh_root = bld.compact(bld.build(0, (int)item_ids.size(), 0, root));
         out.bvh = std::move(bld.nodes);
         out.bvh_depth = bld.depth;
         if (out.bvh_depth + 2 > rtcdev::BVH_STACK) return "BVH deeper than the traversal stack";
         out.leaf_items.resize(item_ids.size());
         out.leaf_tri.assign(item_ids.size() * 10, 0.0);
         for (size_t i = 0; i < item_ids.size(); ++i) {
-            const int32_t id = item_ids[(size_t)bld.order[i]];
+            const int32_t id = item_ids[(size_t)bld.items[i].index];
             rtcdev::LeafItem li{id, 0, 0, -1};
             if (id >= 0) {
                 const rtcdev::Prim& p = out.prims[(size_t)id];

@@ -1,4 +1,9 @@
-set -x
-python __graft_entry__.py --smoke
-python bench.py --steps 5 --warmup 3 | tee gpurun_out/bench_n1.json
-python bench.py --impl reference --steps 2 --warmup 1 | tee gpurun_out/bench_ref.json
+# bench at N = 1 (and the reference arm); N > 1 when the box has the GPUs: tools/gpu_bench.sh [N]
+mkdir -p gpurun_out
+N=${1:-1}
+if [ "$N" = "1" ]; then
+  python bench.py --steps 10 --warmup 3 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench rc=$?"; cat gpurun_out/bench_n1.json; tail -5 gpurun_out/bench_n1.err
+  python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cat gpurun_out/bench_ref.json
+else
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"; cat gpurun_out/bench_n$N.json; tail -8 gpurun_out/bench_n$N.err
+fi
