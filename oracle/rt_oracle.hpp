@@ -7,8 +7,8 @@
 // use anything under oracle/.
 //
 // Parity pinning: oracle/test_oracle.cpp checks this restatement against the reference's
-// own known-answer unit tests (transcribed as data), and tests/test_golden_png.py checks
-// whole renders against the reference's committed PNG outputs (decoded fixtures).
+// own known-answer unit tests (transcribed as data), and tests/test_oracle_cpu.py checks
+// windows of native-resolution renders against the reference's committed PNG outputs (tests/golden/).
 // Unpinned by the reference's tests: noise.rs (Simplex is pinned only through the
 // hexagon PNG; Fractal by nothing), MixtureKind::{Blend,RingGradient}, JitterKind::Color.
 //
