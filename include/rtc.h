@@ -161,6 +161,7 @@ typedef struct rtc_stats {
     uint64_t ray_transforms;  /* world -> object ray transforms (src/ray.rs:14-19) actually computed */
     /* RTC_FLAG_PROFILE only: CUDA-event time per kernel class, launches serialised on one stream */
     double ms_trace, ms_shadow, ms_shade;
+    uint64_t max_node_visits; /* the longest single closest-hit traversal of the call (BVH node visits of one ray) */
 } rtc_stats;
 
 typedef struct rtc_scene rtc_scene;

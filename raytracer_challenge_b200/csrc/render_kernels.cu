@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
     const uint32_t stride = gridDim.x * blockDim.x;
     // every lane of a warp runs the same number of iterations so the warp-aggregated push stays convergent
     const uint32_t n_round = (n_in + 31u) & ~31u;
-    uint32_t c_active = 0;
+    uint32_t c_active = 0, longest = 0;
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
         Ray ray;
@@ -157,7 +157,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
         double n1 = 1.0, n2 = 1.0;
         if (active) {
             c_active++;
+            const uint32_t nodes_before = tally.nodes;
             hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
+            longest = max(longest, tally.nodes - nodes_before);
             if ((FEAT & FEAT_TRANSPARENT) && hit.prim >= 0) {
                 const int material = __ldg(&sc.prims[hit.prim].material);
                 if (sc.materials[material].transparency != 0.0)
@@ -180,6 +182,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
         }
     }
     flush_tally(tally, lv.stats, lane);
+    for (int off = 16; off; off >>= 1) longest = max(longest, __shfl_down_sync(0xffffffffu, longest, off));
+    if (lane == 0 && longest) atomicMax(lv.stats + 7, (unsigned long long)longest);
     if (PRIMARY) {
         for (int off = 16; off; off >>= 1) c_active += __shfl_down_sync(0xffffffffu, c_active, off);
         if (lane == 0 && c_active) atomicAdd(lv.stats + 0, (unsigned long long)c_active);

@@ -50,7 +50,7 @@ struct LevelParams {
     unsigned long long* hit_count;
     uint8_t* shadow;
     double* accum;              // 3 doubles per sample of the batch
-    unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms
+    unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms, [7] most node visits of one closest-hit query
     int* overflow;
 };
 

@@ -78,6 +78,8 @@ struct DeviceCtx {
     uint64_t counter_batches = 0;
     int* overflow = nullptr;
     std::vector<cudaEvent_t> prof_events;  // RTC_FLAG_PROFILE: one event per launch boundary
+    void* spare_arena = nullptr;           // scene arena of the last destroyed scene, reused by the next create
+    size_t spare_arena_bytes = 0;
 };
 DeviceCtx g_ctx[MAX_DEVICES];
 
@@ -127,6 +129,7 @@ struct rtc_scene {
     rtchost::HostScene host;
     rtcdev::Scene dev{};
     void* arena = nullptr;  // one device allocation holding every scene array
+    size_t arena_bytes = 0;
 };
 
 extern "C" {
@@ -234,7 +237,19 @@ int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16) {
 void rtc_scene_destroy(rtc_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->arena);
+    if (s->arena) {
+        // cudaFree synchronises the device and was seen to take hundreds of ms now and then; the arena is parked in
+        // the device context instead, where the next rtc_scene_create (the next frame of a par_render loop) picks it up
+        DeviceCtx& c = g_ctx[s->device];
+        std::lock_guard<std::mutex> lock(c.mu);
+        void* drop = s->arena;
+        if (s->arena_bytes > c.spare_arena_bytes) {
+            drop = c.spare_arena;
+            c.spare_arena = s->arena;
+            c.spare_arena_bytes = s->arena_bytes;
+        }
+        if (drop) cudaFree(drop);
+    }
     delete s;
 }
 
@@ -250,6 +265,7 @@ void rtc_release_device_memory(int device) {
     cudaFree(c.counters); c.counters = nullptr;
     cudaFreeHost(c.counters_host); c.counters_host = nullptr;
     c.counter_batches = 0;
+    cudaFree(c.spare_arena); c.spare_arena = nullptr; c.spare_arena_bytes = 0;
 }
 
 int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
@@ -287,7 +303,20 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
                  o_leaf_tri = PLACE(h.leaf_tri), o_unbounded = PLACE(h.unbounded), o_csg_ops = PLACE(h.csg_ops), o_csg_roots = PLACE(h.csg_roots);
 #undef PLACE
     h.device_bytes = (int64_t)blob.size();
-    if (cudaMalloc(&s->arena, blob.size()) != cudaSuccess) return fail("rtc_scene_create: cudaMalloc of the scene arena failed");
+    {
+        DeviceCtx& c = g_ctx[device];
+        std::lock_guard<std::mutex> lock(c.mu);
+        if (c.spare_arena && c.spare_arena_bytes >= blob.size()) {
+            s->arena = c.spare_arena;
+            s->arena_bytes = c.spare_arena_bytes;
+            c.spare_arena = nullptr;
+            c.spare_arena_bytes = 0;
+        }
+    }
+    if (!s->arena) {
+        if (cudaMalloc(&s->arena, blob.size()) != cudaSuccess) return fail("rtc_scene_create: cudaMalloc of the scene arena failed");
+        s->arena_bytes = blob.size();
+    }
     if (cudaMemcpy(s->arena, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
         cudaFree(s->arena);
         return fail(std::string("rtc_scene_create: scene upload failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -413,7 +442,10 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     uint64_t worst = 1;
     for (int k = 0; k < o.fuel && fan == 2; ++k) worst *= 2;
     const uint64_t unit = row_major ? (uint64_t)f.tiles_x * per_tile : per_tile;  // batch granularity in pixel slots
-    const uint64_t target_samples = (uint64_t)env_int("RTC_BATCH_SAMPLES", 2 << 20, 1024, 1 << 28);
+    // default: about RTC_BATCHES (4) batches per call so the pipelines have something to overlap, within [256 Ki, 2 Mi]
+    // samples (measured: more, smaller batches only add launches; fewer leave the deep levels' tails exposed)
+    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)env_int("RTC_BATCHES", 4, 1, 1024), 256u << 10), 2u << 20);
+    const uint64_t target_samples = (uint64_t)env_int("RTC_BATCH_SAMPLES", (int)auto_samples, 1024, 1 << 28);
     const uint64_t max_records = (uint64_t)24 << 20;  // records per queue
     uint64_t batch_samples = std::min(target_samples, std::max<uint64_t>(max_records / worst, 1));
     uint64_t batch_pixels = std::max<uint64_t>(batch_samples / f.spp / unit, 1) * unit;
@@ -552,12 +584,13 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         // R_ref: the reference re-traces every secondary sub-tree once per light, so a ray at
         // bounce level k exists L^k times there, and each of its hits issues L shadow queries.
         double mult = 1.0;
-        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0, hits_all = 0, tally[4] = {0, 0, 0, 0};
+        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0, hits_all = 0, tally[4] = {0, 0, 0, 0}, longest = 0;
         double ref = 0.0;
         for (uint64_t b = 0; b < n_batches; ++b) {
             const unsigned long long* c = ctx.counters_host + b * COUNTERS_PER_BATCH;
             primary += c[32]; refl += c[33]; refr += c[34];
             for (int k = 0; k < 4; ++k) tally[k] += c[35 + k];
+            longest = std::max<uint64_t>(longest, c[39]);
             mult = 1.0;
             for (int level = 0; level <= o.fuel; ++level) {
                 const uint64_t n_in = level == 0 ? c[32] : std::min<uint64_t>(c[level], q_cap);
@@ -583,6 +616,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         stats->triangle_tests = tally[1];
         stats->primitive_tests = tally[2];
         stats->ray_transforms = tally[3];
+        stats->max_node_visits = longest;
         for (size_t k = 1; k < n_prof; ++k) {
             float t = 0.f;
             if (prof_class[k] < 0 || cudaEventElapsedTime(&t, ctx.prof_events[k - 1], ctx.prof_events[k]) != cudaSuccess) continue;
@@ -646,6 +680,7 @@ int rtc_render_multi(rtc_scene* const* scenes, int n, const rtc_camera* cam, con
             stats->surface_hits += a.surface_hits; stats->bvh_node_visits += a.bvh_node_visits;
             stats->triangle_tests += a.triangle_tests; stats->primitive_tests += a.primitive_tests;
             stats->ray_transforms += a.ray_transforms;
+            stats->max_node_visits = std::max(stats->max_node_visits, a.max_node_visits);
             stats->ms_kernels = std::max(stats->ms_kernels, a.ms_kernels);  // devices run concurrently: the slowest one counts
             stats->ms_trace_shade = std::max(stats->ms_trace_shade, a.ms_trace_shade);
         }

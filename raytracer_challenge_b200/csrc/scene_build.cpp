@@ -4,6 +4,7 @@
 #include <atomic>
 #include <thread>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <limits>
@@ -123,8 +124,10 @@ struct Builder {
     std::vector<Item> items;
     std::vector<BvhNode> nodes;  // build(): slot mid - 1 of the node that splits at `mid` (sparse); compact(): final
     double pad;
+    double leaf_weight = 3.0;  // cost of one exact f64 primitive test relative to one fp32 node visit
     std::atomic<int> depth{0};
     Builder(const std::vector<Box>& boxes, double pad_) : pad(pad_) {
+        if (const char* w = std::getenv("RTC_LEAF_WEIGHT")) leaf_weight = std::max(0.1, std::atof(w));
         items.resize(boxes.size());
         for (size_t i = 0; i < boxes.size(); ++i) {
             Item& it = items[i];
@@ -215,8 +218,8 @@ struct Builder {
             rb = range_box(mid, end);
         } else {
             // leaf cost: every item test is an f64 primitive intersection (expensive) -> weight 3 vs 1 per node
-            const double leaf_cost = 3.0 * n;
-            const double split_cost = 1.0 + 3.0 * best_cost / std::max(area(whole), 1e-300);
+            const double leaf_cost = leaf_weight * n;
+            const double split_cost = 1.0 + leaf_weight * best_cost / std::max(area(whole), 1e-300);
             if (n <= 4 && leaf_cost <= split_cost) return leaf_link(begin, n);
             auto it = std::partition(items.begin() + begin, items.begin() + end, [&](const Item& x) { return bin_of(x, best_axis) <= best_bin; });
             mid = (int)(it - items.begin());

@@ -141,6 +141,7 @@ pub struct rtc_stats {
     pub ms_trace: f64,
     pub ms_shadow: f64,
     pub ms_shade: f64,
+    pub max_node_visits: u64,
 }
 
 #[repr(C)]
