@@ -143,6 +143,22 @@ def run_reference(args):
 
 
 def run_cuda(args):
+    # stdout carries exactly one line (the JSON): anything a library prints meanwhile (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        line = run_cuda_inner(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_cuda_inner(args):
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -301,9 +317,7 @@ def run_cuda(args):
     sess.close()
     if world > 1:
         dist.destroy_process_group()
-    if line is not None:
-        print(json.dumps(line))
-    return 0
+    return line
 
 
 def rooflines(R, prof, world):
@@ -337,18 +351,23 @@ def rooflines(R, prof, world):
     sec = max(d["ms"], 1e-9) * 1e-3
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(tpath):
+    traffic_source = None
+    if os.path.exists(tpath):  # per-launch DRAM bytes of the same kernel from the committed `ncu --set full` capture
         with open(tpath) as f:
-            traffic = json.load(f)
+            t = json.load(f)
+        traffic = t.get("per_launch_dram_bytes", {}).get(dominant)
+        traffic_source = t.get("source")
     out = {}
     try:
         mb = R.microbench()
     except Exception as e:  # noqa: BLE001
         mb = {"error": str(e)}
     gbs = d["bytes"] / sec / 1e9
+    n_launch = int(prof.kernel_launches // 3)  # trace / shadow / shade launch once per level per batch
     out["roofline"] = {
         "bound": "hbm", "kernel": dominant, "achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
-        "traffic": traffic, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+        "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_source,
+        "launches_per_frame": n_launch, "achieved_bytes_per_launch": d["bytes"] / max(n_launch, 1), "ms_per_launch": d["ms"] / max(n_launch, 1), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
         "ms_per_frame_in_this_kernel": d["ms"], "algorithmic_bytes_per_frame": d["bytes"],
         "note": "HBM sees only ray queues, hit lists and the frame buffer (the 1.6 MB scene is L1/L2-resident): this path is bound by "
                 "CUDA-core issue under divergence and by L1/L2 latency on BVH fetches, not by HBM — see roofline_fp64 / roofline_fp32 and DESIGN.md",

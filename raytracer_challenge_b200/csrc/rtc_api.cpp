@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
@@ -277,7 +278,9 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     if (device < 0 || device >= n_dev || device >= MAX_DEVICES) return fail("rtc_scene_create: device ordinal out of range");
     std::unique_ptr<rtc_scene> s(new rtc_scene);
     s->device = device;
+    const auto t_build0 = std::chrono::steady_clock::now();
     const std::string err = rtchost::build_host_scene(*desc, s->host);
+    const auto t_build1 = std::chrono::steady_clock::now();
     if (!err.empty()) return fail("rtc_scene_create: " + err);
     CU(cudaSetDevice(device));
     {
@@ -349,6 +352,11 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
+    if (std::getenv("RTC_TRACE")) {
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        std::fprintf(stderr, "rtc_scene_create: host build %.3f ms, pack + upload %.3f ms (%zu bytes)\n", ms(t_build0, t_build1),
+                     ms(t_build1, std::chrono::steady_clock::now()), blob.size());
+    }
     *out = s.release();
     return 0;
 }
