@@ -194,8 +194,12 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
     int sp = 0;
     int link = sc.bvh_root;
     float thi = walk_thi(v.tmax(), w.te);
+    // "while-while" (Aila & Laine): every lane first descends through inner nodes until it stands on a leaf, THEN the
+    // warp runs the leaf code once for all of them.  With a single if/else loop almost every iteration has some lane
+    // on a leaf, so every iteration pays for the (4-5x more expensive, f64) leaf code.
+    constexpr int WALK_DONE = (int)0x80000000;  // never a leaf link: ~enc with enc >= 0 is > INT_MIN
     for (;;) {
-        if (link >= 0) {
+        while (link >= 0) {
             tally.nodes++;
             const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
             const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
@@ -207,17 +211,20 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
                 const bool first0 = n0 <= n1;
                 stack[sp++] = first0 ? c1 : c0;
                 link = first0 ? c0 : c1;
-                continue;
+            } else if (h0) {
+                link = c0;
+            } else if (h1) {
+                link = c1;
+            } else {
+                link = sp ? stack[--sp] : WALK_DONE;
             }
-            if (h0) { link = c0; continue; }
-            if (h1) { link = c1; continue; }
-        } else {
-            const int enc = ~link;
-            const int first = enc >> 2, count = (enc & 3) + 1;
-            for (int i = 0; i < count; ++i)
-                if (v.leaf(first + i)) return;
-            thi = walk_thi(v.tmax(), w.te);
         }
+        if (link == WALK_DONE) return;
+        const int enc = ~link;
+        const int first = enc >> 2, count = (enc & 3) + 1;
+        for (int i = 0; i < count; ++i)
+            if (v.leaf(first + i)) return;
+        thi = walk_thi(v.tmax(), w.te);
         if (sp == 0) return;
         link = stack[--sp];
     }

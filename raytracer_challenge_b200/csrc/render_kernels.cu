@@ -1,20 +1,22 @@
-// Wavefront kernels of the render path.  Three launches per bounce level replace the recursion of
-// World::color_at -> shade_hit -> reflected_color / refracted_color (src/world.rs:50-149):
+// Wavefront kernels of the render path.  The recursion of World::color_at -> shade_hit -> reflected_color /
+// refracted_color (src/world.rs:50-149) becomes, per batch of samples:
 //
-//   trace_closest : one thread per ray of the level (level 0: Camera::ray_at_pixel, src/camera.rs:39-55, generated
-//                   in-kernel; level k>0: the compacted queue the previous level wrote) -> closest hit
-//                   (World::intersect + sort + hit, src/world.rs:18-24, src/intersection.rs:123-132) and, for hits
-//                   on transparent materials, n1/n2 (src/intersection.rs:70-103) -> compacted hit list
-//   trace_shadow  : one thread per (hit, light), light-major so a warp's rays run towards the same light:
-//                   World::is_shadowed (src/world.rs:26-48) -> one byte per (hit, light)
-//   shade         : one thread per hit: prepare_state (src/intersection.rs:50-121), pattern colour, Phong term per
-//                   light (src/shape.rs:429-463), accumulate throughput * surface colour, push reflected / refracted
-//                   children (scalar throughput, remaining fuel) to the next level's queue (src/world.rs:66-132)
+//   trace_spawn  x (fuel + 1), a chain: one thread per ray of the level (level 0: Camera::ray_at_pixel,
+//                  src/camera.rs:39-55, generated in-kernel; level k > 0: the queue level k-1 wrote) -> closest hit
+//                  (World::intersect + sort + hit, src/world.rs:18-24, src/intersection.rs:123-132), n1/n2 for
+//                  transparent hits (src/intersection.rs:70-103), the surface frame of prepare_state
+//                  (src/intersection.rs:50-68) -> hit record appended to the level's segment of the hit list, and the
+//                  reflected / refracted children (scalar throughput, remaining fuel; src/world.rs:66-132) pushed to
+//                  the next level's queue
+//   trace_shadow x 1: one thread per (hit, light) over the hits of ALL levels, light-major: World::is_shadowed
+//                  (src/world.rs:26-48) -> one byte per (hit, light)
+//   shade        x (fuel + 1), in level order: pattern colour, Phong term per light (src/shape.rs:429-463),
+//                  throughput * surface colour added to the sample
 //
-// Each kernel holds exactly one BVH traversal (or none), so its instruction footprint stays small and the lanes of a
-// warp run the same code; the hit list removes the lanes that would idle after a miss (profiles/README.md, r01a).
-// The geometric part of prepare_state (point, normal, over_point) is recomputed by the shadow and the shade kernel
-// from (ray, t, primitive, u, v) instead of being stored: ~100 flops against ~150 bytes of queue traffic.
+// Each kernel holds one BVH traversal (or none), so its instruction footprint stays small (profiles/README.md, r01a);
+// the level-to-level dependency is the trace chain only, the shadow rays of a batch are one fat launch instead of one
+// thin launch per level, and neither the shadow nor the shading kernel gathers from the ray queue or recomputes the
+// surface frame: everything they need is in the hit record (96 B, coalesced).
 //
 // The reference evaluates the secondary rays once per light inside the light loop (src/world.rs:58-79), i.e. a
 // child's colour is added L times; here each child is traced once with its weight multiplied by L.
@@ -135,37 +137,86 @@ __device__ __forceinline__ Surface surface_at(const Scene& sc, const Prim& prim,
     return s;
 }
 
-// ---- kernel 1: closest hit -> compacted hit list ---------------------------------------------------------------
+// prefix sums of the per-level hit counts: first[k] = hits of the levels before k, first[n_levels] = all hits
+__device__ __forceinline__ uint32_t hit_prefix(const HitList& hl, uint32_t* first) {
+    uint32_t total = 0;
+    for (int k = 0; k < hl.n_levels; ++k) {
+        first[k] = total;
+        const unsigned long long n = hl.counts[k];
+        total += (uint32_t)(n < hl.seg_cap[k] ? n : hl.seg_cap[k]);
+    }
+    first[hl.n_levels] = total;
+    return total;
+}
+
+// ---- kernel 1: closest hit + surface frame + children --------------------------------------------------------
+// One thread per ray of the level.  For a hit it computes the geometric half of prepare_state once, appends the hit
+// record to this level's segment of the hit list and pushes the reflected / refracted children to the next level's
+// queue (src/world.rs:66-78,84-132) — so the next level depends on this kernel only, and the shadow / shading work
+// of all levels is done afterwards in two fat launches.
 template <int FEAT, bool PRIMARY>
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest(const Scene sc, const FrameParams f, const LevelParams lv) {
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRACE_MIN_BLOCKS_TRANSPARENT : RTC_TRACE_MIN_BLOCKS) trace_spawn(const Scene sc, const FrameParams f, const LevelParams lv, const HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
     const uint32_t n_in = level_rays<PRIMARY>(lv);
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
-    // every lane of a warp runs the same number of iterations so the warp-aggregated push stays convergent
+    const int L = sc.n_lights;
+    const uint32_t seg = hl.seg_off[lv.level], seg_cap = hl.seg_cap[lv.level];
+    // every lane of a warp runs the same number of iterations so the warp-aggregated pushes stay convergent
     const uint32_t n_round = (n_in + 31u) & ~31u;
-    uint32_t c_active = 0, longest = 0;
+    uint32_t c_active = 0, longest = 0, c_refl = 0, c_refr = 0;
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
         Ray ray;
-        double w;
-        uint32_t sample;
-        int fuel;
+        double w = 0.0;
+        uint32_t sample = 0;
+        int fuel = 0;
         const bool active = idx < n_in && load_ray<PRIMARY>(f, lv, idx, ray, w, sample, fuel);
         Hit hit;
         hit.prim = -1;
-        double n1 = 1.0, n2 = 1.0;
+        bool push_refl = false, push_refr = false;
+        Ray r_refl, r_refr;
+        double w_refl = 0.0, w_refr = 0.0;
+        Surface s;
         if (active) {
             c_active++;
             const uint32_t nodes_before = tally.nodes;
             hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
             longest = max(longest, tally.nodes - nodes_before);
-            if ((FEAT & FEAT_TRANSPARENT) && hit.prim >= 0) {
-                const int material = __ldg(&sc.prims[hit.prim].material);
-                if (sc.materials[material].transparency != 0.0)
+            if (hit.prim >= 0) {
+                const Prim prim = load_prim(sc, hit.prim);
+                const Material& mat = sc.materials[prim.material];
+                const double reflective = mat.reflective, transparency = mat.transparency;
+                double n1 = 1.0, n2 = 1.0, reflectance = 0.0;
+                if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0)
                     refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, tally, lv.overflow);
+                s = surface_at(sc, prim, ray, hit.t, hit.u, hit.v);
+                if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) reflectance = schlick(s.eye, s.normal, n1, n2);
+                if (fuel > 0 && L > 0) {
+                    const bool both = reflective > 0.0 && transparency > 0.0;
+                    if (reflective != 0.0) {
+                        push_refl = true;
+                        r_refl.o = s.over_point;
+                        r_refl.d = reflect(ray.d, s.normal);
+                        w_refl = w * (double)L * reflective * (both ? reflectance : 1.0);
+                    }
+                    if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) {
+                        const double n_ratio = n1 / n2;
+                        const double cos_i = dot(s.eye, s.normal);
+                        const double sin2_t = (n_ratio * n_ratio) * (1.0 - cos_i * cos_i);
+                        if (!(sin2_t > 1.0)) {
+                            const double cos_t = sqrt(1.0 - sin2_t);
+                            push_refr = true;
+                            r_refr.o = s.point - (s.normal * RTC_EPSILON);
+                            r_refr.d = s.normal * (n_ratio * cos_i - cos_t) - s.eye * n_ratio;
+                            w_refr = w * (double)L * transparency * (both ? (1.0 - reflectance) : 1.0);
+                        }
+                    }
+                }
             }
         }
+        const unsigned below = (1u << lane) - 1u;
+        // ---- hit record ----
         const bool is_hit = active && hit.prim >= 0;
         const unsigned m = __ballot_sync(0xffffffffu, is_hit);
         if (m) {
@@ -173,49 +224,90 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_closest
             if (lane == 0) base = atomicAdd(lv.hit_count, (unsigned long long)__popc(m));
             base = __shfl_sync(0xffffffffu, base, 0);
             if (is_hit) {
-                const uint64_t slot = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
-                lv.hit_ray[slot] = idx;
-                lv.hit0[slot] = make_double2(hit.t, __longlong_as_double((long long)hit.prim));
-                lv.hit1[slot] = make_double2(hit.u, hit.v);
-                if (FEAT & FEAT_TRANSPARENT) lv.hit2[slot] = make_double2(n1, n2);
+                const uint64_t slot = base + (uint64_t)__popc(m & below);
+                if (slot < seg_cap) {
+                    const size_t at = (size_t)seg + slot;
+                    hl.a[at] = make_double2(s.over_point.x, s.over_point.y);
+                    hl.b[at] = make_double2(s.over_point.z, s.normal.x);
+                    hl.c[at] = make_double2(s.normal.y, s.normal.z);
+                    hl.d[at] = make_double2(s.eye.x, s.eye.y);
+                    hl.e[at] = make_double2(s.eye.z, w);
+                    hl.f[at] = make_double2(__longlong_as_double((long long)((uint64_t)sample << 32 | (uint32_t)hit.prim)), 0.0);
+                } else *lv.overflow = 2;
+            }
+        }
+        // ---- children: warp-aggregated compaction into the next level's queue, one atomic per warp ----
+        const unsigned m_refl = __ballot_sync(0xffffffffu, push_refl);
+        const unsigned m_refr = (FEAT & FEAT_TRANSPARENT) ? __ballot_sync(0xffffffffu, push_refr) : 0u;
+        const int n_push = __popc(m_refl) + __popc(m_refr);
+        if (n_push) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(lv.out_count, (unsigned long long)n_push);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            const uint64_t packed_fuel = (uint64_t)(uint32_t)(fuel - 1) << 32 | sample;
+            if (push_refl) {
+                const uint64_t slot = base + (uint64_t)__popc(m_refl & below);
+                if (slot < lv.out_capacity) {
+                    lv.out_q0[slot] = make_double2(r_refl.o.x, r_refl.o.y);
+                    lv.out_q1[slot] = make_double2(r_refl.o.z, r_refl.d.x);
+                    lv.out_q2[slot] = make_double2(r_refl.d.y, r_refl.d.z);
+                    lv.out_q3[slot] = make_double2(w_refl, __longlong_as_double((long long)packed_fuel));
+                } else *lv.overflow = 2;
+                c_refl++;
+            }
+            if ((FEAT & FEAT_TRANSPARENT) && push_refr) {
+                const uint64_t slot = base + (uint64_t)__popc(m_refl) + (uint64_t)__popc(m_refr & below);
+                if (slot < lv.out_capacity) {
+                    lv.out_q0[slot] = make_double2(r_refr.o.x, r_refr.o.y);
+                    lv.out_q1[slot] = make_double2(r_refr.o.z, r_refr.d.x);
+                    lv.out_q2[slot] = make_double2(r_refr.d.y, r_refr.d.z);
+                    lv.out_q3[slot] = make_double2(w_refr, __longlong_as_double((long long)packed_fuel));
+                } else *lv.overflow = 2;
+                c_refr++;
             }
         }
     }
     flush_tally(tally, lv.stats, lane);
-    for (int off = 16; off; off >>= 1) longest = max(longest, __shfl_down_sync(0xffffffffu, longest, off));
-    if (lane == 0 && longest) atomicMax(lv.stats + 7, (unsigned long long)longest);
-    if (PRIMARY) {
-        for (int off = 16; off; off >>= 1) c_active += __shfl_down_sync(0xffffffffu, c_active, off);
-        if (lane == 0 && c_active) atomicAdd(lv.stats + 0, (unsigned long long)c_active);
+    for (int off = 16; off; off >>= 1) {
+        longest = max(longest, __shfl_down_sync(0xffffffffu, longest, off));
+        c_refl += __shfl_down_sync(0xffffffffu, c_refl, off);
+        c_refr += __shfl_down_sync(0xffffffffu, c_refr, off);
+        c_active += __shfl_down_sync(0xffffffffu, c_active, off);
+    }
+    if (lane == 0) {
+        if (longest) atomicMax(lv.stats + 7, (unsigned long long)longest);
+        if (c_refl) atomicAdd(lv.stats + 1, (unsigned long long)c_refl);
+        if (c_refr) atomicAdd(lv.stats + 2, (unsigned long long)c_refr);
+        if (PRIMARY && c_active) atomicAdd(lv.stats + 0, (unsigned long long)c_active);
     }
 }
 
-// ---- kernel 2: World::is_shadowed for every (hit, light) ------------------------------------------------------
-template <int FEAT, bool PRIMARY, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_shadow(const Scene sc, const FrameParams f, const LevelParams lv) {
+// ---- kernel 2: World::is_shadowed for every (hit, light) of the batch, all levels in one launch ----------------
+// Light-major: consecutive threads take consecutive hits towards the SAME light, so a warp's rays start next to each
+// other and head the same way.  Reads 24 B (over_point) per thread, coalesced; writes one byte.
+template <int FEAT, bool ANYHIT>
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADOW_MIN_BLOCKS) trace_shadow(const Scene sc, const FrameParams f, const LevelParams lv, const HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
-    const uint32_t n_hits = (uint32_t)*lv.hit_count;
+    uint32_t first[MAX_LEVELS + 1];
+    const uint32_t n_hits = hit_prefix(hl, first);
     const uint32_t L = (uint32_t)sc.n_lights;
-    const uint32_t total = n_hits * L;  // < 2^32: checked by the host (queue capacity * lights)
+    const uint32_t total = n_hits * L;  // < 2^32: checked by the host (hit capacity * lights)
     const uint32_t stride = gridDim.x * blockDim.x;
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         const uint32_t li = i / n_hits;
-        const uint32_t h = i - li * n_hits;
-        const double2 h0 = lv.hit0[h], h1 = lv.hit1[h];
-        const int prim_id = (int)__double_as_longlong(h0.y);
-        Ray ray;
-        double w;
-        uint32_t sample;
-        int fuel;
-        load_ray<PRIMARY>(f, lv, lv.hit_ray[h], ray, w, sample, fuel);
-        const Prim prim = load_prim(sc, prim_id);
-        const Surface s = surface_at(sc, prim, ray, h0.x, h1.x, h1.y);
+        const uint32_t j = i - li * n_hits;  // packed hit index over all levels
+        int k = 0;
+        while (k + 1 < hl.n_levels && j >= first[k + 1]) ++k;
+        const size_t at = (size_t)hl.seg_off[k] + (j - first[k]);
+        const double2 a = hl.a[at];
+        const double oz = hl.b[at].x;
+        const V3 over_point = mk(a.x, a.y, oz);
         const Light& light = sc.lights[li];
-        const V3 to_light = mk(light.origin[0], light.origin[1], light.origin[2]) - s.over_point;
+        const V3 to_light = mk(light.origin[0], light.origin[1], light.origin[2]) - over_point;
         const double distance = magnitude(to_light);
         Ray sray;
-        sray.o = s.over_point;
+        sray.o = over_point;
         sray.d = normalize(to_light);
         bool shadowed;
         if (ANYHIT) {
@@ -229,138 +321,64 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_TRACE_MIN_BLOCKS) trace_shadow(
     flush_tally(tally, lv.stats, threadIdx.x & 31u);
 }
 
-// ---- kernel 3: shading + children -----------------------------------------------------------------------------
-template <bool TRANSPARENT, bool PRIMARY>
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADE_MIN_BLOCKS) shade(const Scene sc, const FrameParams f, const LevelParams lv) {
+// ---- kernel 3: shading of one level's hits -------------------------------------------------------------------
+// World::shade_hit light loop (src/world.rs:58-64) + Shape::lighting (src/shape.rs:429-463); one launch per level, in
+// level order on the batch's stream, so a sample's contributions are added in a fixed order.
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADE_MIN_BLOCKS) shade(const Scene sc, const LevelParams lv, const HitList hl) {
     __shared__ uint8_t s_perm[512];
     for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
     __syncthreads();
 
-    const uint32_t n_hits = (uint32_t)*lv.hit_count;
+    uint32_t first[MAX_LEVELS + 1];
+    const uint32_t n_all = hit_prefix(hl, first);
+    const uint32_t n_hits = first[lv.level + 1] - first[lv.level];
+    const uint32_t seg = hl.seg_off[lv.level];
     const int L = sc.n_lights;
-    const unsigned lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t n_round = (n_hits + 31u) & ~31u;
-    uint32_t c_refl = 0, c_refr = 0;
-    for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n_round; h += stride) {
-        bool push_refl = false, push_refr = false;
-        Ray r_refl, r_refr;
-        double w_refl = 0.0, w_refr = 0.0;
-        uint32_t sample = 0;
-        int fuel = 0;
-        if (h < n_hits) {
-            const double2 h0 = lv.hit0[h], h1 = lv.hit1[h];
-            const int prim_id = (int)__double_as_longlong(h0.y);
-            Ray ray;
-            double w;
-            load_ray<PRIMARY>(f, lv, lv.hit_ray[h], ray, w, sample, fuel);
-            const Prim prim = load_prim(sc, prim_id);
-            const Material& mat = sc.materials[prim.material];
-            const Surface s = surface_at(sc, prim, ray, h0.x, h1.x, h1.y);
-            const double reflective = mat.reflective, transparency = mat.transparency;
-            double n1 = 1.0, n2 = 1.0, reflectance = 0.0;
-            if (TRANSPARENT && transparency != 0.0) {
-                const double2 h2 = lv.hit2[h];
-                n1 = h2.x;
-                n2 = h2.y;
-                reflectance = schlick(s.eye, s.normal, n1, n2);
-            }
-            // ---- World::shade_hit light loop, src/world.rs:58-64 + Shape::lighting, src/shape.rs:429-463 ----
-            Rgb color;
-            if (mat.flags & 1) color = rgb(mat.plain[0], mat.plain[1], mat.plain[2]);
-            else {
-                V3 pp = s.over_point;
-                double pw = 1.0;
-                xf_point4(sc.matinvs[prim.matinv].m, pp, pw);
-                color = pattern_color(sc, s_perm, mat.pattern, pp, pw);
-            }
-            Rgb sum = rgb(0.0, 0.0, 0.0);
-            for (int li = 0; li < L; ++li) {
-                const Light& light = sc.lights[li];
-                const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
-                const Rgb intensity = rgb(light.intensity[0], light.intensity[1], light.intensity[2]);
-                const V3 lightv = normalize(lpos - s.over_point);
-                const bool shadowed = lv.shadow[(uint32_t)li * n_hits + h] != 0;
-                const Rgb effective = color * intensity;
-                Rgb surface = effective * mat.ambient;
-                const double light_dot_normal = dot(lightv, s.normal);
-                if (!shadowed && light_dot_normal >= 0.0) {
-                    const Rgb diffuse = effective * mat.diffuse * light_dot_normal;
-                    Rgb specular = rgb(0.0, 0.0, 0.0);
-                    const double reflect_dot_eye = dot(reflect(-lightv, s.normal), s.eye);
-                    if (reflect_dot_eye > 0.0) specular = intensity * mat.specular * pow(reflect_dot_eye, mat.shininess);
-                    surface = surface + diffuse + specular;
-                } else {
-                    surface = surface + rgb(0.0, 0.0, 0.0) + rgb(0.0, 0.0, 0.0);
-                }
-                sum = sum + surface;
-            }
-            double* acc = lv.accum + 3 * (size_t)sample;
-            atomicAdd(acc + 0, sum.r * w);
-            atomicAdd(acc + 1, sum.g * w);
-            atomicAdd(acc + 2, sum.b * w);
-            // ---- children: src/world.rs:66-78,84-132 ----
-            if (fuel > 0 && L > 0) {
-                const bool both = reflective > 0.0 && transparency > 0.0;
-                if (reflective != 0.0) {
-                    push_refl = true;
-                    r_refl.o = s.over_point;
-                    r_refl.d = reflect(ray.d, s.normal);
-                    w_refl = w * (double)L * reflective * (both ? reflectance : 1.0);
-                }
-                if (TRANSPARENT && transparency != 0.0) {
-                    const double n_ratio = n1 / n2;
-                    const double cos_i = dot(s.eye, s.normal);
-                    const double sin2_t = (n_ratio * n_ratio) * (1.0 - cos_i * cos_i);
-                    if (!(sin2_t > 1.0)) {
-                        const double cos_t = sqrt(1.0 - sin2_t);
-                        push_refr = true;
-                        r_refr.o = s.point - (s.normal * RTC_EPSILON);
-                        r_refr.d = s.normal * (n_ratio * cos_i - cos_t) - s.eye * n_ratio;
-                        w_refr = w * (double)L * transparency * (both ? (1.0 - reflectance) : 1.0);
-                    }
-                }
-            }
+    for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n_hits; h += stride) {
+        const size_t at = (size_t)seg + h;
+        const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at], d = hl.d[at], e = hl.e[at];
+        const uint64_t bits = (uint64_t)__double_as_longlong(hl.f[at].x);
+        const V3 over_point = mk(a.x, a.y, b.x), normal = mk(b.y, c.x, c.y), eye = mk(d.x, d.y, e.x);
+        const double w = e.y;
+        const uint32_t sample = (uint32_t)(bits >> 32);
+        const Prim prim = load_prim(sc, (int)(uint32_t)(bits & 0xffffffffu));
+        const Material& mat = sc.materials[prim.material];
+        Rgb color;
+        if (mat.flags & 1) color = rgb(mat.plain[0], mat.plain[1], mat.plain[2]);
+        else {
+            V3 pp = over_point;
+            double pw = 1.0;
+            xf_point4(sc.matinvs[prim.matinv].m, pp, pw);
+            color = pattern_color(sc, s_perm, mat.pattern, pp, pw);
         }
-        // ---- warp-aggregated compaction into the next level's queue: one atomic per warp ----
-        const unsigned m_refl = __ballot_sync(0xffffffffu, push_refl);
-        const unsigned m_refr = TRANSPARENT ? __ballot_sync(0xffffffffu, push_refr) : 0u;
-        const int n_push = __popc(m_refl) + __popc(m_refr);
-        if (n_push) {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(lv.out_count, (unsigned long long)n_push);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            const unsigned below = (1u << lane) - 1u;
-            const uint64_t packed_fuel = (uint64_t)(uint32_t)(fuel - 1) << 32 | sample;
-            if (push_refl) {
-                const uint64_t slot = base + (uint64_t)__popc(m_refl & below);
-                if (slot < lv.out_capacity) {
-                    lv.out_q0[slot] = make_double2(r_refl.o.x, r_refl.o.y);
-                    lv.out_q1[slot] = make_double2(r_refl.o.z, r_refl.d.x);
-                    lv.out_q2[slot] = make_double2(r_refl.d.y, r_refl.d.z);
-                    lv.out_q3[slot] = make_double2(w_refl, __longlong_as_double((long long)packed_fuel));
-                } else *lv.overflow = 2;
-                c_refl++;
+        const double specular_k = mat.specular, shininess = mat.shininess;
+        Rgb sum = rgb(0.0, 0.0, 0.0);
+        for (int li = 0; li < L; ++li) {
+            const Light& light = sc.lights[li];
+            const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
+            const Rgb intensity = rgb(light.intensity[0], light.intensity[1], light.intensity[2]);
+            const V3 lightv = normalize(lpos - over_point);
+            const bool shadowed = lv.shadow[(uint32_t)li * n_all + first[lv.level] + h] != 0;
+            const Rgb effective = color * intensity;
+            Rgb surface = effective * mat.ambient;
+            const double light_dot_normal = dot(lightv, normal);
+            if (!shadowed && light_dot_normal >= 0.0) {
+                const Rgb diffuse = effective * mat.diffuse * light_dot_normal;
+                Rgb specular = rgb(0.0, 0.0, 0.0);
+                const double reflect_dot_eye = dot(reflect(-lightv, normal), eye);
+                // intensity * 0 * powf(..) is +0 for any finite power: skip the pow when the material has no highlight
+                if (reflect_dot_eye > 0.0 && specular_k != 0.0) specular = intensity * specular_k * pow(reflect_dot_eye, shininess);
+                surface = surface + diffuse + specular;
+            } else {
+                surface = surface + rgb(0.0, 0.0, 0.0) + rgb(0.0, 0.0, 0.0);
             }
-            if (TRANSPARENT && push_refr) {
-                const uint64_t slot = base + (uint64_t)__popc(m_refl) + (uint64_t)__popc(m_refr & below);
-                if (slot < lv.out_capacity) {
-                    lv.out_q0[slot] = make_double2(r_refr.o.x, r_refr.o.y);
-                    lv.out_q1[slot] = make_double2(r_refr.o.z, r_refr.d.x);
-                    lv.out_q2[slot] = make_double2(r_refr.d.y, r_refr.d.z);
-                    lv.out_q3[slot] = make_double2(w_refr, __longlong_as_double((long long)packed_fuel));
-                } else *lv.overflow = 2;
-                c_refr++;
-            }
+            sum = sum + surface;
         }
-    }
-    for (int off = 16; off; off >>= 1) {
-        c_refl += __shfl_down_sync(0xffffffffu, c_refl, off);
-        c_refr += __shfl_down_sync(0xffffffffu, c_refr, off);
-    }
-    if (lane == 0) {
-        if (c_refl) atomicAdd(lv.stats + 1, (unsigned long long)c_refl);
-        if (c_refr) atomicAdd(lv.stats + 2, (unsigned long long)c_refr);
+        double* acc = lv.accum + 3 * (size_t)sample;
+        atomicAdd(acc + 0, sum.r * w);
+        atomicAdd(acc + 1, sum.g * w);
+        atomicAdd(acc + 2, sum.b * w);
     }
 }
 
@@ -390,42 +408,30 @@ __global__ void resolve_pixels(const FrameParams f, const double* __restrict__ a
 void upload_perm(const uint8_t* perm512) { cudaMemcpyToSymbol(c_perm, perm512, 512); }
 
 template <int FEAT>
-static void launch_trace_feat(bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    if (primary) trace_closest<FEAT, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    else trace_closest<FEAT, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
+static void launch_trace_feat(bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+    if (primary) trace_spawn<FEAT, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+    else trace_spawn<FEAT, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
 }
-void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    if (feat & (FEAT_CSG | FEAT_GATES)) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES>(primary, grid, st, sc, f, lv);
-    else if (feat & FEAT_TRANSPARENT) launch_trace_feat<FEAT_TRANSPARENT>(primary, grid, st, sc, f, lv);
-    else launch_trace_feat<0>(primary, grid, st, sc, f, lv);
+void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+    if (feat & (FEAT_CSG | FEAT_GATES)) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES>(primary, grid, st, sc, f, lv, hl);
+    else if (feat & FEAT_TRANSPARENT) launch_trace_feat<FEAT_TRANSPARENT>(primary, grid, st, sc, f, lv, hl);
+    else launch_trace_feat<0>(primary, grid, st, sc, f, lv, hl);
 }
 
-template <int FEAT, bool ANYHIT>
-static void launch_shadow_feat(bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    if (primary) trace_shadow<FEAT, true, ANYHIT><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    else trace_shadow<FEAT, false, ANYHIT><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-}
-void launch_shadow(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
+void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     if (sc.n_lights == 0) return;
     const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
     if (sc.all_cast_shadow) {
-        if (full) launch_shadow_feat<FEAT_CSG | FEAT_GATES, true>(primary, grid, st, sc, f, lv);
-        else launch_shadow_feat<0, true>(primary, grid, st, sc, f, lv);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<0, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     } else {
-        if (full) launch_shadow_feat<FEAT_CSG | FEAT_GATES, false>(primary, grid, st, sc, f, lv);
-        else launch_shadow_feat<0, false>(primary, grid, st, sc, f, lv);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<0, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     }
 }
 
-void launch_shade(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    const bool tr = (feat & FEAT_TRANSPARENT) != 0;
-    if (tr) {
-        if (primary) shade<true, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-        else shade<true, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    } else {
-        if (primary) shade<false, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-        else shade<false, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    }
+void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {
+    shade<<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
 }
 
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major) {

@@ -8,13 +8,21 @@
 #define RTC_BLOCK 128
 // resident blocks per SM the compiler must allow for (register cap = 65536 / (128 * blocks))
 #ifndef RTC_TRACE_MIN_BLOCKS
-#define RTC_TRACE_MIN_BLOCKS 5
+#define RTC_TRACE_MIN_BLOCKS 6
+#endif
+#ifndef RTC_SHADOW_MIN_BLOCKS
+#define RTC_SHADOW_MIN_BLOCKS 8
+#endif
+#ifndef RTC_TRACE_MIN_BLOCKS_TRANSPARENT  // the n1/n2 replay keeps more state alive: trade occupancy for no spills
+#define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 4
 #endif
 #ifndef RTC_SHADE_MIN_BLOCKS
-#define RTC_SHADE_MIN_BLOCKS 4
+#define RTC_SHADE_MIN_BLOCKS 5
 #endif
 
 namespace rtcdev {
+
+constexpr int MAX_LEVELS = 13;  // fuel <= 12
 
 // Per-frame constants (camera = the six values Camera::ray_at_pixel reads, src/camera.rs:39-55).
 struct FrameParams {
@@ -29,14 +37,23 @@ struct FrameParams {
     int32_t pad;
 };
 
-// One bounce level of one batch.  All arrays are structure-of-arrays of 16-byte chunks, so a warp's loads and
-// stores are fully coalesced 512-byte transactions.
+// Hit list of one batch: structure-of-arrays of 16-byte chunks (a warp's accesses are whole 512-byte lines), one
+// segment per bounce level at a static offset.  Everything the shadow and shading kernels need is in the record, so
+// neither of them gathers from the ray queue or recomputes the surface frame:
+//   a = (over_point.x, over_point.y)   b = (over_point.z, normal.x)   c = (normal.y, normal.z)
+//   d = (eye.x, eye.y)                 e = (eye.z, throughput)        f = (primitive | sample << 32, unused)
+struct HitList {
+    double2 *a, *b, *c, *d, *e, *f;
+    const unsigned long long* counts;  // hits per level (device counters)
+    uint32_t seg_off[MAX_LEVELS];      // first record of each level's segment
+    uint32_t seg_cap[MAX_LEVELS];
+    int32_t n_levels;
+    int32_t pad;
+};
+
+// One bounce level of one batch.
 //   ray queue (64 B per ray):  q0 = (origin.x, origin.y)  q1 = (origin.z, dir.x)  q2 = (dir.y, dir.z)
 //                              q3 = (throughput, fuel<<32 | sample)
-//   hit list (compacted: one entry per ray that hit something; 36 / 52 B per hit):
-//                              hit_ray = index of the ray in the level's input,  hit0 = (t, primitive index)
-//                              hit1 = (u, v)   hit2 = (n1, n2) [scenes with transparent materials only]
-//   shadow[li * n_hits + h]    1 = light li is occluded at hit h
 struct LevelParams {
     const double2 *in_q0, *in_q1, *in_q2, *in_q3;
     double2 *out_q0, *out_q1, *out_q2, *out_q3;
@@ -45,20 +62,20 @@ struct LevelParams {
     uint64_t in_capacity, out_capacity;
     uint64_t first_sample;  // primary level: first sample ordinal of this batch
     uint64_t n_primary;     // primary level: samples in this batch
-    uint32_t* hit_ray;
-    double2 *hit0, *hit1, *hit2;
-    unsigned long long* hit_count;
-    uint8_t* shadow;
+    int32_t level;
+    int32_t pad;
+    unsigned long long* hit_count;  // this level's counter (= hits.counts + level)
+    uint8_t* shadow;            // [light][all hits of the batch, level segments packed]: 1 = occluded
     double* accum;              // 3 doubles per sample of the batch
     unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms, [7] most node visits of one closest-hit query
     int* overflow;
 };
 
 void upload_perm(const uint8_t* perm512);
-// The three kernels of one level, in launch order.
-void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
-void launch_shadow(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
-void launch_shade(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+// Per batch: trace_spawn once per level (a chain), then ONE shadow launch over every hit of the batch, then shade per level.
+void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
+void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
+void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hits);
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major);
 
 }  // namespace rtcdev

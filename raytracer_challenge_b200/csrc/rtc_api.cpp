@@ -54,12 +54,10 @@ struct Pipe {
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     double2* q[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
-    uint32_t* hit_ray = nullptr;
-    double2* hit[3] = {nullptr, nullptr, nullptr};
+    double2* hit[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint8_t* shadow = nullptr;
     double* accum = nullptr;
-    uint64_t q_capacity = 0, shadow_bytes = 0, accum_samples = 0;
-    bool hit2 = false;
+    uint64_t q_capacity = 0, hit_capacity = 0, shadow_bytes = 0, accum_samples = 0;
 };
 
 // Per-device render context: streams, events and scratch memory.  It outlives scenes, so that the drop-in call
@@ -87,12 +85,10 @@ DeviceCtx g_ctx[MAX_DEVICES];
 void free_pipe(Pipe& p) {
     for (int a = 0; a < 2; ++a)
         for (int b = 0; b < 4; ++b) { cudaFree(p.q[a][b]); p.q[a][b] = nullptr; }
-    cudaFree(p.hit_ray); p.hit_ray = nullptr;
     for (auto& h : p.hit) { cudaFree(h); h = nullptr; }
     cudaFree(p.shadow); p.shadow = nullptr;
     cudaFree(p.accum); p.accum = nullptr;
-    p.q_capacity = p.shadow_bytes = p.accum_samples = 0;
-    p.hit2 = false;
+    p.q_capacity = p.hit_capacity = p.shadow_bytes = p.accum_samples = 0;
 }
 
 int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the device
@@ -361,19 +357,22 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     return 0;
 }
 
-static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t shadow_bytes, uint64_t accum_samples, bool hit2) {
-    if (q_capacity > p.q_capacity || (hit2 && !p.hit2)) {
-        const uint64_t acc = p.accum_samples, sh = p.shadow_bytes;
-        double* keep_accum = p.accum; uint8_t* keep_shadow = p.shadow;
-        p.accum = nullptr; p.shadow = nullptr;
-        free_pipe(p);
-        p.accum = keep_accum; p.accum_samples = acc; p.shadow = keep_shadow; p.shadow_bytes = sh;
+static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t shadow_bytes, uint64_t accum_samples) {
+    if (q_capacity > p.q_capacity) {
+        for (int a = 0; a < 2; ++a)
+            for (int c = 0; c < 4; ++c) {
+                cudaFree(p.q[a][c]); p.q[a][c] = nullptr;
+            }
+        p.q_capacity = 0;
         for (int a = 0; a < 2; ++a)
             for (int c = 0; c < 4; ++c) CU(cudaMalloc((void**)&p.q[a][c], q_capacity * sizeof(double2)));
-        CU(cudaMalloc((void**)&p.hit_ray, q_capacity * sizeof(uint32_t)));
-        for (int c = 0; c < (hit2 ? 3 : 2); ++c) CU(cudaMalloc((void**)&p.hit[c], q_capacity * sizeof(double2)));
         p.q_capacity = q_capacity;
-        p.hit2 = hit2;
+    }
+    if (hit_capacity > p.hit_capacity) {
+        for (auto& h : p.hit) { cudaFree(h); h = nullptr; }
+        p.hit_capacity = 0;
+        for (auto& h : p.hit) CU(cudaMalloc((void**)&h, hit_capacity * sizeof(double2)));
+        p.hit_capacity = hit_capacity;
     }
     if (shadow_bytes > p.shadow_bytes) {
         cudaFree(p.shadow); p.shadow = nullptr; p.shadow_bytes = 0;
@@ -460,13 +459,22 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     batch_pixels = std::min(batch_pixels, std::max<uint64_t>((n_slots + unit - 1) / unit, 1) * unit);
     batch_samples = batch_pixels * f.spp;
     const uint64_t q_cap = batch_samples * worst;
-    if (q_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
+    // hit list: one segment per level, sized for that level's worst case (fan^level rays per sample)
+    rtcdev::HitList hits{};
+    uint64_t hit_cap = 0, level_cap = batch_samples;
+    hits.n_levels = o.fuel + 1;
+    for (int k = 0; k <= o.fuel; ++k) {
+        hits.seg_off[k] = (uint32_t)hit_cap;
+        hits.seg_cap[k] = (uint32_t)level_cap;
+        hit_cap += level_cap;
+        if (fan == 2) level_cap *= 2;
+    }
+    if (hit_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
     const uint64_t n_batches = std::max<uint64_t>((n_slots + batch_pixels - 1) / batch_pixels, 1);
     const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
     const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
-    const bool hit2 = (s->feat & rtcdev::FEAT_TRANSPARENT) != 0;
     for (int p = 0; p < n_pipes; ++p)
-        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, q_cap * (uint64_t)std::max(L, 1), batch_samples, hit2)) return rc;
+        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
     if (n_out > ctx.out_pixels) {
         cudaFree(ctx.out); ctx.out = nullptr; ctx.out_pixels = 0;
         CU(cudaMalloc((void**)&ctx.out, std::max<uint64_t>(n_out, 1) * 3 * sizeof(double)));
@@ -510,7 +518,9 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         if (!npix) break;
         unsigned long long* cnt = ctx.counters + b * COUNTERS_PER_BATCH;
         CU(cudaMemsetAsync(p.accum, 0, npix * f.spp * 3 * sizeof(double), st));
-        for (int level = 0; level <= o.fuel; ++level) {
+        hits.a = p.hit[0]; hits.b = p.hit[1]; hits.c = p.hit[2]; hits.d = p.hit[3]; hits.e = p.hit[4]; hits.f = p.hit[5];
+        hits.counts = cnt + 16;
+        auto level_params = [&](int level) {
             rtcdev::LevelParams lv{};
             const int in = level & 1, outq = in ^ 1;
             lv.in_q0 = p.q[in][0]; lv.in_q1 = p.q[in][1]; lv.in_q2 = p.q[in][2]; lv.in_q3 = p.q[in][3];
@@ -521,24 +531,25 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
             lv.out_capacity = p.q_capacity;
             lv.first_sample = first * f.spp;
             lv.n_primary = npix * f.spp;
-            lv.hit_ray = p.hit_ray;
-            lv.hit0 = p.hit[0]; lv.hit1 = p.hit[1]; lv.hit2 = p.hit[2];
+            lv.level = level;
             lv.hit_count = cnt + 16 + level;
             lv.shadow = p.shadow;
             lv.accum = p.accum;
             lv.stats = cnt + 32;
             lv.overflow = ctx.overflow;
-            int grid = grid_full;
-            if (level == 0) grid = (int)std::min<uint64_t>((uint64_t)grid_full, (lv.n_primary + RTC_BLOCK - 1) / RTC_BLOCK);
-            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(-1); }
-            rtcdev::launch_trace(s->feat, level == 0, grid, st, s->dev, f, lv);
-            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
-            rtcdev::launch_shadow(s->feat, level == 0, grid_full, st, s->dev, f, lv);
-            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
-            rtcdev::launch_shade(s->feat, level == 0, grid, st, s->dev, f, lv);
-            if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
-            launches += L > 0 ? 3 : 2;
-        }
+            return lv;
+        };
+        const int grid0 = (int)std::min<uint64_t>((uint64_t)grid_full, (npix * f.spp + RTC_BLOCK - 1) / RTC_BLOCK);
+        if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(-1); }
+        for (int level = 0; level <= o.fuel; ++level)  // the chain: level k+1 depends on level k only
+            rtcdev::launch_trace(s->feat, level == 0, level == 0 ? grid0 : grid_full, st, s->dev, f, level_params(level), hits);
+        if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
+        rtcdev::launch_shadow(s->feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
+        if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
+        for (int level = 0; level <= o.fuel; ++level)  // in level order: a sample's terms are added in a fixed order
+            rtcdev::launch_shade(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
+        if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
+        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0);
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
         launches++;
         if (host_out) {  // this batch's pixels are final: copy them out while the other pipelines keep tracing

@@ -4,5 +4,5 @@ python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu.log 2>&1; echo "pyte
 python tools/perf_probe.py "$@" > gpurun_out/probe.jsonl 2> gpurun_out/probe.err; echo "probe rc=$?"; python -c "
 import json
 for l in open('gpurun_out/probe.jsonl'):
-    d=json.loads(l); print(d.get('scene'), d.get('res'), d.get('ms_kernels'), d.get('mrays_s'), d.get('launches'), d.get('e2e_ms_total'))
+    d=json.loads(l); print(d.get('scene'), d.get('res'), d.get('ms_kernels'), d.get('mrays_s'), d.get('launches'), d.get('serial_ms'), d.get('hits'), d.get('rays'))
 "; tail -5 gpurun_out/probe.err

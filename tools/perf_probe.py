@@ -20,8 +20,10 @@ for c in cases:
         _, n, st = s.render_device(R.Opts())
         if best is None or st.ms_kernels < best.ms_kernels:
             best = st
+    _, _, pr = s.render_device(R.Opts(flags=R.FLAG_PROFILE))
+    _, _, pr = s.render_device(R.Opts(flags=R.FLAG_PROFILE))
     out, st2 = s.render(R.Opts())
     print(json.dumps({"scene": name, "res": res, "open_s": round(t_open, 3), "ms_kernels": round(best.ms_kernels, 3), "rays": best.rays,
                       "mrays_s": round(best.rays / best.ms_kernels / 1e3, 1), "rays_ref": best.rays_ref, "launches": best.kernel_launches,
-                      "e2e_ms_total": round(st2.ms_total, 2), "d2h_ms": round(st2.ms_d2h, 2), "build": s.build_stats}))
+                      "serial_ms": {"trace": round(pr.ms_trace, 3), "shadow": round(pr.ms_shadow, 3), "shade": round(pr.ms_shade, 3)}, "hits": best.surface_hits, "e2e_ms_total": round(st2.ms_total, 2), "d2h_ms": round(st2.ms_d2h, 2), "build": s.build_stats}))
     s.close()
