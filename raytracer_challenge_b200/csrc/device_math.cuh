@@ -231,20 +231,44 @@ __device__ __forceinline__ const Ray& object_ray(const Scene& sc, const Ray& wor
 // seven intersectors with their f64 divisions and square roots are ~2 000 instructions, and every kernel that can
 // meet an arbitrary primitive shares this one copy (the hot kinds are inlined at their call sites instead).
 // tri_rec: the primitive's (p1, e1, e2) record if it is a triangle.
-__device__ __noinline__ void roots_generic(const Scene& sc, int kind_flags, int geom, const double* __restrict__ tri_rec, const Ray& r, Roots& out) {
+//
+// The out-of-line body only sees COPIES (roots_generic below): a pointer into the caller's query state handed to a
+// real call would pin that state — the cached object ray, the tallies, the whole visitor and through it the scene
+// descriptor — in local memory for the entire kernel (r01d: 4x more local than global requests in the walk).
+struct GenericCall {
+    Ray r;
+    Roots out;
+};
+__device__ __noinline__ void roots_generic_body(const double* __restrict__ ranges, int kind_flags, int geom, const double* __restrict__ tri_rec, GenericCall* c) {
     const int kind = kind_flags & 0xff;
+    const Ray r = c->r;
+    Roots out;
+    out.n = 0;
+    out.u = 0.0;
+    out.v = 0.0;
     switch (kind) {
         case 0: isect_sphere(r, out); break;
         case 1: isect_plane(r, out); break;
         case 2: isect_cube(r, out); break;
-        case 3: isect_cylinder(r, __ldg(sc.ranges + 2 * geom), __ldg(sc.ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
-        case 4: isect_cone(r, __ldg(sc.ranges + 2 * geom), __ldg(sc.ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
+        case 3: isect_cylinder(r, __ldg(ranges + 2 * geom), __ldg(ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
+        case 4: isect_cone(r, __ldg(ranges + 2 * geom), __ldg(ranges + 2 * geom + 1), (kind_flags & 0x200) != 0, out); break;
         default: {
             V3 p1, e1, e2;
             load_tri(tri_rec, p1, e1, e2);
             isect_triangle(r, p1, e1, e2, out);
         }
     }
+    c->out = out;
+}
+__device__ __forceinline__ void roots_generic(const Scene& sc, int kind_flags, int geom, const double* __restrict__ tri_rec, const Ray& r, Roots& out) {
+    GenericCall c;
+    c.r = r;
+    roots_generic_body(sc.ranges, kind_flags, geom, tri_rec, &c);
+    out.n = c.out.n;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) out.t[k] = c.out.t[k];
+    out.u = c.out.u;
+    out.v = c.out.v;
 }
 
 // A plane only reads the y components of the object-space ray (src/shape.rs:622-633), i.e. row 1 of the transform:

@@ -71,6 +71,11 @@ struct Query {
         : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), overflow(ovf), skip_negative(skip_neg) {
         cache.xform = -1;
     }
+    // copy of a query for an out-of-line evaluation: the gates are already known
+    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg, uint32_t passed_gates)
+        : sc(s), ray(r), passed(passed_gates), tally(tl), overflow(ovf), skip_negative(skip_neg) {
+        cache.xform = -1;
+    }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
         if (!(FEAT & FEAT_GATES)) return true;
         return (__ldg(&sc.prims[prim_id].gate_mask) & ~passed) == 0u;
@@ -93,7 +98,7 @@ struct Query {
 // Group::intersect for a CSG subtree (src/shape.rs:230-269): gather, stable-sort by t, filter, recursively.
 // Returns the number of surviving crossings in `list` (sorted by t), or -1 on overflow.
 template <int FEAT>
-__device__ __noinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cross* list) {
+__device__ __forceinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cross* list) {
     int marks[MAX_CSG_MARKS];
     int nm = 0, n = 0;
     for (int k = 0; k < root.n_ops; ++k) {
@@ -125,6 +130,34 @@ __device__ __noinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cross*
         }
     }
     return n;
+}
+
+// Out-of-line evaluation of one CSG item.  It works on COPIES of the query state (see roots_generic in
+// device_math.cuh: a pointer into the caller's state handed to a real call would pin that state in local memory).
+struct CsgCall {
+    Ray ray;
+    uint32_t passed;
+    int skip_negative;
+    Tally tally;
+    int n;  // surviving crossings in `list`, sorted by t; -1 = overflow
+    Cross list[MAX_CSG_LIST];
+};
+template <int FEAT>
+__device__ __noinline__ void csg_call_body(const Scene& sc, int root, int* overflow, CsgCall* c) {
+    const Ray ray = c->ray;
+    Tally t = {0u, 0u, 0u, 0u};
+    Query<FEAT> q(sc, ray, t, overflow, c->skip_negative != 0, c->passed);
+    c->n = csg_eval<FEAT>(q, sc.csg_roots[root], c->list);
+    c->tally = t;
+}
+template <int FEAT>
+__device__ __forceinline__ void csg_call(Query<FEAT>& q, int root, CsgCall& c) {
+    c.ray = q.ray;
+    c.passed = q.passed;
+    c.skip_negative = q.skip_negative ? 1 : 0;
+    csg_call_body<FEAT>(q.sc, root, q.overflow, &c);
+    q.tally.nodes += c.tally.nodes; q.tally.tris += c.tally.tris; q.tally.prims += c.tally.prims; q.tally.xforms += c.tally.xforms;
+    if (c.n < 0) *q.overflow = 1;
 }
 
 // ---- fp32 BVH walk ---------------------------------------------------------------------------
@@ -248,10 +281,12 @@ struct ClosestVisitor {
     __device__ __forceinline__ void offer_roots(const Roots& r, int id) {
         for (int k = 0; k < r.n; ++k) offer(r.t[k], id, r.u, r.v);
     }
-    __device__ __noinline__ bool csg(int root) {
-        Cross list[MAX_CSG_LIST];
-        const int n = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
-        if (n < 0) { *q.overflow = 1; return true; }
+    __device__ __forceinline__ bool csg(int root) {
+        CsgCall c;
+        csg_call<FEAT>(q, root, c);
+        const int n = c.n;
+        const Cross* list = c.list;
+        if (n < 0) return true;
         for (int k = 0; k < n; ++k)
             if (list[k].t >= 0.0) {  // list is sorted: the first non-negative entry is this item's hit
                 double u = 0.0, v = 0.0;
@@ -304,12 +339,12 @@ struct AnyVisitor {
             if (r.t[k] >= 0.0 && r.t[k] < dist) { found = true; return true; }
         return false;
     }
-    __device__ __noinline__ bool csg(int root) {
-        Cross list[MAX_CSG_LIST];
-        const int n = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
-        if (n < 0) { *q.overflow = 1; return true; }
-        for (int k = 0; k < n; ++k)
-            if (list[k].t >= 0.0 && list[k].t < dist) { found = true; return true; }
+    __device__ __forceinline__ bool csg(int root) {
+        CsgCall c;
+        csg_call<FEAT>(q, root, c);
+        if (c.n < 0) return true;
+        for (int k = 0; k < c.n; ++k)
+            if (c.list[k].t >= 0.0 && c.list[k].t < dist) { found = true; return true; }
         return false;
     }
     __device__ __forceinline__ bool item(int id) {
@@ -359,12 +394,12 @@ struct CollectVisitor {
             if (push(r.t[k], id)) return true;
         return false;
     }
-    __device__ __noinline__ bool csg(int root) {
-        Cross list[MAX_CSG_LIST];
-        const int m = csg_eval<FEAT>(q, q.sc.csg_roots[root], list);
-        if (m < 0) { *q.overflow = 1; return true; }
-        for (int k = 0; k < m; ++k)
-            if (push(list[k].t, list[k].prim)) return true;
+    __device__ __forceinline__ bool csg(int root) {
+        CsgCall c;
+        csg_call<FEAT>(q, root, c);
+        if (c.n < 0) return true;
+        for (int k = 0; k < c.n; ++k)
+            if (push(c.list[k].t, c.list[k].prim)) return true;
         return false;
     }
     __device__ __forceinline__ bool item(int id) {
@@ -382,8 +417,16 @@ struct CollectVisitor {
     }
 };
 
+struct IndexCall {
+    Ray ray;
+    double n1, n2;
+    Tally tally;
+};
 template <int FEAT>
-__device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray, double hit_t, int hit_prim, bool brute, double& n1, double& n2, Tally& tally, int* overflow) {
+__device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit_t, int hit_prim, bool brute, int* overflow, IndexCall* call) {
+    const Ray ray = call->ray;
+    Tally tally = {0u, 0u, 0u, 0u};
+    double n1, n2;
     Cross xs[MAX_CROSSINGS];
     CollectVisitor<FEAT> v(sc, ray, hit_t, xs, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
@@ -409,11 +452,24 @@ __device__ __noinline__ void refractive_indices(const Scene& sc, const Ray& ray,
             for (int k = at; k + 1 < no; ++k) open[k] = open[k + 1];
             no--;
         } else {
-            if (no >= MAX_CONTAINERS) { *overflow = 1; return; }
+            if (no >= MAX_CONTAINERS) { *overflow = 1; break; }
             open[no++] = xs[i].prim;
         }
         if (is_hit) n2 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
     }
+    call->n1 = n1;
+    call->n2 = n2;
+    call->tally = tally;
+}
+// Out of line, over copies of the ray and the tallies (see roots_generic in device_math.cuh).
+template <int FEAT>
+__device__ __forceinline__ void refractive_indices(const Scene& sc, const Ray& ray, double hit_t, int hit_prim, bool brute, double& n1, double& n2, Tally& tally, int* overflow) {
+    IndexCall c;
+    c.ray = ray;
+    refractive_indices_body<FEAT>(sc, hit_t, hit_prim, brute, overflow, &c);
+    n1 = c.n1;
+    n2 = c.n2;
+    tally.nodes += c.tally.nodes; tally.tris += c.tally.tris; tally.prims += c.tally.prims; tally.xforms += c.tally.xforms;
 }
 
 }  // namespace rtcdev
