@@ -14,7 +14,7 @@
 #define RTC_SHADOW_MIN_BLOCKS 8
 #endif
 #ifndef RTC_TRACE_MIN_BLOCKS_TRANSPARENT  // the n1/n2 replay keeps more state alive: trade occupancy for no spills
-#define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 4
+#define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 3
 #endif
 #ifndef RTC_SHADE_MIN_BLOCKS
 #define RTC_SHADE_MIN_BLOCKS 5

@@ -44,14 +44,15 @@ const uint8_t kPerm[256] = {
     81,  51,  145, 235, 249, 14,  239, 107, 49,  192, 214, 31,  181, 199, 106, 157, 184, 84,  204, 176, 115, 121, 50,  45,  127, 4,
     150, 254, 138, 236, 205, 93,  222, 114, 67,  29,  24,  72,  243, 141, 128, 195, 78,  66,  215, 61,  156, 180};
 
-constexpr int MAX_PIPES = 4;
+constexpr int MAX_PIPES = 8;
 constexpr int MAX_DEVICES = 64;
 constexpr int COUNTERS_PER_BATCH = 64;  // [0..15] queue counts per level, [16..31] hit counts per level, [32..34] stats
 
 // Scratch of one pipeline (= one CUDA stream working through batches): ray queues (ping-pong), hit list, shadow
 // bytes, sample accumulators.
 struct Pipe {
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;  // the one in use by the current render: stream_flat or stream_staggered
+    cudaStream_t stream_flat = nullptr, stream_staggered = nullptr;
     cudaEvent_t done = nullptr;
     double2* q[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     double2* hit[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -91,15 +92,27 @@ void free_pipe(Pipe& p) {
     p.q_capacity = p.hit_capacity = p.shadow_bytes = p.accum_samples = 0;
 }
 
+int env_int(const char* name, int fallback, int lo, int hi);
+
 int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the device
     if (c.ready) return 0;
     c.device = device;
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     c.sm_count = prop.multiProcessorCount;
+    // Two streams per pipeline.  Renders that leave the frame in HBM use equal priorities: the batches share the SMs
+    // evenly and finish together, which is the fastest way through the kernels.  Renders that copy each finished
+    // batch to the host use descending priorities: batch 0 is then done (and on its way over PCIe) while the other
+    // pipelines are still tracing, instead of every copy queueing up behind the last kernel.
+    int prio_least = 0, prio_greatest = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));  // numerically lower = higher priority
+    int pipe_index = 0;
     for (Pipe& p : c.pipe) {
-        CU(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithPriority(&p.stream_flat, cudaStreamNonBlocking, prio_least));
+        CU(cudaStreamCreateWithPriority(&p.stream_staggered, cudaStreamNonBlocking, std::min(prio_least, prio_greatest + pipe_index)));
+        p.stream = p.stream_flat;
         CU(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
+        pipe_index++;
     }
     for (auto& e : c.ev) CU(cudaEventCreate(&e));
     CU(cudaMalloc((void**)&c.overflow, sizeof(int)));
@@ -449,9 +462,10 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     uint64_t worst = 1;
     for (int k = 0; k < o.fuel && fan == 2; ++k) worst *= 2;
     const uint64_t unit = row_major ? (uint64_t)f.tiles_x * per_tile : per_tile;  // batch granularity in pixel slots
-    // default: about RTC_BATCHES (4) batches per call so the pipelines have something to overlap, within [256 Ki, 2 Mi]
-    // samples (measured: more, smaller batches only add launches; fewer leave the deep levels' tails exposed)
-    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)env_int("RTC_BATCHES", 4, 1, 1024), 256u << 10), 2u << 20);
+    // default: about RTC_BATCHES batches per call so the pipelines have something to overlap, within [256 Ki, 2 Mi]
+    // samples (measured: more, smaller batches only add launches; fewer leave the deep levels' tails exposed).
+    // 4 when the frame stays in HBM; 6 when each finished batch is copied out, so that the copies start earlier.
+    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)env_int("RTC_BATCHES", host_out ? 6 : 4, 1, 1024), 256u << 10), 2u << 20);
     const uint64_t target_samples = (uint64_t)env_int("RTC_BATCH_SAMPLES", (int)auto_samples, 1024, 1 << 28);
     const uint64_t max_records = (uint64_t)24 << 20;  // records per queue
     uint64_t batch_samples = std::min(target_samples, std::max<uint64_t>(max_records / worst, 1));
@@ -490,6 +504,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         ctx.counter_batches = nb;
     }
 
+    const bool staggered = host_out != nullptr && env_int("RTC_STREAM_PRIORITIES", 1, 0, 1) != 0;
+    for (Pipe& p : ctx.pipe) p.stream = staggered ? p.stream_staggered : p.stream_flat;
     cudaStream_t st0 = ctx.pipe[0].stream;
     const size_t counter_bytes = n_batches * COUNTERS_PER_BATCH * sizeof(unsigned long long);
     CU(cudaMemsetAsync(ctx.counters, 0, counter_bytes, st0));
@@ -498,6 +514,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
     uint64_t launches = 0;
+    const bool timeline = std::getenv("RTC_TIMELINE") != nullptr;  // debugging aid: when each batch's kernels / copy finished
+    std::vector<cudaEvent_t> tl_events;
     size_t n_prof = 0;  // profile mode: event k is recorded after launch k-1 (classes cycle trace, shadow, shade)
     auto prof_mark = [&](cudaStream_t st) -> int {
         if (!profile) return 0;
@@ -552,6 +570,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0);
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
         launches++;
+        if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, st)); tl_events.push_back(e); }
         if (host_out) {  // this batch's pixels are final: copy them out while the other pipelines keep tracing
             uint64_t off_px, len_px;
             if (row_major) {
@@ -583,6 +602,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
                 len_px = npix;
             }
             if (len_px) CU(cudaMemcpyAsync(host_out + 3 * off_px, ctx.out + 3 * off_px, len_px * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, st)); tl_events.push_back(e); }
         }
     }
     CU(cudaGetLastError());
@@ -598,6 +618,16 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx.ev[0], ctx.ev[1]));
     const int overflow = *h_overflow;
+    if (timeline) {
+        std::fprintf(stderr, "rtc_render timeline (ms after start; per batch: kernels done%s):", host_out ? ", copy done" : "");
+        for (cudaEvent_t e : tl_events) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, ctx.ev[0], e);
+            std::fprintf(stderr, " %.2f", t);
+            cudaEventDestroy(e);
+        }
+        std::fprintf(stderr, " | all %.2f\n", ms);
+    }
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
         // R_ref: the reference re-traces every secondary sub-tree once per light, so a ray at

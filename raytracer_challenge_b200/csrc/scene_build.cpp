@@ -1,9 +1,13 @@
 #include "scene_build.hpp"
 
+#include <emmintrin.h>
+
 #include <algorithm>
 #include <atomic>
 #include <thread>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <functional>
@@ -115,120 +119,69 @@ float f32_up(double x) {
 }
 
 // ---- binned-SAH BVH2 over item boxes ------------------------------------------------------
+// The build runs on the boxes the device will test: per item the fp32 box, padded and rounded outwards.  Rounding
+// outwards is monotone, so the union of the rounded item boxes IS the rounded union — a node's stored box is the
+// plain min / max of its items' boxes, and the whole build is four-wide SSE min / max (baseline x86-64, no -march).
 struct Builder {
-    struct Item {  // box + centroid of one BVH item, kept in leaf order (partitioned in place: sequential passes)
-        Box box;
-        double c[3];
-        int32_t index;
+    struct alignas(16) Item {  // kept in leaf order (partitioned in place: sequential passes)
+        __m128 lo, hi;  // lanes x, y, z; lane w unused
+        __m128 c;       // centroid; lane w carries the item's index (bit pattern)
+    };
+    struct Bounds {
+        __m128 lo, hi;
+        void reset() { lo = _mm_set1_ps(std::numeric_limits<float>::infinity()); hi = _mm_set1_ps(-std::numeric_limits<float>::infinity()); }
+        void add(__m128 l, __m128 h) { lo = _mm_min_ps(lo, l); hi = _mm_max_ps(hi, h); }
+        void add(const Bounds& b) { add(b.lo, b.hi); }
+        float area() const {
+            alignas(16) float d[4];
+            _mm_store_ps(d, _mm_sub_ps(hi, lo));
+            return 2.0f * (d[0] * d[1] + d[1] * d[2] + d[2] * d[0]);
+        }
     };
     std::vector<Item> items;
     std::vector<BvhNode> nodes;  // build(): slot mid - 1 of the node that splits at `mid` (sparse); compact(): final
-    double pad;
-    double leaf_weight = 3.0;  // cost of one exact f64 primitive test relative to one fp32 node visit
+    float leaf_weight = 3.0f;    // cost of one exact f64 primitive test relative to one fp32 node visit
+    int fork_levels = 4;         // the top levels of the tree fork a thread per left subtree (RTC_BUILD_FORK_LEVELS, 0 = sequential)
     std::atomic<int> depth{0};
-    Builder(const std::vector<Box>& boxes, double pad_) : pad(pad_) {
-        if (const char* w = std::getenv("RTC_LEAF_WEIGHT")) leaf_weight = std::max(0.1, std::atof(w));
+
+    Builder(const std::vector<Box>& boxes, double pad) {
+        if (const char* w = std::getenv("RTC_LEAF_WEIGHT")) leaf_weight = (float)std::max(0.1, std::atof(w));
+        if (const char* w = std::getenv("RTC_BUILD_FORK_LEVELS")) fork_levels = std::min(8, std::max(0, std::atoi(w)));
         items.resize(boxes.size());
         for (size_t i = 0; i < boxes.size(); ++i) {
-            Item& it = items[i];
-            it.box = boxes[i];
-            for (int k = 0; k < 3; ++k) it.c[k] = 0.5 * (it.box.lo[k] + it.box.hi[k]);
-            it.index = (int32_t)i;
+            alignas(16) float lo[4] = {0.f, 0.f, 0.f, 0.f}, hi[4] = {0.f, 0.f, 0.f, 0.f}, c[4];
+            for (int k = 0; k < 3; ++k) {
+                lo[k] = f32_down(boxes[i].lo[k] - pad);
+                hi[k] = f32_up(boxes[i].hi[k] + pad);
+                c[k] = 0.5f * lo[k] + 0.5f * hi[k];
+            }
+            const int32_t index = (int32_t)i;
+            std::memcpy(&c[3], &index, 4);
+            items[i].lo = _mm_load_ps(lo);
+            items[i].hi = _mm_load_ps(hi);
+            items[i].c = _mm_load_ps(c);
         }
         nodes.resize(boxes.size());
     }
-
-    static double area(const Box& b) {
-        if (b.empty()) return 0.0;
-        const double dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
-        return 2.0 * (dx * dy + dy * dz + dz * dx);
+    int32_t index_of(size_t slot) const {
+        alignas(16) float c[4];
+        _mm_store_ps(c, items[slot].c);
+        int32_t index;
+        std::memcpy(&index, &c[3], 4);
+        return index;
     }
-    Box range_box(int begin, int end) const {
-        Box b;
-        for (int i = begin; i < end; ++i) b.add(items[(size_t)i].box);
+    Bounds range_bounds(int begin, int end) const {
+        Bounds b;
+        b.reset();
+        for (int i = begin; i < end; ++i) b.add(items[(size_t)i].lo, items[(size_t)i].hi);
         return b;
-    }
-    void store_box(float lo[3], float hi[3], const Box& b) const {
-        for (int k = 0; k < 3; ++k) { lo[k] = f32_down(b.lo[k] - pad); hi[k] = f32_up(b.hi[k] + pad); }
     }
     static int32_t leaf_link(int begin, int count) { return ~((begin << 2) | (count - 1)); }
 
-    // Binned-SAH split of items [begin, end) whose union is `whole`; returns the link for the range.
-    // Subtrees over disjoint item ranges are independent, so the top levels fork threads.  A node's slot is derived
-    // from its split position (unique per inner node), which makes the result independent of thread timing;
-    // compact() then renumbers the nodes in depth-first order, the layout a sequential build would produce.
-    int32_t build(int begin, int end, int level, const Box& whole) {
-        for (int seen = depth.load(); level > seen && !depth.compare_exchange_weak(seen, level);) {}
-        const int n = end - begin;
-        if (n <= 1) return leaf_link(begin, n);
-        const int NB = std::min(16, std::max(4, n));  // few items: few bins (the per-node fixed cost is what small nodes pay)
-        Box cb;  // centroid bounds: the split candidates
-        for (int i = begin; i < end; ++i) cb.add(items[(size_t)i].c);
-        double ext[3], scale[3];
-        for (int a = 0; a < 3; ++a) {
-            ext[a] = cb.hi[a] - cb.lo[a];
-            scale[a] = ext[a] > 0.0 ? (double)NB / ext[a] : 0.0;
-        }
-        auto bin_of = [&](const Item& it, int a) {
-            const int k = (int)((it.c[a] - cb.lo[a]) * scale[a]);
-            return std::min(std::max(k, 0), NB - 1);
-        };
-        Box bin_box[3][16];
-        int bin_n[3][16] = {};
-        for (int i = begin; i < end; ++i) {  // one pass fills the bins of all three axes
-            const Item& it = items[(size_t)i];
-            for (int a = 0; a < 3; ++a) {
-                if (!(ext[a] > 0.0)) continue;
-                const int k = bin_of(it, a);
-                bin_box[a][k].add(it.box);
-                bin_n[a][k]++;
-            }
-        }
-        double best_cost = INF;
-        int best_axis = -1, best_bin = -1;
-        Box best_left, best_right;
-        for (int a = 0; a < 3; ++a) {
-            if (!(ext[a] > 0.0)) continue;
-            Box right_box[16];
-            int right_n[16];
-            Box acc;
-            int cnt = 0;
-            for (int k = NB - 1; k > 0; --k) {
-                acc.add(bin_box[a][k]);
-                cnt += bin_n[a][k];
-                right_box[k] = acc;
-                right_n[k] = cnt;
-            }
-            Box left;
-            int ln = 0;
-            for (int k = 0; k < NB - 1; ++k) {
-                left.add(bin_box[a][k]);
-                ln += bin_n[a][k];
-                if (ln == 0 || right_n[k + 1] == 0) continue;
-                const double cost = area(left) * ln + area(right_box[k + 1]) * right_n[k + 1];
-                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; best_left = left; best_right = right_box[k + 1]; }
-            }
-        }
-        int mid;
-        Box lb, rb;
-        if (best_axis < 0) {
-            if (n <= 4) return leaf_link(begin, n);
-            mid = begin + n / 2;  // identical centroids: split by index
-            lb = range_box(begin, mid);
-            rb = range_box(mid, end);
-        } else {
-            // leaf cost: every item test is an f64 primitive intersection (expensive) -> weight 3 vs 1 per node
-            const double leaf_cost = leaf_weight * n;
-            const double split_cost = 1.0 + leaf_weight * best_cost / std::max(area(whole), 1e-300);
-            if (n <= 4 && leaf_cost <= split_cost) return leaf_link(begin, n);
-            auto it = std::partition(items.begin() + begin, items.begin() + end, [&](const Item& x) { return bin_of(x, best_axis) <= best_bin; });
-            mid = (int)(it - items.begin());
-            lb = best_left;
-            rb = best_right;
-        }
+    int32_t finish(int begin, int mid, int end, int level, const Bounds& lb, const Bounds& rb) {
         const int32_t self = mid - 1;
         int32_t l, r;
-        if (level < 4 && n >= 1024) {
+        if (level < fork_levels && end - begin >= 1024) {
             std::thread left([&] { l = build(begin, mid, level + 1, lb); });
             r = build(mid, end, level + 1, rb);
             left.join();
@@ -238,16 +191,160 @@ struct Builder {
         }
         BvhNode& nd = nodes[(size_t)self];
         std::memset(&nd, 0, sizeof nd);
-        store_box(nd.lo0, nd.hi0, lb);
-        store_box(nd.lo1, nd.hi1, rb);
+        alignas(16) float v[4];
+        _mm_store_ps(v, lb.lo); for (int k = 0; k < 3; ++k) nd.lo0[k] = v[k];
+        _mm_store_ps(v, lb.hi); for (int k = 0; k < 3; ++k) nd.hi0[k] = v[k];
+        _mm_store_ps(v, rb.lo); for (int k = 0; k < 3; ++k) nd.lo1[k] = v[k];
+        _mm_store_ps(v, rb.hi); for (int k = 0; k < 3; ++k) nd.hi1[k] = v[k];
         nd.c0 = l;
         nd.c1 = r;
         return self;
+    }
+
+    // 2..8 items: every split of the items sorted by centroid, per axis (no bins: the fixed cost of 48 bins is what
+    // the thousands of small nodes at the bottom of the tree would pay).
+    int32_t build_small(int begin, int end, int level, const Bounds& whole) {
+        const int n = end - begin;
+        float best_cost = std::numeric_limits<float>::infinity();
+        int best_split = -1;
+        int best_order[8];
+        Bounds best_left, best_right;
+        alignas(16) float cen[8][4];
+        for (int i = 0; i < n; ++i) _mm_store_ps(cen[i], items[(size_t)(begin + i)].c);
+        for (int a = 0; a < 3; ++a) {
+            int order[8];
+            for (int i = 0; i < n; ++i) {  // stable insertion sort by centroid
+                int j = i;
+                while (j > 0 && cen[order[j - 1]][a] > cen[i][a]) { order[j] = order[j - 1]; --j; }
+                order[j] = i;
+            }
+            if (!(cen[order[0]][a] < cen[order[n - 1]][a])) continue;  // no extent along this axis
+            Bounds suffix[8];
+            Bounds acc;
+            acc.reset();
+            for (int i = n - 1; i > 0; --i) {
+                const Item& it = items[(size_t)(begin + order[i])];
+                acc.add(it.lo, it.hi);
+                suffix[i] = acc;
+            }
+            acc.reset();
+            for (int sp = 1; sp < n; ++sp) {
+                const Item& it = items[(size_t)(begin + order[sp - 1])];
+                acc.add(it.lo, it.hi);
+                const float cost = acc.area() * (float)sp + suffix[sp].area() * (float)(n - sp);
+                if (cost < best_cost) {
+                    best_cost = cost; best_split = sp; best_left = acc; best_right = suffix[sp];
+                    for (int i = 0; i < n; ++i) best_order[i] = order[i];
+                }
+            }
+        }
+        int mid;
+        Bounds lb, rb;
+        if (best_split < 0) {
+            if (n <= 4) return leaf_link(begin, n);
+            mid = begin + n / 2;  // identical centroids: split by index
+            lb = range_bounds(begin, mid);
+            rb = range_bounds(mid, end);
+        } else {
+            // leaf cost: every item test is an f64 primitive intersection (expensive) -> weight 3 vs 1 per node
+            const float leaf_cost = leaf_weight * (float)n;
+            const float split_cost = 1.0f + leaf_weight * best_cost / std::max(whole.area(), 1e-30f);
+            if (n <= 4 && leaf_cost <= split_cost) return leaf_link(begin, n);
+            Item tmp[8];
+            for (int i = 0; i < n; ++i) tmp[i] = items[(size_t)(begin + best_order[i])];
+            for (int i = 0; i < n; ++i) items[(size_t)(begin + i)] = tmp[i];
+            mid = begin + best_split;
+            lb = best_left;
+            rb = best_right;
+        }
+        return finish(begin, mid, end, level, lb, rb);
+    }
+
+    // Binned-SAH split of items [begin, end) whose union is `whole`; returns the link for the range.
+    // Subtrees over disjoint item ranges are independent, so the top levels fork threads.  A node's slot is derived
+    // from its split position (unique per inner node), which makes the result independent of thread timing;
+    // compact() then renumbers the nodes in depth-first order, the layout a sequential build would produce.
+    int32_t build(int begin, int end, int level, const Bounds& whole) {
+        for (int seen = depth.load(); level > seen && !depth.compare_exchange_weak(seen, level);) {}
+        const int n = end - begin;
+        if (n <= 1) return leaf_link(begin, n);
+        if (n <= 8) return build_small(begin, end, level, whole);
+        const int NB = std::min(16, n);
+        Bounds cb;  // centroid bounds: the split candidates
+        cb.reset();
+        for (int i = begin; i < end; ++i) cb.add(items[(size_t)i].c, items[(size_t)i].c);
+        alignas(16) float ext[4], scale[4];
+        _mm_store_ps(ext, _mm_sub_ps(cb.hi, cb.lo));
+        for (int a = 0; a < 3; ++a) scale[a] = ext[a] > 0.0f ? (float)NB / ext[a] : 0.0f;
+        scale[3] = 0.0f;
+        const __m128 vscale = _mm_load_ps(scale), vtop = _mm_set1_ps((float)(NB - 1)), vzero = _mm_setzero_ps();
+        auto bins_of = [&](const Item& it, int k[4]) {
+            const __m128 f = _mm_min_ps(_mm_max_ps(_mm_mul_ps(_mm_sub_ps(it.c, cb.lo), vscale), vzero), vtop);
+            _mm_store_si128(reinterpret_cast<__m128i*>(k), _mm_cvttps_epi32(f));
+        };
+        Bounds bin_box[3][16];
+        int bin_n[3][16];
+        for (int a = 0; a < 3; ++a)
+            for (int k = 0; k < NB; ++k) { bin_box[a][k].reset(); bin_n[a][k] = 0; }
+        for (int i = begin; i < end; ++i) {  // one pass fills the bins of all three axes
+            const Item& it = items[(size_t)i];
+            alignas(16) int k[4];
+            bins_of(it, k);
+            for (int a = 0; a < 3; ++a) {
+                bin_box[a][k[a]].add(it.lo, it.hi);
+                bin_n[a][k[a]]++;
+            }
+        }
+        float best_cost = std::numeric_limits<float>::infinity();
+        int best_axis = -1, best_bin = -1;
+        Bounds best_left, best_right;
+        for (int a = 0; a < 3; ++a) {
+            if (!(ext[a] > 0.0f)) continue;
+            Bounds right_box[16];
+            int right_n[16];
+            Bounds acc;
+            acc.reset();
+            int cnt = 0;
+            for (int k = NB - 1; k > 0; --k) {
+                acc.add(bin_box[a][k]);
+                cnt += bin_n[a][k];
+                right_box[k] = acc;
+                right_n[k] = cnt;
+            }
+            Bounds left;
+            left.reset();
+            int ln = 0;
+            for (int k = 0; k < NB - 1; ++k) {
+                left.add(bin_box[a][k]);
+                ln += bin_n[a][k];
+                if (ln == 0 || right_n[k + 1] == 0) continue;
+                const float cost = left.area() * (float)ln + right_box[k + 1].area() * (float)right_n[k + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = a; best_bin = k; best_left = left; best_right = right_box[k + 1]; }
+            }
+        }
+        int mid;
+        Bounds lb, rb;
+        if (best_axis < 0) {
+            mid = begin + n / 2;  // identical centroids: split by index
+            lb = range_bounds(begin, mid);
+            rb = range_bounds(mid, end);
+        } else {
+            auto it = std::partition(items.begin() + begin, items.begin() + end, [&](const Item& x) {
+                alignas(16) int k[4];
+                bins_of(x, k);
+                return k[best_axis] <= best_bin;
+            });
+            mid = (int)(it - items.begin());
+            lb = best_left;
+            rb = best_right;
+        }
+        return finish(begin, mid, end, level, lb, rb);
     }
     // depth-first renumbering of the sparse slots into a dense array; returns the new root link
     int32_t compact(int32_t root) {
         if (root < 0) { nodes.clear(); return root; }
         std::vector<BvhNode> dense;
+        dense.reserve(nodes.size());
         std::vector<std::pair<int32_t, int32_t>> stack;  // (sparse slot, dense index)
         dense.emplace_back();
         stack.push_back({root, 0});
@@ -348,9 +445,21 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         out.lights.push_back(l);
     }
 
+    const bool trace = std::getenv("RTC_TRACE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    const auto t0 = now();
     // ---- primitives ----
     std::map<std::string, int32_t> xf_index, mi_index;
     std::vector<Box> prim_box((size_t)d.n_prims);
+    out.prims.reserve((size_t)d.n_prims);
+    {
+        size_t n_tri = 0;
+        for (int i = 0; i < d.n_prims; ++i) n_tri += d.prims[i].kind == RTC_TRIANGLE || d.prims[i].kind == RTC_SMOOTH_TRIANGLE;
+        out.tri_pe.reserve(n_tri * 10);
+        out.tri_n.reserve(n_tri * 10);
+    }
+    int32_t last_xf = -1, last_mi = -1;  // the triangles of a mesh share their matrices: compare with the previous primitive first
     for (int i = 0; i < d.n_prims; ++i) {
         const rtc_prim& p = d.prims[i];
         if (p.kind < RTC_SPHERE || p.kind > RTC_SMOOTH_TRIANGLE) return "prim " + std::to_string(i) + ": unknown kind";
@@ -367,19 +476,17 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         rtcdev::Prim q{};
         q.kind_flags = p.kind | (p.casts_shadow ? 0x100 : 0) | (p.closed ? 0x200 : 0);
         q.material = p.material;
-        q.xform = dedupe(xf_index, out.xforms, xf);
-        q.matinv = dedupe(mi_index, out.matinvs, mi);
+        if (last_xf < 0 || std::memcmp(&out.xforms[(size_t)last_xf], &xf, sizeof xf) != 0) last_xf = dedupe(xf_index, out.xforms, xf);
+        if (last_mi < 0 || std::memcmp(&out.matinvs[(size_t)last_mi], &mi, sizeof mi) != 0) last_mi = dedupe(mi_index, out.matinvs, mi);
+        q.xform = last_xf;
+        q.matinv = last_mi;
         q.geom = -1;
         if (p.kind == RTC_TRIANGLE || p.kind == RTC_SMOOTH_TRIANGLE) {
             q.geom = (int32_t)(out.tri_pe.size() / 10);
-            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.p1[k]);
-            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.e1[k]);
-            for (int k = 0; k < 3; ++k) out.tri_pe.push_back(p.e2[k]);
-            out.tri_pe.push_back(0.0);
-            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n1[k]);
-            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n2[k]);
-            for (int k = 0; k < 3; ++k) out.tri_n.push_back(p.n3[k]);
-            out.tri_n.push_back(0.0);
+            const double pe[10] = {p.p1[0], p.p1[1], p.p1[2], p.e1[0], p.e1[1], p.e1[2], p.e2[0], p.e2[1], p.e2[2], 0.0};
+            const double nn[10] = {p.n1[0], p.n1[1], p.n1[2], p.n2[0], p.n2[1], p.n2[2], p.n3[0], p.n3[1], p.n3[2], 0.0};
+            out.tri_pe.insert(out.tri_pe.end(), pe, pe + 10);
+            out.tri_n.insert(out.tri_n.end(), nn, nn + 10);
         } else if (p.kind == RTC_CYLINDER || p.kind == RTC_CONE) {
             q.geom = (int32_t)(out.ranges.size() / 2);
             out.ranges.push_back(p.min);
@@ -390,6 +497,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         prim_box[(size_t)i] = prim_bounds(p);
     }
 
+    const auto t1 = now();
     // ---- group tree: gates, CSG roots, items --------------------------------------------------
     std::vector<int> visited_node((size_t)d.n_nodes, 0), visited_prim((size_t)d.n_prims, 0);
     std::vector<Box> item_boxes;   // per BVH item
@@ -526,6 +634,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
     if (!err.empty()) return err;
     if (next_prim != d.n_prims) return "some primitives are not reachable from the root node";
 
+    const auto t2 = now();
+    auto t3 = t2;
     // ---- BVH over the bounded items -------------------------------------------------------------
     out.n_bvh_items = (int32_t)item_ids.size();
     if (!item_ids.empty()) {
@@ -536,14 +646,15 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         // fp32 traversal error bound is ~9 * 2^-24 * S (DESIGN.md "conservative fp32 culling"); pad with margin
         const double pad = 4e-6 * std::max(S, 1e-30);
         Builder bld(item_boxes, pad);
-        out.bvh_root = bld.compact(bld.build(0, (int)item_ids.size(), 0, root));
+        out.bvh_root = bld.compact(bld.build(0, (int)item_ids.size(), 0, bld.range_bounds(0, (int)item_ids.size())));
         out.bvh = std::move(bld.nodes);
         out.bvh_depth = bld.depth;
+        t3 = now();
         if (out.bvh_depth + 2 > rtcdev::BVH_STACK) return "BVH deeper than the traversal stack";
         out.leaf_items.resize(item_ids.size());
         out.leaf_tri.assign(item_ids.size() * 10, 0.0);
         for (size_t i = 0; i < item_ids.size(); ++i) {
-            const int32_t id = item_ids[(size_t)bld.items[i].index];
+            const int32_t id = item_ids[(size_t)bld.index_of(i)];
             rtcdev::LeafItem li{id, 0, 0, -1};
             if (id >= 0) {
                 const rtcdev::Prim& p = out.prims[(size_t)id];
@@ -558,6 +669,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         for (int k = 0; k < 3; ++k) { out.root_lo[k] = root.lo[k] - pad; out.root_hi[k] = root.hi[k] + pad; }
     }
     if (out.bvh.empty()) out.bvh.emplace_back();  // keep device pointers non-null
+    if (trace)
+        std::fprintf(stderr, "build_host_scene: prims %.3f ms, group tree %.3f ms, bvh %.3f ms, leaf items %.3f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, t3), ms(t3, now()));
     return "";
 }
 
