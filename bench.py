@@ -256,25 +256,35 @@ def run_cuda_inner(args):
     if rank == 0:
         host_image[:] = np.nan
 
+    trace_steps = bool(os.environ.get("RTC_E2E_TRACE"))
+
     def e2e_step():
+        ta = time.perf_counter()
         rc = drv.drv_e2e_step(sess.handle, local, C.byref(opts), out_ptr, C.byref(st), err, 1024)
         if rc != 0:
             raise R.RtcError(err.value.decode())
+        tb = time.perf_counter()
         if world > 1:
-            dist.barrier()  # the frame is complete when every rank's bands have landed
+            frame.frame_barrier(rank, world)  # the frame is complete when every rank's bands have landed
+        if trace_steps:
+            print(f"rank {rank}: step call {(tb - ta) * 1e3:.3f} ms, frame barrier {(time.perf_counter() - tb) * 1e3:.3f} ms", file=sys.stderr)
         return st.rays
 
     barrier()
     for _ in range(warmup):
         e2e_step()
     barrier()
-    frame_ok = bool(np.isfinite(host_image).all()) if rank == 0 else True
+    frame_ok = bool(np.isfinite(host_image).all()) if rank == 0 else True  # every pixel was written by some rank
+    barrier()  # (rank 0's check must not count as the other ranks' first step)
     t0 = time.perf_counter()
     e2e_rays = 0
     for _ in range(args.steps):
         e2e_rays += e2e_step()
+    t_loop = time.perf_counter()
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    if trace_steps:
+        print(f"rank {rank}: e2e loop {(t_loop - t0) * 1e3:.3f} ms for {args.steps} steps, closing barrier {e2e_ms - (t_loop - t0) * 1e3:.3f} ms", file=sys.stderr)
     e2e_ms_max = reduce(e2e_ms, MAX)
     e2e_rays_all = reduce(float(e2e_rays), SUM)
     e2e_value = e2e_rays_all / e2e_ms_max / 1e3
@@ -296,7 +306,7 @@ def run_cuda_inner(args):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h, "frame_ms": e2e_ms_max / args.steps,
                     "path": "rtc_scene_create + rtc_render (page-locked host f64 rgb, copies overlapped with tracing) + rtc_scene_destroy per step"
-                            + ("" if world == 1 else "; every rank writes its bands into one shared host image, barrier per frame")},
+                            + ("" if world == 1 else "; every rank writes its bands into one shared host image, shared-memory barrier per frame")},
             "gpu_launches": int(launches_all),
         }
         line.update(rooflines(R, prof, world))

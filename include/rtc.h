@@ -172,6 +172,11 @@ int rtc_device_count(void);
 /* Copies and uploads the scene to CUDA device `device`, building the BVH.  0 = ok. */
 int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
 
+/* The same for `n` distinct devices at once: ONE host build (validation, flattening, BVH), one upload per device
+ * (in parallel); out[i] is the handle for devices[i].  What Image::par_render does before rtc_render_multi.
+ * All or nothing: on failure no handle is returned. */
+int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n, rtc_scene** out);
+
 void rtc_scene_destroy(rtc_scene* scene);
 
 /* Blocking render into caller-allocated host memory: out_rgb holds one (r,g,b) f64 triple per

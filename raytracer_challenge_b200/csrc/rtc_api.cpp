@@ -136,7 +136,7 @@ int env_int(const char* name, int fallback, int lo, int hi) {
 struct rtc_scene {
     int device = 0;
     int feat = 0;
-    rtchost::HostScene host;
+    std::shared_ptr<rtchost::HostScene> host;  // shared by the handles of one rtc_scene_create_multi call
     rtcdev::Scene dev{};
     void* arena = nullptr;  // one device allocation holding every scene array
     size_t arena_bytes = 0;
@@ -232,7 +232,7 @@ static int64_t host_stat(const rtchost::HostScene& h, int key) {
     }
 }
 
-int64_t rtc_scene_stat(const rtc_scene* s, int key) { return s ? host_stat(s->host, key) : -1; }
+int64_t rtc_scene_stat(const rtc_scene* s, int key) { return s && s->host ? host_stat(*s->host, key) : -1; }
 
 int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16) {
     if (!desc) return fail("rtc_scene_validate: null argument");
@@ -278,47 +278,39 @@ void rtc_release_device_memory(int device) {
     cudaFree(c.spare_arena); c.spare_arena = nullptr; c.spare_arena_bytes = 0;
 }
 
-int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
-    if (!desc || !out) return fail("rtc_scene_create: null argument");
-    *out = nullptr;
-    int n_dev = 0;
-    CU(cudaGetDeviceCount(&n_dev));
-    if (n_dev <= 0) return fail("rtc_scene_create: no CUDA device (this library has no CPU fallback)");
-    if (device < 0 || device >= n_dev || device >= MAX_DEVICES) return fail("rtc_scene_create: device ordinal out of range");
-    std::unique_ptr<rtc_scene> s(new rtc_scene);
-    s->device = device;
-    const auto t_build0 = std::chrono::steady_clock::now();
-    const std::string err = rtchost::build_host_scene(*desc, s->host);
-    const auto t_build1 = std::chrono::steady_clock::now();
-    if (!err.empty()) return fail("rtc_scene_create: " + err);
-    CU(cudaSetDevice(device));
-    {
-        DeviceCtx& c = g_ctx[device];
-        std::lock_guard<std::mutex> lock(c.mu);
-        if (int rc = ctx_init(c, device)) return rc;
-    }
+}  // extern "C"
 
-    // Pack every array into one staging blob (256-byte aligned sections): one cudaMalloc + one copy.
-    rtchost::HostScene& h = s->host;
-    rtcdev::Scene& d = s->dev;
+// Every array of the flattened scene in one staging blob (256-byte aligned sections): one cudaMalloc + one copy per device.
+struct PackedScene {
     std::vector<unsigned char> blob;
+    size_t o_prims, o_xforms, o_matinvs, o_tri_pe, o_tri_n, o_ranges, o_materials, o_patterns, o_lights, o_gates, o_bvh, o_leaf_items,
+        o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots;
+};
+static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     auto place = [&](const void* src, size_t bytes) -> size_t {
-        const size_t off = (blob.size() + 255) & ~(size_t)255;
-        blob.resize(off + std::max<size_t>(bytes, 16));
-        if (bytes) std::memcpy(blob.data() + off, src, bytes);
+        const size_t off = (p.blob.size() + 255) & ~(size_t)255;
+        p.blob.resize(off + std::max<size_t>(bytes, 16));
+        if (bytes) std::memcpy(p.blob.data() + off, src, bytes);
         return off;
     };
 #define PLACE(vec) place((vec).data(), (vec).size() * sizeof((vec)[0]))
-    const size_t o_prims = PLACE(h.prims), o_xforms = PLACE(h.xforms), o_matinvs = PLACE(h.matinvs), o_tri_pe = PLACE(h.tri_pe),
-                 o_tri_n = PLACE(h.tri_n), o_ranges = PLACE(h.ranges), o_materials = PLACE(h.materials), o_patterns = PLACE(h.patterns),
-                 o_lights = PLACE(h.lights), o_gates = PLACE(h.gates), o_bvh = PLACE(h.bvh), o_leaf_items = PLACE(h.leaf_items),
-                 o_leaf_tri = PLACE(h.leaf_tri), o_unbounded = PLACE(h.unbounded), o_csg_ops = PLACE(h.csg_ops), o_csg_roots = PLACE(h.csg_roots);
+    p.o_prims = PLACE(h.prims); p.o_xforms = PLACE(h.xforms); p.o_matinvs = PLACE(h.matinvs); p.o_tri_pe = PLACE(h.tri_pe);
+    p.o_tri_n = PLACE(h.tri_n); p.o_ranges = PLACE(h.ranges); p.o_materials = PLACE(h.materials); p.o_patterns = PLACE(h.patterns);
+    p.o_lights = PLACE(h.lights); p.o_gates = PLACE(h.gates); p.o_bvh = PLACE(h.bvh); p.o_leaf_items = PLACE(h.leaf_items);
+    p.o_leaf_tri = PLACE(h.leaf_tri); p.o_unbounded = PLACE(h.unbounded); p.o_csg_ops = PLACE(h.csg_ops); p.o_csg_roots = PLACE(h.csg_roots);
 #undef PLACE
-    h.device_bytes = (int64_t)blob.size();
+    h.device_bytes = (int64_t)p.blob.size();
+}
+
+// Device half of rtc_scene_create: arena (reused from the device context when one is parked there), copy, pointers.
+static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
+    const int device = s->device;
+    if (cudaSetDevice(device) != cudaSuccess) { err = "cudaSetDevice failed"; return 1; }
+    DeviceCtx& c = g_ctx[device];
     {
-        DeviceCtx& c = g_ctx[device];
         std::lock_guard<std::mutex> lock(c.mu);
-        if (c.spare_arena && c.spare_arena_bytes >= blob.size()) {
+        if (ctx_init(c, device)) { err = g_error; return 1; }
+        if (c.spare_arena && c.spare_arena_bytes >= p.blob.size()) {
             s->arena = c.spare_arena;
             s->arena_bytes = c.spare_arena_bytes;
             c.spare_arena = nullptr;
@@ -326,30 +318,34 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
         }
     }
     if (!s->arena) {
-        if (cudaMalloc(&s->arena, blob.size()) != cudaSuccess) return fail("rtc_scene_create: cudaMalloc of the scene arena failed");
-        s->arena_bytes = blob.size();
+        if (cudaMalloc(&s->arena, p.blob.size()) != cudaSuccess) { err = "cudaMalloc of the scene arena failed"; return 1; }
+        s->arena_bytes = p.blob.size();
     }
-    if (cudaMemcpy(s->arena, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+    if (cudaMemcpy(s->arena, p.blob.data(), p.blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        err = std::string("scene upload failed: ") + cudaGetErrorString(cudaGetLastError());
         cudaFree(s->arena);
-        return fail(std::string("rtc_scene_create: scene upload failed: ") + cudaGetErrorString(cudaGetLastError()));
+        s->arena = nullptr;
+        return 1;
     }
+    const rtchost::HostScene& h = *s->host;
+    rtcdev::Scene& d = s->dev;
     unsigned char* base = (unsigned char*)s->arena;
-    d.prims = (const rtcdev::Prim*)(base + o_prims);
-    d.xforms = (const rtcdev::Xform*)(base + o_xforms);
-    d.matinvs = (const rtcdev::MatInv*)(base + o_matinvs);
-    d.tri_pe = (const double*)(base + o_tri_pe);
-    d.tri_n = (const double*)(base + o_tri_n);
-    d.ranges = (const double*)(base + o_ranges);
-    d.materials = (const rtcdev::Material*)(base + o_materials);
-    d.patterns = (const rtcdev::Pattern*)(base + o_patterns);
-    d.lights = (const rtcdev::Light*)(base + o_lights);
-    d.gates = (const rtcdev::Gate*)(base + o_gates);
-    d.bvh = (const rtcdev::BvhNode*)(base + o_bvh);
-    d.leaf_items = (const rtcdev::LeafItem*)(base + o_leaf_items);
-    d.leaf_tri = (const double*)(base + o_leaf_tri);
-    d.unbounded = (const int32_t*)(base + o_unbounded);
-    d.csg_ops = (const rtcdev::CsgOp*)(base + o_csg_ops);
-    d.csg_roots = (const rtcdev::CsgRoot*)(base + o_csg_roots);
+    d.prims = (const rtcdev::Prim*)(base + p.o_prims);
+    d.xforms = (const rtcdev::Xform*)(base + p.o_xforms);
+    d.matinvs = (const rtcdev::MatInv*)(base + p.o_matinvs);
+    d.tri_pe = (const double*)(base + p.o_tri_pe);
+    d.tri_n = (const double*)(base + p.o_tri_n);
+    d.ranges = (const double*)(base + p.o_ranges);
+    d.materials = (const rtcdev::Material*)(base + p.o_materials);
+    d.patterns = (const rtcdev::Pattern*)(base + p.o_patterns);
+    d.lights = (const rtcdev::Light*)(base + p.o_lights);
+    d.gates = (const rtcdev::Gate*)(base + p.o_gates);
+    d.bvh = (const rtcdev::BvhNode*)(base + p.o_bvh);
+    d.leaf_items = (const rtcdev::LeafItem*)(base + p.o_leaf_items);
+    d.leaf_tri = (const double*)(base + p.o_leaf_tri);
+    d.unbounded = (const int32_t*)(base + p.o_unbounded);
+    d.csg_ops = (const rtcdev::CsgOp*)(base + p.o_csg_ops);
+    d.csg_roots = (const rtcdev::CsgRoot*)(base + p.o_csg_roots);
     d.n_prims = (int32_t)h.prims.size();
     d.n_lights = (int32_t)h.lights.size();
     d.n_gates = (int32_t)h.gates.size();
@@ -361,13 +357,64 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
+    return 0;
+}
+
+extern "C" {
+
+// One host build (validation, flattening, BVH), one upload per device.  rtc_scene_create is the n = 1 case.
+int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n, rtc_scene** out) {
+    if (!desc || !devices || !out || n <= 0) return fail("rtc_scene_create: null argument");
+    for (int i = 0; i < n; ++i) out[i] = nullptr;
+    int n_dev = 0;
+    CU(cudaGetDeviceCount(&n_dev));
+    if (n_dev <= 0) return fail("rtc_scene_create: no CUDA device (this library has no CPU fallback)");
+    for (int i = 0; i < n; ++i) {
+        if (devices[i] < 0 || devices[i] >= n_dev || devices[i] >= MAX_DEVICES) return fail("rtc_scene_create: device ordinal out of range");
+        for (int j = 0; j < i; ++j)
+            if (devices[j] == devices[i]) return fail("rtc_scene_create_multi: device listed twice");
+    }
+    const auto t_build0 = std::chrono::steady_clock::now();
+    auto host = std::make_shared<rtchost::HostScene>();
+    const std::string err = rtchost::build_host_scene(*desc, *host);
+    if (!err.empty()) return fail("rtc_scene_create: " + err);
+    const auto t_build1 = std::chrono::steady_clock::now();
+    PackedScene packed;
+    pack_scene(*host, packed);
+    std::vector<std::unique_ptr<rtc_scene>> made((size_t)n);
+    std::vector<std::string> errors((size_t)n);
+    std::vector<int> rcs((size_t)n, 0);
+    auto one = [&](int i) {
+        made[(size_t)i].reset(new rtc_scene);
+        made[(size_t)i]->device = devices[i];
+        made[(size_t)i]->host = host;
+        rcs[(size_t)i] = upload_scene(made[(size_t)i].get(), packed, errors[(size_t)i]);
+    };
+    if (n == 1) one(0);
+    else {
+        std::vector<std::thread> workers;
+        for (int i = 0; i < n; ++i) workers.emplace_back(one, i);
+        for (auto& w : workers) w.join();
+    }
+    for (int i = 0; i < n; ++i)
+        if (rcs[(size_t)i]) {
+            const std::string why = errors[(size_t)i];
+            for (auto& m : made)
+                if (m && m->arena) { cudaSetDevice(m->device); cudaFree(m->arena); }
+            return fail("rtc_scene_create: device " + std::to_string(devices[i]) + ": " + why);
+        }
     if (std::getenv("RTC_TRACE")) {
         auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-        std::fprintf(stderr, "rtc_scene_create: host build %.3f ms, pack + upload %.3f ms (%zu bytes)\n", ms(t_build0, t_build1),
-                     ms(t_build1, std::chrono::steady_clock::now()), blob.size());
+        std::fprintf(stderr, "rtc_scene_create: host build %.3f ms, pack + upload to %d device(s) %.3f ms (%zu bytes each)\n", ms(t_build0, t_build1), n,
+                     ms(t_build1, std::chrono::steady_clock::now()), packed.blob.size());
     }
-    *out = s.release();
+    for (int i = 0; i < n; ++i) out[i] = made[(size_t)i].release();
     return 0;
+}
+
+int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
+    if (!desc || !out) return fail("rtc_scene_create: null argument");
+    return rtc_scene_create_multi(desc, &device, 1, out);
 }
 
 static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t shadow_bytes, uint64_t accum_samples) {

@@ -146,6 +146,12 @@ struct Builder {
 
     Builder(const std::vector<Box>& boxes, double pad) {
         if (const char* w = std::getenv("RTC_LEAF_WEIGHT")) leaf_weight = (float)std::max(0.1, std::atof(w));
+        {   // one process per GPU (torchrun sets LOCAL_WORLD_SIZE): the ranks of a node build at the same time, share the cores
+            int cores = (int)std::thread::hardware_concurrency();
+            if (const char* w = std::getenv("LOCAL_WORLD_SIZE")) cores /= std::max(1, std::atoi(w));
+            fork_levels = 0;
+            while (fork_levels < 4 && (2 << fork_levels) <= cores) fork_levels++;
+        }
         if (const char* w = std::getenv("RTC_BUILD_FORK_LEVELS")) fork_levels = std::min(8, std::max(0, std::atoi(w)));
         items.resize(boxes.size());
         for (size_t i = 0; i < boxes.size(); ++i) {

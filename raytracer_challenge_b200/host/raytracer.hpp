@@ -681,17 +681,11 @@ class Image {
             if (n <= 0) throw std::runtime_error(std::string("Image::par_render: no CUDA device: ") + rtc_last_error());
             for (int i = 0; i < n; ++i) devices.push_back(i);
         }
-        std::vector<rtc_scene*> scenes;
+        std::vector<rtc_scene*> scenes(devices.size(), nullptr);
         auto release = [&] { for (rtc_scene* sc : scenes) rtc_scene_destroy(sc); };
-        for (int dev : devices) {
-            rtc_scene* sc = nullptr;
-            if (rtc_scene_create(&d, dev, &sc) != 0) {
-                const std::string err = rtc_last_error();
-                release();
-                throw std::runtime_error("rtc_scene_create: " + err);
-            }
-            scenes.push_back(sc);
-        }
+        // one host build (flattening, BVH), one upload per device
+        if (rtc_scene_create_multi(&d, devices.data(), (int)devices.size(), scenes.data()) != 0)
+            throw std::runtime_error(std::string("rtc_scene_create: ") + rtc_last_error());
         const rtc_camera cam = camera.to_c();
         Image img;
         const bool windowed = ro.opts.win_w > 0 && ro.opts.win_h > 0;

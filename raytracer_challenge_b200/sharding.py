@@ -82,14 +82,34 @@ class SharedFrame:
     def __init__(self, height, width, name=None, create=False):
         self.shape = (height, width, 3)
         nbytes = int(np.prod(self.shape)) * 8
-        self.shm = shared_memory.SharedMemory(name=name, create=create, size=nbytes if create else 0)
+        flags_at = (nbytes + 4095) // 4096 * 4096  # per-rank frame counters live behind the image (frame_barrier)
+        self.shm = shared_memory.SharedMemory(name=name, create=create, size=flags_at + self.MAX_RANKS * 8 if create else 0)
         self.owner = create
         self.array = np.ndarray(self.shape, dtype=np.float64, buffer=self.shm.buf)
+        self.flags = np.ndarray((self.MAX_RANKS,), dtype=np.int64, buffer=self.shm.buf, offset=flags_at)
+        if create:
+            self.flags[:] = 0
+        self.seq = 0
         self.pinned = False
+
+    MAX_RANKS = 64
 
     @property
     def name(self):
         return self.shm.name
+
+    def frame_barrier(self, rank, world, timeout_s=60.0):
+        """Every rank calls this once per frame, after its bands have landed in the image (its render call has
+        returned): returns when all `world` ranks have.  A counter per rank in the shared segment; each rank writes
+        only its own (aligned 8-byte stores), so no atomics are needed.  A node-local stand-in for a collective
+        barrier, which costs milliseconds per call here."""
+        import time
+        self.seq += 1
+        self.flags[rank] = self.seq
+        t0 = time.perf_counter()
+        while int(self.flags[:world].min()) < self.seq:
+            if time.perf_counter() - t0 > timeout_s:
+                raise TimeoutError("SharedFrame.frame_barrier: a rank did not arrive")
 
     @property
     def ptr(self):
@@ -106,6 +126,7 @@ class SharedFrame:
             load_rtc().rtc_host_unregister(self.ptr)
             self.pinned = False
         self.array = None
+        self.flags = None
         self.shm.close()
         if self.owner:
             self.shm.unlink()

@@ -152,6 +152,7 @@ pub struct rtc_scene {
 extern "C" {
     pub fn rtc_device_count() -> c_int;
     pub fn rtc_scene_create(desc: *const rtc_scene_desc, device: c_int, out: *mut *mut rtc_scene) -> c_int;
+    pub fn rtc_scene_create_multi(desc: *const rtc_scene_desc, devices: *const c_int, n: c_int, out: *mut *mut rtc_scene) -> c_int;
     pub fn rtc_scene_destroy(scene: *mut rtc_scene);
     pub fn rtc_render(scene: *mut rtc_scene, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;
     pub fn rtc_render_multi(scenes: *const *mut rtc_scene, n: c_int, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;

@@ -155,16 +155,12 @@ pub fn render(camera: &Camera, world: &World) -> Vec<Color> {
     let desc = flat.desc();
     let n_dev = unsafe { rtc_device_count() };
     assert!(n_dev > 0, "raytracer: no CUDA device: {}", last_error());
-    let mut scenes: Vec<*mut rtc_scene> = Vec::new();
-    for dev in 0..n_dev {
-        let mut s: *mut rtc_scene = std::ptr::null_mut();
-        let rc = unsafe { rtc_scene_create(&desc, dev, &mut s) };
-        if rc != 0 {
-            let msg = last_error();
-            for s in &scenes { unsafe { rtc_scene_destroy(*s) } }
-            panic!("rtc_scene_create: {}", msg);
-        }
-        scenes.push(s);
+    // one host build (flattening, BVH), one upload per GPU
+    let devices: Vec<i32> = (0..n_dev).collect();
+    let mut scenes: Vec<*mut rtc_scene> = vec![std::ptr::null_mut(); devices.len()];
+    let rc = unsafe { rtc_scene_create_multi(&desc, devices.as_ptr(), n_dev, scenes.as_mut_ptr()) };
+    if rc != 0 {
+        panic!("rtc_scene_create: {}", last_error());
     }
     let (transform_inv, pixel_size, half_width, half_height) = camera.ffi_parts();
     let cam = rtc_camera { hsize: camera.hsize as i32, vsize: camera.vsize as i32, transform_inv: m16(&transform_inv), pixel_size, half_width, half_height };

@@ -23,7 +23,7 @@ def declared_functions():
 
 def test_header_declares_the_expected_entry_points():
     names = declared_functions()
-    for must in ["rtc_scene_create", "rtc_scene_destroy", "rtc_render", "rtc_render_device", "rtc_render_multi", "rtc_last_error",
+    for must in ["rtc_scene_create", "rtc_scene_create_multi", "rtc_scene_destroy", "rtc_render", "rtc_render_device", "rtc_render_multi", "rtc_last_error",
                  "rtc_device_count", "rtc_shard_pixels", "rtc_quantize", "rtc_scene_validate"]:
         assert must in names
 

@@ -39,7 +39,7 @@ def worker(rank, world, port, w, h, shm_name, q):
         # path 1: shared host frame
         frame = sharding.SharedFrame(h, w, name=shm_name, create=False)
         sharding.place_bands(frame.array, local, rank, world)
-        dist.barrier()
+        frame.frame_barrier(rank, world)  # the per-frame barrier of the end-to-end bench: counters in the shared segment
         if rank == 0:
             want = fake_pixel(np.arange(w * h)).reshape(h, w, 3)
             q.put(("shared", bool(np.array_equal(frame.array, want))))
