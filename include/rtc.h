@@ -156,6 +156,7 @@ typedef struct rtc_stats {
     int32_t reserved;
     /* work actually done by the traversal kernels (inputs of the roofline model) */
     uint64_t surface_hits;    /* rays that hit something = shaded surface points */
+    /* work tallies, RTC_FLAG_PROFILE only (0 otherwise: the counters cost registers in the traversal loop) */
     uint64_t bvh_node_visits; /* each visit = two fp32 slab tests */
     uint64_t triangle_tests, primitive_tests; /* exact f64 intersections: triangles / every other kind */
     uint64_t ray_transforms;  /* world -> object ray transforms (src/ray.rs:14-19) actually computed */

@@ -17,6 +17,8 @@ constexpr int BVH_STACK = 48;
 constexpr int FEAT_TRANSPARENT = 1;  // some material has transparency != 0: n1/n2 replay needed
 constexpr int FEAT_CSG = 2;          // CSG items present
 constexpr int FEAT_GATES = 4;        // group boxes that must be evaluated exactly
+constexpr int FEAT_TALLY = 8;        // RTC_FLAG_PROFILE: count the work done (node visits, primitive tests, ...); off, the counters and
+                                     // their registers do not exist in the kernel
 
 // Per distinct (transform_inv, transform_inv_tsp) pair.  Affine: rows 0..2 only.
 struct Xform {

@@ -65,17 +65,20 @@ struct Query {
     uint32_t passed;
     ObjRay cache;
     Tally& tally;
+    Tally scratch;  // FEAT_TALLY off: the increments land here, are never read, and the compiler drops them
     int* overflow;
     bool skip_negative;  // the query only wants crossings with t >= 0 (set by the closest-hit and shadow visitors)
     __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg)
-        : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), overflow(ovf), skip_negative(skip_neg) {
+        : sc(s), ray(r), passed(gates_passed<FEAT>(s, r)), tally(tl), scratch{0u, 0u, 0u, 0u}, overflow(ovf), skip_negative(skip_neg) {
         cache.xform = -1;
     }
     // copy of a query for an out-of-line evaluation: the gates are already known
     __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg, uint32_t passed_gates)
-        : sc(s), ray(r), passed(passed_gates), tally(tl), overflow(ovf), skip_negative(skip_neg) {
+        : sc(s), ray(r), passed(passed_gates), tally(tl), scratch{0u, 0u, 0u, 0u}, overflow(ovf), skip_negative(skip_neg) {
         cache.xform = -1;
     }
+    static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
+    __device__ __forceinline__ Tally& counters() { return kTally ? tally : scratch; }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
         if (!(FEAT & FEAT_GATES)) return true;
         return (__ldg(&sc.prims[prim_id].gate_mask) & ~passed) == 0u;
@@ -85,13 +88,13 @@ struct Query {
         r.n = 0;
         const Prim p = load_prim(sc, id);
         if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
-        prim_roots<0x02>(sc, p, ray, cache, tally, skip_negative, r);  // planes are the usual always-tested primitive
+        prim_roots<0x02>(sc, p, ray, cache, counters(), skip_negative, r);  // planes are the usual always-tested primitive
     }
     // crossings of a BVH leaf item that is a primitive
     __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
         r.n = 0;
         if (!gate_ok(li.id)) return;
-        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, tally, skip_negative, r);  // triangles, spheres
+        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, counters(), skip_negative, r);  // triangles, spheres
     }
 };
 
@@ -156,13 +159,13 @@ __device__ __forceinline__ void csg_call(Query<FEAT>& q, int root, CsgCall& c) {
     c.passed = q.passed;
     c.skip_negative = q.skip_negative ? 1 : 0;
     csg_call_body<FEAT>(q.sc, root, q.overflow, &c);
-    q.tally.nodes += c.tally.nodes; q.tally.tris += c.tally.tris; q.tally.prims += c.tally.prims; q.tally.xforms += c.tally.xforms;
+    if (FEAT & FEAT_TALLY) { q.tally.nodes += c.tally.nodes; q.tally.tris += c.tally.tris; q.tally.prims += c.tally.prims; q.tally.xforms += c.tally.xforms; }
     if (c.n < 0) *q.overflow = 1;
 }
 
 // ---- fp32 BVH walk ---------------------------------------------------------------------------
 struct Walk {
-    float ox, oy, oz, ix, iy, iz;
+    float px, py, pz, ix, iy, iz;  // p = origin * inverse direction: a slab plane is at fma(plane, i, -p)
     double te;   // world t of the re-origin
     float tlo;   // lower end of the admissible interval, relative to te
 };
@@ -189,19 +192,23 @@ __device__ __forceinline__ bool walk_setup(const Scene& sc, const Ray& ray, int 
         w.tlo = -CUDART_INF_F;
     }
     if (!(fabs(w.te) <= 1.7e308)) { w.te = 0.0; w.tlo = mode == 0 ? 0.0f : -CUDART_INF_F; }
-    w.ox = (float)(o[0] + w.te * d[0]);
-    w.oy = (float)(o[1] + w.te * d[1]);
-    w.oz = (float)(o[2] + w.te * d[2]);
     w.ix = 1.0f / (float)d[0];
     w.iy = 1.0f / (float)d[1];
     w.iz = 1.0f / (float)d[2];
+    // One fused multiply-add per plane instead of a subtract and a multiply (explicit: the build has -fmad=false for
+    // the f64 code).  The extra rounding of p is <= 2^-24 |o| in distance, far inside the padding of the boxes
+    // ("conservative fp32 culling").  A zero direction component gives inf - inf = NaN, which the
+    // min / max chain ignores: that axis then rejects nothing, which is still a superset.
+    w.px = (float)(o[0] + w.te * d[0]) * w.ix;
+    w.py = (float)(o[1] + w.te * d[1]) * w.iy;
+    w.pz = (float)(o[2] + w.te * d[2]) * w.iz;
     return true;
 }
 
 __device__ __forceinline__ bool slab(const Walk& w, float lx, float ly, float lz, float hx, float hy, float hz, float thi, float& tnear) {
-    const float ax = (lx - w.ox) * w.ix, bx = (hx - w.ox) * w.ix;
-    const float ay = (ly - w.oy) * w.iy, by = (hy - w.oy) * w.iy;
-    const float az = (lz - w.oz) * w.iz, bz = (hz - w.oz) * w.iz;
+    const float ax = __fmaf_rn(lx, w.ix, -w.px), bx = __fmaf_rn(hx, w.ix, -w.px);
+    const float ay = __fmaf_rn(ly, w.iy, -w.py), by = __fmaf_rn(hy, w.iy, -w.py);
+    const float az = __fmaf_rn(lz, w.iz, -w.pz), bz = __fmaf_rn(hz, w.iz, -w.pz);
     const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), w.tlo));
     const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), thi));
     tnear = t0;
@@ -233,7 +240,7 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
     constexpr int WALK_DONE = (int)0x80000000;  // never a leaf link: ~enc with enc >= 0 is > INT_MIN
     for (;;) {
         while (link >= 0) {
-            tally.nodes++;
+            if (V::kTally) tally.nodes++;
             const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
             const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
             float n0, n1;
@@ -266,6 +273,7 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
 // ---- closest hit ---------------------------------------------------------------------------------
 template <int FEAT>
 struct ClosestVisitor {
+    static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
     Query<FEAT> q;
     Hit best;
     double limit;   // exclusive upper bound on t (shadow queries on scenes with non-casting shapes), else +inf
@@ -293,7 +301,7 @@ struct ClosestVisitor {
                 const Prim p = load_prim(q.sc, list[k].prim);
                 if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
                     Roots r;
-                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.tally, false, r);
+                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.counters(), false, r);
                     u = r.u; v = r.v;
                 }
                 offer(list[k].t, list[k].prim, u, v);
@@ -329,6 +337,7 @@ __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, doub
 // ---- shadow query: World::is_shadowed (src/world.rs:26-48) -------------------------------------------
 template <int FEAT>
 struct AnyVisitor {
+    static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
     Query<FEAT> q;
     double dist;
     bool found;
@@ -377,6 +386,7 @@ __device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double 
 // ---- n1 / n2: replay of the container walk of Intersection::prepare_state (src/intersection.rs:70-103) ----
 template <int FEAT>
 struct CollectVisitor {
+    static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
     Query<FEAT> q;
     double thit;
     Cross* out;
@@ -469,7 +479,7 @@ __device__ __forceinline__ void refractive_indices(const Scene& sc, const Ray& r
     refractive_indices_body<FEAT>(sc, hit_t, hit_prim, brute, overflow, &c);
     n1 = c.n1;
     n2 = c.n2;
-    tally.nodes += c.tally.nodes; tally.tris += c.tally.tris; tally.prims += c.tally.prims; tally.xforms += c.tally.xforms;
+    if (FEAT & FEAT_TALLY) { tally.nodes += c.tally.nodes; tally.tris += c.tally.tris; tally.prims += c.tally.prims; tally.xforms += c.tally.xforms; }
 }
 
 }  // namespace rtcdev

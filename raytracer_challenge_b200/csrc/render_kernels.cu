@@ -164,6 +164,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRA
     const uint32_t seg = hl.seg_off[lv.level], seg_cap = hl.seg_cap[lv.level];
     // every lane of a warp runs the same number of iterations so the warp-aggregated pushes stay convergent
     const uint32_t n_round = (n_in + 31u) & ~31u;
+    // Counters cost registers in the hottest loop of the program: the work tallies exist only under RTC_FLAG_PROFILE
+    // (FEAT_TALLY), the reflected / refracted split only where both kinds occur (otherwise the host reads the number
+    // of children off the queue counters).
+    constexpr bool TALLY = (FEAT & FEAT_TALLY) != 0;
+    constexpr bool SPLIT = (FEAT & FEAT_TRANSPARENT) != 0;
     uint32_t c_active = 0, longest = 0, c_refl = 0, c_refr = 0;
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
@@ -179,10 +184,10 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRA
         double w_refl = 0.0, w_refr = 0.0;
         Surface s;
         if (active) {
-            c_active++;
+            if (PRIMARY) c_active++;
             const uint32_t nodes_before = tally.nodes;
             hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
-            longest = max(longest, tally.nodes - nodes_before);
+            if (TALLY) longest = max(longest, tally.nodes - nodes_before);
             if (hit.prim >= 0) {
                 const Prim prim = load_prim(sc, hit.prim);
                 const Material& mat = sc.materials[prim.material];
@@ -253,7 +258,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRA
                     lv.out_q2[slot] = make_double2(r_refl.d.y, r_refl.d.z);
                     lv.out_q3[slot] = make_double2(w_refl, __longlong_as_double((long long)packed_fuel));
                 } else *lv.overflow = 2;
-                c_refl++;
+                if (SPLIT) c_refl++;
             }
             if ((FEAT & FEAT_TRANSPARENT) && push_refr) {
                 const uint64_t slot = base + (uint64_t)__popc(m_refl) + (uint64_t)__popc(m_refr & below);
@@ -263,21 +268,21 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRA
                     lv.out_q2[slot] = make_double2(r_refr.d.y, r_refr.d.z);
                     lv.out_q3[slot] = make_double2(w_refr, __longlong_as_double((long long)packed_fuel));
                 } else *lv.overflow = 2;
-                c_refr++;
+                if (SPLIT) c_refr++;
             }
         }
     }
-    flush_tally(tally, lv.stats, lane);
+    if (TALLY) flush_tally(tally, lv.stats, lane);
     for (int off = 16; off; off >>= 1) {
-        longest = max(longest, __shfl_down_sync(0xffffffffu, longest, off));
-        c_refl += __shfl_down_sync(0xffffffffu, c_refl, off);
-        c_refr += __shfl_down_sync(0xffffffffu, c_refr, off);
-        c_active += __shfl_down_sync(0xffffffffu, c_active, off);
+        if (TALLY) longest = max(longest, __shfl_down_sync(0xffffffffu, longest, off));
+        if (SPLIT) c_refl += __shfl_down_sync(0xffffffffu, c_refl, off);
+        if (SPLIT) c_refr += __shfl_down_sync(0xffffffffu, c_refr, off);
+        if (PRIMARY) c_active += __shfl_down_sync(0xffffffffu, c_active, off);
     }
     if (lane == 0) {
-        if (longest) atomicMax(lv.stats + 7, (unsigned long long)longest);
-        if (c_refl) atomicAdd(lv.stats + 1, (unsigned long long)c_refl);
-        if (c_refr) atomicAdd(lv.stats + 2, (unsigned long long)c_refr);
+        if (TALLY && longest) atomicMax(lv.stats + 7, (unsigned long long)longest);
+        if (SPLIT && c_refl) atomicAdd(lv.stats + 1, (unsigned long long)c_refl);
+        if (SPLIT && c_refr) atomicAdd(lv.stats + 2, (unsigned long long)c_refr);
         if (PRIMARY && c_active) atomicAdd(lv.stats + 0, (unsigned long long)c_active);
     }
 }
@@ -318,7 +323,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADOW_MIN_BLOCKS) trace_shadow
         }
         lv.shadow[i] = shadowed ? 1 : 0;
     }
-    flush_tally(tally, lv.stats, threadIdx.x & 31u);
+    if (FEAT & FEAT_TALLY) flush_tally(tally, lv.stats, threadIdx.x & 31u);
 }
 
 // ---- kernel 3: shading of one level's hits -------------------------------------------------------------------
@@ -412,22 +417,33 @@ static void launch_trace_feat(bool primary, int grid, cudaStream_t st, const Sce
     if (primary) trace_spawn<FEAT, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     else trace_spawn<FEAT, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
 }
+template <int TALLY>
+static void launch_trace_tally(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+    if (feat & (FEAT_CSG | FEAT_GATES)) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES | TALLY>(primary, grid, st, sc, f, lv, hl);
+    else if (feat & FEAT_TRANSPARENT) launch_trace_feat<FEAT_TRANSPARENT | TALLY>(primary, grid, st, sc, f, lv, hl);
+    else launch_trace_feat<TALLY>(primary, grid, st, sc, f, lv, hl);
+}
+// feat: the scene's FEAT_* bits, plus FEAT_TALLY when the caller wants the work counted
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
-    if (feat & (FEAT_CSG | FEAT_GATES)) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES>(primary, grid, st, sc, f, lv, hl);
-    else if (feat & FEAT_TRANSPARENT) launch_trace_feat<FEAT_TRANSPARENT>(primary, grid, st, sc, f, lv, hl);
-    else launch_trace_feat<0>(primary, grid, st, sc, f, lv, hl);
+    if (feat & FEAT_TALLY) launch_trace_tally<FEAT_TALLY>(feat, primary, grid, st, sc, f, lv, hl);
+    else launch_trace_tally<0>(feat, primary, grid, st, sc, f, lv, hl);
 }
 
-void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
-    if (sc.n_lights == 0) return;
+template <int TALLY>
+static void launch_shadow_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
     if (sc.all_cast_shadow) {
-        if (full) trace_shadow<FEAT_CSG | FEAT_GATES, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else trace_shadow<0, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     } else {
-        if (full) trace_shadow<FEAT_CSG | FEAT_GATES, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else trace_shadow<0, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     }
+}
+void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+    if (sc.n_lights == 0) return;
+    if (feat & FEAT_TALLY) launch_shadow_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv, hl);
+    else launch_shadow_tally<0>(feat, grid, st, sc, f, lv, hl);
 }
 
 void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {

@@ -560,6 +560,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     CU(cudaEventRecord(ctx.ev[0], st0));
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
+    const int feat = s->feat | (profile ? rtcdev::FEAT_TALLY : 0);  // the work tallies are counted under RTC_FLAG_PROFILE only
     uint64_t launches = 0;
     const bool timeline = std::getenv("RTC_TIMELINE") != nullptr;  // debugging aid: when each batch's kernels / copy finished
     std::vector<cudaEvent_t> tl_events;
@@ -607,9 +608,9 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         const int grid0 = (int)std::min<uint64_t>((uint64_t)grid_full, (npix * f.spp + RTC_BLOCK - 1) / RTC_BLOCK);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(-1); }
         for (int level = 0; level <= o.fuel; ++level)  // the chain: level k+1 depends on level k only
-            rtcdev::launch_trace(s->feat, level == 0, level == 0 ? grid0 : grid_full, st, s->dev, f, level_params(level), hits);
+            rtcdev::launch_trace(feat, level == 0, level == 0 ? grid0 : grid_full, st, s->dev, f, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
-        rtcdev::launch_shadow(s->feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
+        rtcdev::launch_shadow(feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
         for (int level = 0; level <= o.fuel; ++level)  // in level order: a sample's terms are added in a fixed order
             rtcdev::launch_shade(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
@@ -684,7 +685,9 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         double ref = 0.0;
         for (uint64_t b = 0; b < n_batches; ++b) {
             const unsigned long long* c = ctx.counters_host + b * COUNTERS_PER_BATCH;
-            primary += c[32]; refl += c[33]; refr += c[34];
+            primary += c[32];
+            if (s->feat & rtcdev::FEAT_TRANSPARENT) { refl += c[33]; refr += c[34]; }
+            else for (int level = 1; level <= o.fuel; ++level) refl += std::min<uint64_t>(c[level], q_cap);  // every child is a reflection
             for (int k = 0; k < 4; ++k) tally[k] += c[35 + k];
             longest = std::max<uint64_t>(longest, c[39]);
             mult = 1.0;
