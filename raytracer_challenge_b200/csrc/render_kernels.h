@@ -8,7 +8,7 @@
 #define RTC_BLOCK 128
 // resident blocks per SM the compiler must allow for (register cap = 65536 / (128 * blocks))
 #ifndef RTC_TRACE_MIN_BLOCKS
-#define RTC_TRACE_MIN_BLOCKS 6
+#define RTC_TRACE_MIN_BLOCKS 7
 #endif
 #ifndef RTC_SHADOW_MIN_BLOCKS
 #define RTC_SHADOW_MIN_BLOCKS 8
