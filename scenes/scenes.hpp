@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <initializer_list>
 #include <optional>
 #include <stdexcept>
 #include <string>
@@ -546,10 +547,250 @@ Scene<A> fuzz(uint64_t seed, size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- §8(f)-4: the remaining example binaries (title images and the cover) ----------------------
+// `Material { pattern, <fields>, ..Material::default() }` of the bins as one expression.
+// keys: a ambient, d diffuse, s specular, h shininess, r reflective, t transparency, i refractive_index
+template <class A>
+typename A::Material material_with(const typename A::Pattern& pattern, std::initializer_list<std::pair<char, double>> fields) {
+    typename A::Material m;
+    m.pattern = pattern;
+    for (const auto& f : fields) {
+        switch (f.first) {
+            case 'a': m.ambient = f.second; break;
+            case 'd': m.diffuse = f.second; break;
+            case 's': m.specular = f.second; break;
+            case 'h': m.shininess = f.second; break;
+            case 'r': m.reflective = f.second; break;
+            case 't': m.transparency = f.second; break;
+            case 'i': m.refractive_index = f.second; break;
+            default: throw std::runtime_error("scenes: unknown material field key");
+        }
+    }
+    return m;
+}
+template <class A>
+typename A::ShapeArgs shape_args(const typename A::Matrix& transform, const typename A::Material& material) {
+    typename A::ShapeArgs a;
+    a.transform = transform;
+    a.material = material;
+    return a;
+}
+
+// src/bin/chapter11_title.rs:15-198 (native 4096x2160): six planes, four matte + one shiny + two glass spheres
+template <class A>
+Scene<A> chapter11_title(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    auto plain = [](double r, double g, double b) { return P::plain(C::make(r, g, b)); };
+    const auto wall_material = material_with<A>(
+        P::stripes(M::scaling(0.25, 0.25, 0.25) * M::rotation_y(PI / 2.0), plain(0.45, 0.45, 0.45), plain(0.55, 0.55, 0.55)),
+        {{'a', 0.0}, {'d', 0.4}, {'s', 0.0}, {'r', 0.3}});
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::rotation_y(0.31415),
+                                        material_with<A>(P::checkers(M::id(), plain(0.35, 0.35, 0.35), plain(0.65, 0.65, 0.65)), {{'s', 0.0}, {'r', 0.4}}))));
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, 5.0, 0.0), material_with<A>(plain(0.8, 0.8, 0.8), {{'a', 0.3}, {'s', 0.0}}))));
+    el.push_back(E::plane(shape_args<A>(M::translation(-5.0, 0.0, 0.0) * M::rotation_z(PI / 2.0) * M::rotation_y(PI / 2.0), wall_material)));
+    el.push_back(E::plane(shape_args<A>(M::translation(5.0, 0.0, 0.0) * M::rotation_z(PI / 2.0) * M::rotation_y(PI / 2.0), wall_material)));
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, 0.0, 5.0) * M::rotation_x(PI / 2.0), wall_material)));
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, 0.0, -5.0) * M::rotation_x(PI / 2.0), wall_material)));
+    el.push_back(E::sphere(shape_args<A>(M::translation(4.6, 0.4, 1.0) * M::scaling(0.4, 0.4, 0.4), material_with<A>(plain(0.8, 0.5, 0.3), {{'h', 50.0}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(4.7, 0.3, 0.4) * M::scaling(0.3, 0.3, 0.3), material_with<A>(plain(0.9, 0.4, 0.5), {{'h', 50.0}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(-1.0, 0.5, 4.5) * M::scaling(0.5, 0.5, 0.5), material_with<A>(plain(0.4, 0.9, 0.6), {{'h', 50.0}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(-1.7, 0.3, 4.7) * M::scaling(0.3, 0.3, 0.3), material_with<A>(plain(0.4, 0.6, 0.9), {{'h', 50.0}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(-0.6, 1.0, 0.6), material_with<A>(plain(1.0, 0.3, 0.2), {{'s', 0.4}, {'h', 5.0}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(0.6, 0.7, -0.6) * M::scaling(0.7, 0.7, 0.7),
+                                         material_with<A>(plain(0.0, 0.0, 0.2), {{'a', 0.0}, {'d', 0.4}, {'s', 0.9}, {'h', 300.0}, {'r', 0.9}, {'t', 0.9}, {'i', 1.5}}))));
+    el.push_back(E::sphere(shape_args<A>(M::translation(-0.7, 0.5, -0.8) * M::scaling(0.5, 0.5, 0.5),
+                                         material_with<A>(plain(0.0, 0.2, 0.0), {{'a', 0.0}, {'d', 0.4}, {'s', 0.9}, {'h', 300.0}, {'r', 0.9}, {'t', 0.9}, {'i', 1.5}}))));
+    s.world.lights.push_back({C::white(), V::point(-4.9, 4.9, -1.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.152,
+                               A::Camera::transform(V::point(-2.6, 1.5, -3.9), V::point(-0.6, 1.0, -0.8), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// src/bin/chapter12_title.rs:15-281 (native 4096x2160): a room made of two huge cubes, a table, a glass cube, a mirror
+template <class A>
+Scene<A> chapter12_title(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    auto plain = [](double r, double g, double b) { return P::plain(C::make(r, g, b)); };
+    auto& el = s.world.elements;
+    el.push_back(E::cube(shape_args<A>(M::scaling(20.0, 7.0, 20.0) * M::translation(0.0, 1.0, 0.0),
+                                       material_with<A>(P::checkers(M::scaling(0.07, 0.07, 0.07), P::plain(C::black()), plain(0.25, 0.25, 0.25)),
+                                                        {{'a', 0.25}, {'d', 0.7}, {'s', 0.9}, {'h', 300.0}, {'r', 0.1}}))));
+    el.push_back(E::cube(shape_args<A>(M::scaling(10.0, 10.0, 10.0),
+                                       material_with<A>(P::checkers(M::scaling(0.05, 20.0, 0.05), plain(0.4863, 0.3765, 0.2941), plain(0.3725, 0.2902, 0.2275)),
+                                                        {{'a', 0.1}, {'d', 0.7}, {'s', 0.9}, {'h', 300.0}, {'r', 0.1}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(0.0, 3.1, 0.0) * M::scaling(3.0, 0.1, 2.0),
+                                       material_with<A>(P::stripes(M::rotation_y(0.1) * M::scaling(0.05, 0.05, 0.05), plain(0.5529, 0.4235, 0.3255), plain(0.6588, 0.5098, 0.4000)),
+                                                        {{'a', 0.1}, {'d', 0.7}, {'s', 0.9}, {'h', 300.0}, {'r', 0.2}}))));
+    const auto leg_material = material_with<A>(plain(0.5529, 0.4235, 0.3255), {{'a', 0.2}, {'d', 0.7}});
+    const double legs[4][2] = {{2.7, -1.7}, {2.7, 1.7}, {-2.7, -1.7}, {-2.7, 1.7}};
+    for (const auto& l : legs) el.push_back(E::cube(shape_args<A>(M::translation(l[0], 1.5, l[1]) * M::scaling(0.1, 1.5, 0.1), leg_material)));
+    el.push_back(E::cube(shape_args<A>(M::translation(0.0, 3.45001, 0.0) * M::rotation_y(0.2) * M::scaling(0.25, 0.25, 0.25),
+                                       material_with<A>(plain(1.0, 1.0, 0.8), {{'a', 0.0}, {'d', 0.3}, {'s', 0.9}, {'h', 300.0}, {'r', 0.7}, {'t', 0.7}, {'i', 1.5}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(1.0, 3.35, -0.9) * M::rotation_y(-0.4) * M::scaling(0.15, 0.15, 0.15),
+                                       material_with<A>(plain(1.0, 0.5, 0.5), {{'r', 0.6}, {'d', 0.4}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-1.5, 3.27, 0.3) * M::rotation_y(0.4) * M::scaling(0.15, 0.07, 0.15), material_with<A>(plain(1.0, 1.0, 0.5), {}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(0.0, 3.25, 1.0) * M::rotation_y(0.4) * M::scaling(0.2, 0.05, 0.05), material_with<A>(plain(0.5, 1.0, 0.5), {}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-0.6, 3.4, -1.0) * M::rotation_y(0.8) * M::scaling(0.05, 0.2, 0.05), material_with<A>(plain(0.5, 0.5, 1.0), {}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(2.0, 3.4, 1.0) * M::rotation_y(0.8) * M::scaling(0.05, 0.2, 0.05), material_with<A>(plain(0.5, 1.0, 1.0), {}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-10.0, 4.0, 1.0) * M::scaling(0.05, 1.0, 1.0), material_with<A>(plain(0.7098, 0.2471, 0.2196), {{'d', 0.6}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-10.0, 3.4, 2.7) * M::scaling(0.05, 0.4, 0.4), material_with<A>(plain(0.2667, 0.2706, 0.6902), {{'d', 0.6}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-10.0, 4.6, 2.7) * M::scaling(0.05, 0.4, 0.4), material_with<A>(plain(0.3098, 0.5961, 0.3098), {{'d', 0.6}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-2.0, 3.5, 9.95) * M::scaling(5.0, 1.5, 0.05), material_with<A>(plain(0.3882, 0.2627, 0.1882), {{'d', 0.6}}))));
+    el.push_back(E::cube(shape_args<A>(M::translation(-2.0, 3.5, 9.95) * M::scaling(4.8, 1.4, 0.06),
+                                       material_with<A>(P::plain(C::black()), {{'a', 0.0}, {'d', 0.0}, {'s', 1.0}, {'h', 300.0}, {'r', 1.0}}))));
+    s.world.lights.push_back({C::make(1.0, 1.0, 0.9), V::point(0.0, 6.9, -5.0)});
+    s.camera = A::Camera::make(hsize, vsize, 0.785,
+                               A::Camera::transform(V::point(8.0, 6.0, -8.0), V::point(0.0, 3.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// src/bin/chapter13_title.rs:14-248 (native 4096x2160): open / closed / concentric cylinders and a glass one
+template <class A>
+Scene<A> chapter13_title(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    auto plain = [](double r, double g, double b) { return P::plain(C::make(r, g, b)); };
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::id(), material_with<A>(P::checkers(M::rotation_y(0.3) * M::scaling(0.25, 0.25, 0.25), plain(0.5, 0.5, 0.5), plain(0.75, 0.75, 0.75)),
+                                                                  {{'a', 0.2}, {'d', 0.9}, {'s', 0.0}}))));
+    el.push_back(E::cylinder(shape_args<A>(M::translation(-1.0, 0.0, 1.0) * M::scaling(0.5, 1.0, 0.5),
+                                           material_with<A>(plain(0.0, 0.0, 0.6), {{'d', 0.1}, {'s', 0.9}, {'h', 300.0}, {'r', 0.9}})),
+                             0.0, 0.75, true));
+    const double concentric[4][5] = {{0.8, 1.0, 1.0, 0.3, 0.2}, {0.6, 1.0, 0.9, 0.4, 0.3}, {0.4, 1.0, 0.8, 0.5, 0.4}, {0.2, 1.0, 0.7, 0.6, 0.5}};
+    for (int k = 0; k < 4; ++k) {
+        const auto& c = concentric[k];
+        el.push_back(E::cylinder(shape_args<A>(M::translation(1.0, 0.0, 0.0) * M::scaling(c[0], 1.0, c[0]),
+                                               material_with<A>(plain(c[1], c[2], c[3]), {{'a', 0.1}, {'d', 0.8}, {'s', 0.9}, {'h', 300.0}})),
+                                 0.0, c[4], k == 3));
+    }
+    const auto deco_fields = std::initializer_list<std::pair<char, double>>{{'a', 0.1}, {'d', 0.9}, {'s', 0.9}, {'h', 300.0}};
+    el.push_back(E::cylinder(shape_args<A>(M::translation(0.0, 0.0, -0.75) * M::scaling(0.05, 1.0, 0.05), material_with<A>(plain(1.0, 0.0, 0.0), deco_fields)), 0.0, 0.3, true));
+    el.push_back(E::cylinder(shape_args<A>(M::translation(0.0, 0.0, -2.25) * M::rotation_y(-0.15) * M::translation(0.0, 0.0, 1.5) * M::scaling(0.05, 1.0, 0.05),
+                                           material_with<A>(plain(1.0, 1.0, 0.0), deco_fields)), 0.0, 0.3, true));
+    el.push_back(E::cylinder(shape_args<A>(M::translation(0.0, 0.0, -2.25) * M::rotation_y(-0.3) * M::translation(0.0, 0.0, 1.5) * M::scaling(0.05, 1.0, 0.05),
+                                           material_with<A>(plain(0.0, 1.0, 0.0), deco_fields)), 0.0, 0.3, true));
+    el.push_back(E::cylinder(shape_args<A>(M::translation(0.0, 0.0, -2.25) * M::rotation_y(-0.45) * M::translation(0.0, 0.0, 1.5) * M::scaling(0.05, 1.0, 0.05),
+                                           material_with<A>(plain(0.0, 1.0, 1.0), deco_fields)), 0.0, 0.3, true));
+    el.push_back(E::cylinder(shape_args<A>(M::translation(0.0, 0.0, -1.5) * M::scaling(0.33, 1.0, 0.33),
+                                           material_with<A>(plain(0.25, 0.0, 0.0), {{'d', 0.1}, {'s', 0.9}, {'h', 300.0}, {'r', 0.9}, {'t', 0.9}, {'i', 1.5}})),
+                             0.0001, 0.5, true));
+    s.world.lights.push_back({C::white(), V::point(1.0, 6.9, -4.9)});
+    s.camera = A::Camera::make(hsize, vsize, 0.314,
+                               A::Camera::transform(V::point(8.0, 3.5, -9.0), V::point(0.0, 0.3, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// src/bin/chapter14_title.rs:14-165 (native 4096x2160): three "wacky" groups (6 legs + 2 caps of 6 open cones), FOUR lights
+template <class A>
+Scene<A> chapter14_title(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto leg = [](const typename A::Matrix& transform) {
+        typename A::ShapeArgs sphere;
+        sphere.transform = M::translation(0.0, 0.0, -1.0) * M::scaling(0.25, 0.25, 0.25);
+        typename A::ShapeArgs cylinder;
+        cylinder.transform = M::translation(0.0, 0.0, -1.0) * M::rotation_y(-0.5236) * M::rotation_z(-1.5708) * M::scaling(0.25, 1.0, 0.25);
+        std::vector<E> parts;
+        parts.push_back(E::sphere(sphere));
+        parts.push_back(E::cylinder(cylinder, 0.0, 1.0, false));
+        return E::composite(transform, std::nullopt, G::Aggregation, std::move(parts));
+    };
+    auto cap = [](const typename A::Matrix& transform) {
+        std::vector<E> cones;
+        for (int i = 0; i < 6; i++) {
+            typename A::ShapeArgs a;
+            a.transform = M::rotation_y(PI / 3.0 * (double)i) * M::rotation_x(-0.7854) * M::scaling(0.24606, 1.37002, 0.24606);
+            cones.push_back(E::cone(a, -1.0, 0.0, false));
+        }
+        return E::composite(transform, std::nullopt, G::Aggregation, std::move(cones));
+    };
+    auto wacky = [&](const typename A::Matrix& transform, const typename A::Material& material) {
+        std::vector<E> elements;
+        for (int i = 0; i < 6; i++) elements.push_back(leg(M::rotation_y(PI / 3.0 * (double)i)));
+        elements.push_back(cap(M::translation(0.0, 1.0, 0.0)));
+        elements.push_back(cap(M::rotation_x(PI) * M::translation(0.0, 1.0, 0.0)));
+        return E::composite(transform, material, G::Aggregation, std::move(elements));
+    };
+    auto body = [](double r, double g, double b) {
+        return material_with<A>(P::plain(C::make(r, g, b)), {{'a', 0.2}, {'d', 0.8}, {'s', 0.7}, {'h', 20.0}});
+    };
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, 0.0, 100.0) * M::rotation_x(1.5708),
+                                        material_with<A>(P::plain(C::white()), {{'a', 1.0}, {'d', 0.0}, {'s', 0.0}}))));
+    el.push_back(wacky(M::translation(-2.8, 0.0, 0.0) * M::rotation_x(0.4363) * M::rotation_y(0.1745), body(0.9, 0.2, 0.4)));
+    el.push_back(wacky(M::rotation_y(0.1745), body(0.2, 0.9, 0.6)));
+    el.push_back(wacky(M::translation(2.8, 0.0, 0.0) * M::rotation_x(-0.4363) * M::rotation_y(-0.1745), body(0.2, 0.3, 1.0)));
+    const double sx[4] = {1.0, -1.0, 1.0, -1.0}, sy[4] = {1.0, 1.0, -1.0, -1.0};
+    for (int k = 0; k < 4; ++k) s.world.lights.push_back({C::make(0.25, 0.25, 0.25), V::point(sx[k] * 10000.0, sy[k] * 10000.0, -10000.0)});
+    s.camera = A::Camera::make(hsize, vsize, 0.9,
+                               A::Camera::transform(V::point(0.0, 0.0, -9.0), V::point(0.0, 0.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// src/bin/cover.rs:14-223 (native 4096x4096): a glass sphere and 17 cubes in nested groups, two lights
+template <class A>
+Scene<A> cover(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto tinted = [](const typename A::Pattern& p) { return material_with<A>(p, {{'d', 0.7}, {'a', 0.1}, {'s', 0.0}, {'r', 0.1}}); };
+    const auto white = tinted(P::plain(C::white()));
+    const auto blue = tinted(P::plain(C::make(0.537, 0.831, 0.914)));
+    const auto red = tinted(P::plain(C::make(0.941, 0.322, 0.388)));
+    const auto purple = tinted(P::plain(C::make(0.373, 0.404, 0.550)));
+    const auto standard_transform = M::scaling(0.5, 0.5, 0.5) * M::translation(1.0, -1.0, 1.0);
+    const auto large_object = M::scaling(3.5, 3.5, 3.5) * standard_transform;
+    const auto medium_object = M::scaling(3.0, 3.0, 3.0) * standard_transform;
+    const auto small_object = M::scaling(2.0, 2.0, 2.0) * standard_transform;
+    auto cube = [](double x, double y, double z, const typename A::Matrix& size, const typename A::Material& m) {
+        return E::cube(shape_args<A>(M::translation(x, y, z) * size, m));
+    };
+    std::vector<E> top;
+    top.push_back(E::sphere(shape_args<A>(large_object, material_with<A>(P::plain(C::make(0.373, 0.404, 0.550)),
+                                                                          {{'d', 0.2}, {'a', 0.0}, {'s', 1.0}, {'h', 200.0}, {'r', 0.7}, {'t', 0.7}, {'i', 1.5}}))));
+    top.push_back(cube(4.0, 0.0, 0.0, medium_object, white));
+    top.push_back(cube(8.5, 1.5, -0.5, large_object, blue));
+    top.push_back(cube(0.0, 0.0, 4.0, large_object, red));
+    top.push_back(cube(4.0, 0.0, 4.0, small_object, white));
+    top.push_back(cube(7.5, 0.5, 4.0, medium_object, purple));
+    top.push_back(cube(-0.25, 0.25, 8.0, medium_object, white));
+    top.push_back(cube(4.0, 1.0, 7.5, large_object, blue));
+    top.push_back(cube(10.0, 2.0, 7.5, medium_object, red));
+    top.push_back(cube(8.0, 2.0, 12.0, small_object, white));
+    top.push_back(cube(20.0, 1.0, 9.0, small_object, white));
+    std::vector<E> bot;
+    bot.push_back(cube(-0.5, -5.0, 0.25, large_object, blue));
+    bot.push_back(cube(4.0, -4.0, 0.0, large_object, red));
+    bot.push_back(cube(8.5, -4.0, 0.0, large_object, white));
+    bot.push_back(cube(0.0, -4.0, 4.0, large_object, white));
+    bot.push_back(cube(-0.5, -4.5, 8.0, large_object, purple));
+    bot.push_back(cube(0.0, -8.0, 4.0, large_object, white));
+    bot.push_back(cube(-0.5, -8.5, 8.0, large_object, white));
+    std::vector<E> all;
+    all.push_back(E::composite(M::id(), std::nullopt, G::Aggregation, std::move(top)));
+    all.push_back(E::composite(M::id(), std::nullopt, G::Aggregation, std::move(bot)));
+    s.world.elements.push_back(E::plane(shape_args<A>(M::translation(0.0, 0.0, 500.0) * M::rotation_x(PI / 2.0),
+                                                      material_with<A>(P::plain(C::white()), {{'a', 1.0}, {'d', 0.0}, {'s', 0.0}}))));
+    s.world.elements.push_back(E::composite(M::id(), std::nullopt, G::Aggregation, std::move(all)));
+    s.world.lights.push_back({C::white(), V::point(50.0, 100.0, -50.0)});
+    s.world.lights.push_back({C::make(0.2, 0.2, 0.2), V::point(-400.0, 50.0, -10.0)});
+    s.camera = A::Camera::make(hsize, vsize, 0.785,
+                               A::Camera::transform(V::point(-6.0, 6.0, -10.0), V::point(6.0, 0.0, 6.0), V::vector(-0.45, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
-                                               "benchmark",     "teapot",        "teapot_low",       "csg_noise"};
+                                               "benchmark",     "teapot",        "teapot_low",       "csg_noise",
+                                               "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover"};
     return n;
 }
 
@@ -564,6 +805,11 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "teapot") return teapot<A>(hsize, vsize);
     if (name == "teapot_low") return teapot_low<A>(hsize, vsize);
     if (name == "csg_noise") return csg_noise<A>(hsize, vsize);
+    if (name == "chapter11_title") return chapter11_title<A>(hsize, vsize);
+    if (name == "chapter12_title") return chapter12_title<A>(hsize, vsize);
+    if (name == "chapter13_title") return chapter13_title<A>(hsize, vsize);
+    if (name == "chapter14_title") return chapter14_title<A>(hsize, vsize);
+    if (name == "cover") return cover<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");
 }

@@ -23,6 +23,12 @@ CROPS = [
     ("hexagon", "hexagon", "chapter14_hexagon.png", [(2688, 800, 64, 32), (1300, 1150, 64, 32), (1728, 1440, 64, 32)]),
     ("benchmark", "benchmark", "chapter14_benchmark.png", [(2000, 1000, 96, 48), (1984, 1280, 64, 32), (100, 1900, 48, 24)]),
     ("teapot", "teapot", "chapter15_teapot.png", [(2040, 1100, 24, 12), (1560, 1560, 24, 12), (888, 576, 24, 12), (2304, 792, 24, 12)]),
+    # the remaining bins (glass spheres / cube / cylinder, cones, a mirror, 4 lights, nested groups)
+    ("chapter11_title", "chapter11_title", "chapter11_title.png", [(2300, 1300, 64, 32), (1500, 1450, 64, 32), (1900, 700, 48, 24), (3000, 1100, 48, 24)]),
+    ("chapter12_title", "chapter12_title", "chapter12_title.png", [(2030, 1000, 64, 32), (1200, 900, 48, 24), (2600, 1200, 48, 24), (700, 700, 48, 24)]),
+    ("chapter13_title", "chapter13_title", "chapter13_title.png", [(1500, 1100, 64, 32), (1050, 1250, 48, 24), (2700, 1300, 48, 24), (2000, 600, 48, 24)]),
+    ("chapter14_title", "chapter14_title", "chapter14_title.png", [(2040, 1060, 64, 32), (900, 800, 48, 24), (3100, 1300, 48, 24), (2040, 850, 48, 24)]),
+    ("cover", "cover", "cover.png", [(1700, 1700, 64, 32), (2600, 2000, 48, 24), (1200, 2800, 48, 24), (1500, 2700, 48, 24)]),
 ]
 
 

@@ -16,6 +16,12 @@ CASES = [
     ("benchmark", 192, 100),
     ("teapot_low", 96, 50),
     ("csg_noise", 160, 90),
+    # the remaining example binaries
+    ("chapter11_title", 192, 100),      # six planes, two glass spheres
+    ("chapter12_title", 192, 100),      # cubes only: a room, a glass cube, a mirror
+    ("chapter13_title", 192, 100),      # open / closed / glass cylinders
+    ("chapter14_title", 192, 100),      # open cones and cylinders in nested groups, four lights
+    ("cover", 128, 128),                # glass sphere + 17 cubes in nested groups, two lights
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
 
 

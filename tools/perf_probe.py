@@ -1,4 +1,4 @@
-"""Quick device-side timing of the named scenes (kernel ms, rays, Mrays/s).  Usage: perf_probe.py [scene WxH]..."""
+"""Quick device-side timing of the named scenes (kernel ms, rays, Mrays/s).  Usage: perf_probe.py [scene:WxH[:SXxSY]]..."""
 import sys, os, time, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import raytracer_challenge_b200 as R
@@ -10,20 +10,21 @@ if "--microbench" in cases:
     print(json.dumps(R.microbench()))
 cases = cases or DEFAULT
 for c in cases:
-    name, res = c.split(":")
+    name, res, *rest = c.split(":")
     w, h = map(int, res.split("x"))
+    spp = tuple(map(int, rest[0].split("x"))) if rest else (1, 1)
     t0 = time.time()
     s = R.Session(name, w, h, device=0)
     t_open = time.time() - t0
     best = None
     for i in range(4):
-        _, n, st = s.render_device(R.Opts())
+        _, n, st = s.render_device(R.Opts(spp=spp))
         if best is None or st.ms_kernels < best.ms_kernels:
             best = st
-    _, _, pr = s.render_device(R.Opts(flags=R.FLAG_PROFILE))
-    _, _, pr = s.render_device(R.Opts(flags=R.FLAG_PROFILE))
-    out, st2 = s.render(R.Opts())
-    print(json.dumps({"scene": name, "res": res, "open_s": round(t_open, 3), "ms_kernels": round(best.ms_kernels, 3), "rays": best.rays,
+    _, _, pr = s.render_device(R.Opts(spp=spp, flags=R.FLAG_PROFILE))
+    _, _, pr = s.render_device(R.Opts(spp=spp, flags=R.FLAG_PROFILE))
+    out, st2 = s.render(R.Opts(spp=spp))
+    print(json.dumps({"scene": name, "res": res, "spp": list(spp), "open_s": round(t_open, 3), "ms_kernels": round(best.ms_kernels, 3), "rays": best.rays,
                       "mrays_s": round(best.rays / best.ms_kernels / 1e3, 1), "rays_ref": best.rays_ref, "launches": best.kernel_launches,
                       "serial_ms": {"trace": round(pr.ms_trace, 3), "shadow": round(pr.ms_shadow, 3), "shade": round(pr.ms_shade, 3)}, "hits": best.surface_hits, "e2e_ms_total": round(st2.ms_total, 2), "d2h_ms": round(st2.ms_d2h, 2), "build": s.build_stats}))
     s.close()
