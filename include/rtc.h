@@ -216,7 +216,8 @@ void rtc_quantize(const double* rgb, uint8_t* out, uint64_t n);
 enum rtc_stat_key {
     RTC_STAT_PRIMS = 0, RTC_STAT_BVH_NODES = 1, RTC_STAT_BVH_DEPTH = 2, RTC_STAT_UNBOUNDED = 3,
     RTC_STAT_GATES_EXACT = 4, RTC_STAT_GATES_CONSERVATIVE = 5, RTC_STAT_GATES_ALWAYS_PASS = 6,
-    RTC_STAT_CSG_ROOTS = 7, RTC_STAT_XFORMS = 8, RTC_STAT_FEATURES = 9, RTC_STAT_BVH_ITEMS = 10, RTC_STAT_DEVICE_BYTES = 11
+    RTC_STAT_CSG_ROOTS = 7, RTC_STAT_XFORMS = 8, RTC_STAT_FEATURES = 9, RTC_STAT_BVH_ITEMS = 10, RTC_STAT_DEVICE_BYTES = 11,
+    RTC_STAT_CONE_GUARDS = 12
 };
 int64_t rtc_scene_stat(const rtc_scene* scene, int key);
 

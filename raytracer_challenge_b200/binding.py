@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_DIR = os.path.join(ROOT, "raytracer_challenge_b200", "lib")
 DATA_DIR = os.path.join(ROOT, "data")
 SCENES = ["default_world", "three_spheres", "glass_air_bubble", "hexagon", "benchmark", "teapot", "teapot_low", "csg_noise",
-          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover"]
+          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope"]
 
 
 class RtcError(RuntimeError):
@@ -52,7 +52,7 @@ class Stats(C.Structure):  # rtc_stats
 
 
 STAT_KEYS = ["prims", "bvh_nodes", "bvh_depth", "unbounded", "gates_exact", "gates_conservative", "gates_always_pass",
-             "csg_roots", "xforms", "features", "bvh_items", "device_bytes"]
+             "csg_roots", "xforms", "features", "bvh_items", "device_bytes", "cone_guards"]
 
 FLAG_BRUTE_FORCE, FLAG_PROFILE, FLAG_SCATTER_ROWS = 1, 2, 4
 

@@ -16,7 +16,7 @@ constexpr int BVH_STACK = 48;
 // Kernel feature bits (compile-time variants of the wavefront kernel)
 constexpr int FEAT_TRANSPARENT = 1;  // some material has transparency != 0: n1/n2 replay needed
 constexpr int FEAT_CSG = 2;          // CSG items present
-constexpr int FEAT_GATES = 4;        // group boxes that must be evaluated exactly
+constexpr int FEAT_GATES = 4;        // per-ray exact pre-tests: group boxes that must be evaluated exactly, cone guards
 constexpr int FEAT_TALLY = 8;        // RTC_FLAG_PROFILE: count the work done (node visits, primitive tests, ...); off, the counters and
                                      // their registers do not exist in the kernel
 
@@ -68,6 +68,15 @@ struct Gate {  // a group box that is neither always-passing nor provably conser
     double lo[3], hi[3];
 };
 
+// A cone with a finite range sits in the BVH under its finite box.  That box holds every crossing the reference can
+// emit EXCEPT the one of the single-root branch (|a| < EPSILON, src/shape.rs:811-818), which has no y-range check.
+// `a` depends only on the object-space direction, so a query first evaluates the reference's own expression per
+// guarded cone (linear part of Ray::transform, then a) and tests every item if one of them is below EPSILON.
+struct ConeGuard {
+    double lin[9];  // upper 3x3 of transform_inv, row-major
+    double pad;
+};  // 80 B, 16-byte aligned
+
 // BVH2 node, 64 B, two float4-aligned child boxes (outward-rounded, padded) + two child links.
 // link >= 0: inner node index; link < 0: leaf, ~link = (first_item << 2) | (count - 1), count <= 4.
 struct BvhNode {
@@ -114,14 +123,15 @@ struct Scene {
     const BvhNode* bvh;
     const LeafItem* leaf_items; // BVH items in leaf order
     const double* leaf_tri;     // 10 doubles per BVH item (triangles only: p1, e1, e2, pad), leaf order
-    const int32_t* unbounded;   // items tested for every ray (planes, cones, infinite cylinders, CSG holding one)
+    const int32_t* unbounded;   // items tested for every ray (planes, unbounded cones / cylinders, CSG holding one)
+    const ConeGuard* guards;    // one per distinct linear transform of the finite cones (see ConeGuard)
     const CsgOp* csg_ops;
     const CsgRoot* csg_roots;
     int32_t n_prims, n_lights, n_gates, n_unbounded, n_bvh_items, n_csg_roots;
     int32_t bvh_root;        // link of the root (may be a leaf); valid only if n_bvh_items > 0
     int32_t all_cast_shadow; // every primitive casts shadows -> shadow queries may stop at the first hit
     int32_t max_children;    // max over materials of (reflective != 0) + (transparency != 0)
-    int32_t pad;
+    int32_t n_guards;
     double root_lo[3], root_hi[3];  // f64 bounds of all BVH items (already padded)
 };
 

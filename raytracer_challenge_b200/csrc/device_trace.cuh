@@ -57,6 +57,29 @@ __device__ __forceinline__ uint32_t gates_passed(const Scene& sc, const Ray& ray
     return m;
 }
 
+// Finite cones are BVH items under finite boxes; the one crossing such a box may not hold belongs to the cone's
+// single-root branch, taken iff |a| < EPSILON with a = dx^2 - dy^2 + dz^2 of the OBJECT-space direction
+// (src/shape.rs:774-818).  This evaluates exactly what the reference evaluates — the direction half of Ray::transform
+// (src/ray.rs:14-19, same operation order as xf_dir) and then a — for every guarded cone transform; the result is
+// bit-identical, so "no guard fires" <=> no cone of the scene takes that branch for this ray, and the BVH result
+// equals the brute-force scan.  A ray that fires a guard (a band ~1e-6 rad wide around each cone's slope) simply
+// tests every item.
+template <int FEAT>
+__device__ __forceinline__ bool near_cone_slope(const Scene& sc, const Ray& ray) {
+    if (!(FEAT & FEAT_GATES)) return false;
+    bool fired = false;
+    for (int g = 0; g < sc.n_guards; ++g) {
+        const double2* q = reinterpret_cast<const double2*>(sc.guards + g);
+        const double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3), q4 = __ldg(q + 4);
+        const double dx = q0.x * ray.d.x + q0.y * ray.d.y + q1.x * ray.d.z;
+        const double dy = q1.y * ray.d.x + q2.x * ray.d.y + q2.y * ray.d.z;
+        const double dz = q3.x * ray.d.x + q3.y * ray.d.y + q4.x * ray.d.z;
+        const double a = dx * dx - dy * dy + dz * dz;
+        fired = fired || approx0(a);
+    }
+    return fired;
+}
+
 // Shared state of one query: the world ray, the object-space ray cache and the group-box gates it passed.
 template <int FEAT>
 struct Query {
@@ -328,6 +351,7 @@ struct ClosestVisitor {
 
 template <int FEAT>
 __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, Tally& tally, int* overflow) {
+    brute = brute || near_cone_slope<FEAT>(sc, ray);
     ClosestVisitor<FEAT> v(sc, ray, limit, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
     walk_bvh(sc, ray, 0, brute, v, tally);
@@ -376,6 +400,7 @@ struct AnyVisitor {
 // [0, dist)" and the walk may stop at the first such crossing.  (Scenes with non-casting shapes use closest_hit.)
 template <int FEAT>
 __device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, Tally& tally, int* overflow) {
+    brute = brute || near_cone_slope<FEAT>(sc, ray);
     AnyVisitor<FEAT> v(sc, ray, dist, tally, overflow);
     for (int i = 0; i < sc.n_unbounded; ++i)
         if (v.item(__ldg(sc.unbounded + i))) return v.found;
@@ -435,6 +460,7 @@ struct IndexCall {
 template <int FEAT>
 __device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit_t, int hit_prim, bool brute, int* overflow, IndexCall* call) {
     const Ray ray = call->ray;
+    brute = brute || near_cone_slope<FEAT>(sc, ray);
     Tally tally = {0u, 0u, 0u, 0u};
     double n1, n2;
     Cross xs[MAX_CROSSINGS];

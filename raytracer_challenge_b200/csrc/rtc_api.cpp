@@ -225,9 +225,10 @@ static int64_t host_stat(const rtchost::HostScene& h, int key) {
             bool transparent = false;
             for (auto& m : h.materials) transparent = transparent || m.transparency != 0.0;
             return (transparent ? rtcdev::FEAT_TRANSPARENT : 0) | (!h.csg_roots.empty() ? rtcdev::FEAT_CSG : 0) |
-                   (!h.gates.empty() ? rtcdev::FEAT_GATES : 0);
+                   (!h.gates.empty() || !h.guards.empty() ? rtcdev::FEAT_GATES : 0);
         }
         case RTC_STAT_DEVICE_BYTES: return h.device_bytes;
+        case RTC_STAT_CONE_GUARDS: return (int64_t)h.guards.size();
         default: return -1;
     }
 }
@@ -284,7 +285,7 @@ void rtc_release_device_memory(int device) {
 struct PackedScene {
     std::vector<unsigned char> blob;
     size_t o_prims, o_xforms, o_matinvs, o_tri_pe, o_tri_n, o_ranges, o_materials, o_patterns, o_lights, o_gates, o_bvh, o_leaf_items,
-        o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots;
+        o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots, o_guards;
 };
 static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     auto place = [&](const void* src, size_t bytes) -> size_t {
@@ -298,6 +299,7 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     p.o_tri_n = PLACE(h.tri_n); p.o_ranges = PLACE(h.ranges); p.o_materials = PLACE(h.materials); p.o_patterns = PLACE(h.patterns);
     p.o_lights = PLACE(h.lights); p.o_gates = PLACE(h.gates); p.o_bvh = PLACE(h.bvh); p.o_leaf_items = PLACE(h.leaf_items);
     p.o_leaf_tri = PLACE(h.leaf_tri); p.o_unbounded = PLACE(h.unbounded); p.o_csg_ops = PLACE(h.csg_ops); p.o_csg_roots = PLACE(h.csg_roots);
+    p.o_guards = PLACE(h.guards);
 #undef PLACE
     h.device_bytes = (int64_t)p.blob.size();
 }
@@ -346,6 +348,8 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     d.unbounded = (const int32_t*)(base + p.o_unbounded);
     d.csg_ops = (const rtcdev::CsgOp*)(base + p.o_csg_ops);
     d.csg_roots = (const rtcdev::CsgRoot*)(base + p.o_csg_roots);
+    d.guards = (const rtcdev::ConeGuard*)(base + p.o_guards);
+    d.n_guards = (int32_t)h.guards.size();
     d.n_prims = (int32_t)h.prims.size();
     d.n_lights = (int32_t)h.lights.size();
     d.n_gates = (int32_t)h.gates.size();

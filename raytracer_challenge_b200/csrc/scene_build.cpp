@@ -23,11 +23,13 @@ constexpr double INF = std::numeric_limits<double>::infinity();
 struct Box {
     double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
     bool bounded = true;  // false: must be tested for every ray
+    bool exact = true;    // false: holds a finite cone, whose single-root crossing may lie outside (see rtcdev::ConeGuard)
     void add(const double p[3]) {
         for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); }
     }
     void add(const Box& b) {
         if (!b.bounded) bounded = false;
+        if (!b.exact) exact = false;
         for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], b.lo[k]); hi[k] = std::max(hi[k], b.hi[k]); }
     }
     bool empty() const { return lo[0] > hi[0]; }
@@ -62,9 +64,10 @@ void xf_point(const double m[12], const double p[3], double out[3]) {
     for (int r = 0; r < 3; ++r) out[r] = m[r * 4] * p[0] + m[r * 4 + 1] * p[1] + m[r * 4 + 2] * p[2] + m[r * 4 + 3];
 }
 
-// World-space bounds of one primitive, or unbounded.  Planes (src/shape.rs:954-957), cylinders with an
-// infinite range and ALL cones are unbounded: a cone's single-root branch (src/shape.rs:811-818) has no
-// y-range check, so its crossings are not confined to [min, max].
+// World-space bounds of one primitive, or unbounded.  Planes (src/shape.rs:954-957) and cylinders / cones with an
+// infinite range are unbounded.  A cone with a finite range gets the box of its walls and caps, marked inexact: its
+// single-root branch (src/shape.rs:811-818) has no y-range check, so for the rare rays that take it the crossing is
+// not confined to [min, max] — those rays are detected per query (rtcdev::ConeGuard) and test every item.
 Box prim_bounds(const rtc_prim& p) {
     Box b;
     double fwd[12];
@@ -80,6 +83,14 @@ Box prim_bounds(const rtc_prim& p) {
             olo[0] = -1.0; ohi[0] = 1.0; olo[2] = -1.0; ohi[2] = 1.0;
             olo[1] = std::min(p.min, p.max); ohi[1] = std::max(p.min, p.max);
             break;
+        case RTC_CONE: {  // walls: x^2 + z^2 = y^2 with min < y < max; caps: radius |min|, |max| (src/shape.rs:767-822)
+            if (!std::isfinite(p.min) || !std::isfinite(p.max)) { b.bounded = false; return b; }
+            const double lim = std::max(std::fabs(p.min), std::fabs(p.max));
+            olo[0] = -lim; ohi[0] = lim; olo[2] = -lim; ohi[2] = lim;
+            olo[1] = std::min(p.min, p.max); ohi[1] = std::max(p.min, p.max);
+            b.exact = false;
+            break;
+        }
         case RTC_TRIANGLE:
         case RTC_SMOOTH_TRIANGLE: {
             double v[3][3];
@@ -87,7 +98,7 @@ Box prim_bounds(const rtc_prim& p) {
             for (auto& q : v) { double w[3]; xf_point(fwd, q, w); b.add(w); }
             goto pad;
         }
-        default:  // plane, cone
+        default:  // plane
             b.bounded = false;
             return b;
     }
@@ -501,6 +512,14 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         if (!p.casts_shadow) out.all_cast_shadow = 0;
         out.prims.push_back(q);
         prim_box[(size_t)i] = prim_bounds(p);
+        if (p.kind == RTC_CONE && prim_box[(size_t)i].bounded) {  // one guard per distinct linear part
+            rtcdev::ConeGuard g{};
+            for (int r = 0; r < 3; ++r)
+                for (int c = 0; c < 3; ++c) g.lin[r * 3 + c] = p.transform_inv[r * 4 + c];
+            bool seen = false;
+            for (const auto& o : out.guards) seen = seen || std::memcmp(&o, &g, sizeof g) == 0;
+            if (!seen) out.guards.push_back(g);
+        }
     }
 
     const auto t1 = now();
@@ -612,7 +631,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         }
         // a finite box that encloses everything below it can only reject rays that miss all of it: skip it
         if (gate_slot >= 0) {
-            bool conservative = sub.bounded;
+            bool conservative = sub.bounded && sub.exact;  // (a finite cone's single-root crossing may lie outside its box)
             for (int k = 0; k < 3 && conservative; ++k) {
                 const double lo = nd.bbox_min[k], hi = nd.bbox_max[k];
                 if (!std::isfinite(lo) || !std::isfinite(hi)) { conservative = false; break; }

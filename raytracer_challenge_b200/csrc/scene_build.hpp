@@ -26,6 +26,7 @@ struct HostScene {
     std::vector<rtcdev::LeafItem> leaf_items;
     std::vector<double> leaf_tri;
     std::vector<int32_t> unbounded;
+    std::vector<rtcdev::ConeGuard> guards;
     std::vector<rtcdev::CsgOp> csg_ops;
     std::vector<rtcdev::CsgRoot> csg_roots;
     int32_t bvh_root = 0;

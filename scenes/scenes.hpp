@@ -786,11 +786,39 @@ Scene<A> cover(size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- authored: rays parallel to a cone's slope (src/shape.rs:811-818) ---------------------------------
+// A narrow camera (use 33x33) looks exactly along the slope of finite cones, so the rows around the image centre take
+// the cone's single-root branch (|a| < EPSILON), whose crossing has no y-range check: it lies on the infinite double
+// cone, far outside [min, max].  Cone A is a top-level element: its phantom crossing is visible.  Cone B sits in a
+// group whose (finite) box the rays miss: the reference rejects it at the group box although its phantom crossing
+// would be nearer.  Rows further from the centre have |a| >= EPSILON and see the floor.
+template <class A>
+Scene<A> cone_slope(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, -10.0, 0.0),
+                                        material_with<A>(P::checkers(M::scaling(0.01, 0.01, 0.01), P::plain(C::make(0.9, 0.9, 0.9)), P::plain(C::make(0.2, 0.2, 0.3))), {{'s', 0.0}}))));
+    el.push_back(E::cone(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.9, 0.3, 0.2)), {{'r', 0.3}})), -1.0, 0.0, true));
+    std::vector<E> grouped;
+    grouped.push_back(E::cone(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.2, 0.9, 0.3)), {})), -1.0, 0.0, true));
+    el.push_back(E::composite(M::translation(0.0, 0.0, -3.0), std::nullopt, G::Aggregation, std::move(grouped)));
+    std::vector<E> csg;
+    csg.push_back(E::cone(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.2, 0.3, 0.9)), {})), -1.0, 0.0, true));
+    csg.push_back(E::sphere(shape_args<A>(M::translation(0.0, -0.5, 0.0) * M::scaling(0.6, 0.6, 0.6), material_with<A>(P::plain(C::make(0.9, 0.9, 0.2)), {}))));
+    el.push_back(E::composite(M::translation(6.0, -8.0, 0.3), std::nullopt, G::Difference, std::move(csg)));
+    s.world.lights.push_back({C::white(), V::point(-10.0, 20.0, -10.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1e-4,
+                               A::Camera::transform(V::point(-4.0, 5.5, 0.3), V::point(-3.0, 4.5, 0.3), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
-                                               "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover"};
+                                               "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope"};
     return n;
 }
 
@@ -810,6 +838,7 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "chapter13_title") return chapter13_title<A>(hsize, vsize);
     if (name == "chapter14_title") return chapter14_title<A>(hsize, vsize);
     if (name == "cover") return cover<A>(hsize, vsize);
+    if (name == "cone_slope") return cone_slope<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");
 }

@@ -83,6 +83,10 @@ def test_host_scene_build(built, name):
         assert b["csg_roots"] >= 1 and (b["features"] & 2)
     if name == "glass_air_bubble":
         assert b["features"] & 1
+    if name == "chapter14_title":  # 36 finite open cones: BVH items behind per-ray guards, only the backdrop plane is tested for every ray
+        assert b["unbounded"] == 1 and b["bvh_items"] == 72 and b["cone_guards"] == 36 and (b["features"] & 4)
+    if name == "cone_slope":  # boxes above a finite cone stay exact gates: its single-root crossing may lie outside them
+        assert b["cone_guards"] == 1 and b["gates_exact"] == 2 and b["gates_conservative"] == 0
 
 
 def _desc(lib_types, **over):

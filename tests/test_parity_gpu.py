@@ -22,6 +22,7 @@ CASES = [
     ("chapter13_title", 192, 100),      # open / closed / glass cylinders
     ("chapter14_title", 192, 100),      # open cones and cylinders in nested groups, four lights
     ("cover", 128, 128),                # glass sphere + 17 cubes in nested groups, two lights
+    ("cone_slope", 33, 33),             # rays along a cone's slope: the single-root branch without y-range check (src/shape.rs:811-818)
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
 
 
