@@ -95,6 +95,28 @@ __device__ __forceinline__ void isect_sphere(const Ray& r, Roots& out) {
     out.t[1] = (-b + sq) / (2.0 * a);
     out.n = 2;
 }
+// The same for a query that only wants crossings with t >= 0 and only the nearest of them (closest hit, shadow):
+// 2a > 0 and sq >= 0, so t0 <= t1 and the sign of t0 is the sign of its numerator.  If t0 >= 0 it is the answer and
+// t1 cannot beat it; if t0 < 0 only t1 can count.  One IEEE division instead of two; the quotient kept is the
+// reference's own.  (A numerator so small that the quotient could round to -0.0, which `t >= 0.0` accepts, and a
+// degenerate a take the two-root path.)
+__device__ __forceinline__ void isect_sphere_nearest(const Ray& r, Roots& out) {
+    const double a = dot(r.d, r.d);
+    const double b = 2.0 * dot(r.d, r.o);
+    const double c = dot(r.o, r.o) - 1.0;
+    const double disc = b * b - 4.0 * a * c;
+    if (disc < 0.0) return;
+    const double sq = sqrt(disc);
+    const double n0 = -b - sq;
+    if (!(a > 0.0) || (n0 < 0.0 && n0 > -1e-280)) {
+        out.t[0] = n0 / (2.0 * a);
+        out.t[1] = (-b + sq) / (2.0 * a);
+        out.n = 2;
+        return;
+    }
+    out.t[0] = (n0 >= 0.0 ? n0 : -b + sq) / (2.0 * a);
+    out.n = 1;
+}
 // src/shape.rs:622-633
 __device__ __forceinline__ void isect_plane(const Ray& r, Roots& out) {
     if (approx0(r.d.y)) return;
@@ -304,7 +326,8 @@ __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int 
         load_tri(tri_rec, p1, e1, e2);
         isect_triangle(r, p1, e1, e2, out);
     } else if ((HOT & 0x01) && kind == 0) {
-        isect_sphere(r, out);
+        if (skip_negative) isect_sphere_nearest(r, out);
+        else isect_sphere(r, out);
     } else {
         roots_generic(sc, kind_flags, geom, tri_rec, r, out);
     }

@@ -196,28 +196,34 @@ struct Walk {
 // mode 0: hits with t >= 0 (closest / shadow); mode 1: every crossing up to tmax (also negative t).
 // Returns false if the ray cannot touch any BVH item.
 __device__ __forceinline__ bool walk_setup(const Scene& sc, const Ray& ray, int mode, Walk& w) {
-    double tn = -CUDART_INF, tf = CUDART_INF;
+    // The root-box interval only decides where the fp32 walk is re-originated and whether the ray can be dropped
+    // without a walk — culling, not parity — so it is computed in fp32 (three f64 divisions less per query) and a ray
+    // is dropped only when it misses by more than the fp32 error of the interval ends (relative 2^-22 is ~10x the
+    // error of a subtract-convert-multiply chain).  The root box is padded like every other box.  Infinite or NaN
+    // ends (zero direction components) never reject: comparisons with NaN are false, fminf / fmaxf ignore NaN.
     const double o[3] = {ray.o.x, ray.o.y, ray.o.z}, d[3] = {ray.d.x, ray.d.y, ray.d.z};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const double inv = 1.0 / d[k];
-        const double a = (sc.root_lo[k] - o[k]) * inv, b = (sc.root_hi[k] - o[k]) * inv;
-        tn = fmax(tn, fmin(a, b));
-        tf = fmin(tf, fmax(a, b));
-    }
-    if (!(tn <= tf)) return false;
-    if (mode == 0) {
-        if (tf < 0.0) return false;
-        w.te = fmax(tn, 0.0);
-        w.tlo = __double2float_rd(-w.te);
-    } else {
-        w.te = fmin(fmax(0.0, tn), tf);
-        w.tlo = -CUDART_INF_F;
-    }
-    if (!(fabs(w.te) <= 1.7e308)) { w.te = 0.0; w.tlo = mode == 0 ? 0.0f : -CUDART_INF_F; }
     w.ix = 1.0f / (float)d[0];
     w.iy = 1.0f / (float)d[1];
     w.iz = 1.0f / (float)d[2];
+    const float inv[3] = {w.ix, w.iy, w.iz};
+    float tn = -CUDART_INF_F, tf = CUDART_INF_F;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float a = (float)(sc.root_lo[k] - o[k]) * inv[k], b = (float)(sc.root_hi[k] - o[k]) * inv[k];
+        tn = fmaxf(tn, fminf(a, b));
+        tf = fminf(tf, fmaxf(a, b));
+    }
+    const float slack = 2.4e-7f * (fminf(fabsf(tn), 1e30f) + fminf(fabsf(tf), 1e30f));  // (an infinite end still rejects)
+    if (tn - tf > slack) return false;
+    if (mode == 0) {
+        if (tf < -slack) return false;
+        w.te = (double)fmaxf(tn, 0.0f);
+        w.tlo = __double2float_rd(-w.te);
+    } else {
+        w.te = (double)fminf(fmaxf(0.0f, tn), tf);
+        w.tlo = -CUDART_INF_F;
+    }
+    if (!(fabs(w.te) <= 1.7e38)) { w.te = 0.0; w.tlo = mode == 0 ? 0.0f : -CUDART_INF_F; }
     // One fused multiply-add per plane instead of a subtract and a multiply (explicit: the build has -fmad=false for
     // the f64 code).  The extra rounding of p is <= 2^-24 |o| in distance, far inside the padding of the boxes
     // ("conservative fp32 culling").  A zero direction component gives inf - inf = NaN, which the

@@ -155,7 +155,7 @@ __device__ __forceinline__ uint32_t hit_prefix(const HitList& hl, uint32_t* firs
 // queue (src/world.rs:66-78,84-132) — so the next level depends on this kernel only, and the shadow / shading work
 // of all levels is done afterwards in two fat launches.
 template <int FEAT, bool PRIMARY>
-__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRACE_MIN_BLOCKS_TRANSPARENT : RTC_TRACE_MIN_BLOCKS) trace_spawn(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_BLOCKS_CSG : (FEAT & FEAT_TRANSPARENT) ? RTC_TRACE_MIN_BLOCKS_TRANSPARENT : RTC_TRACE_MIN_BLOCKS) trace_spawn(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
     const uint32_t n_in = level_rays<PRIMARY>(lv);
     const unsigned lane = threadIdx.x & 31u;
@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_TRANSPARENT) ? RTC_TRA
 // Light-major: consecutive threads take consecutive hits towards the SAME light, so a warp's rays start next to each
 // other and head the same way.  Reads 24 B (over_point) per thread, coalesced; writes one byte.
 template <int FEAT, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADOW_MIN_BLOCKS) trace_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) trace_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
     uint32_t first[MAX_LEVELS + 1];
     const uint32_t n_hits = hit_prefix(hl, first);

@@ -16,6 +16,12 @@
 #ifndef RTC_TRACE_MIN_BLOCKS_TRANSPARENT  // the n1/n2 replay keeps more state alive: trade occupancy for no spills
 #define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 3
 #endif
+#ifndef RTC_TRACE_MIN_BLOCKS_CSG  // CSG evaluation on top of that
+#define RTC_TRACE_MIN_BLOCKS_CSG 3
+#endif
+#ifndef RTC_SHADOW_MIN_BLOCKS_CSG
+#define RTC_SHADOW_MIN_BLOCKS_CSG 8
+#endif
 #ifndef RTC_SHADE_MIN_BLOCKS
 #define RTC_SHADE_MIN_BLOCKS 5
 #endif
