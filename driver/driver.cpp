@@ -5,6 +5,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <sstream>
 #include <memory>
 #include <string>
 
@@ -147,6 +149,81 @@ int64_t drv_par_render_ppm(const char* name, const char* data_dir, int hsize, in
         const std::string ppm = img.ppm();
         if ((int64_t)ppm.size() <= out_cap) std::memcpy(out, ppm.data(), ppm.size());
         return (int64_t)ppm.size();
+    } catch (const std::exception& e) {
+        set_err(err, errlen, e.what());
+        return -1;
+    }
+}
+
+// ---- host-only helpers for the CPU tests of the steps either side of the path ----
+
+// Image::ppm (kind 0) / Image::png (kind 1) of a caller-supplied f64 rgb image; returns the encoded length.
+int64_t drv_image_encode(const double* rgb, int hsize, int vsize, int kind, char* out, int64_t out_cap) {
+    rtc::Image img;
+    img.hsize = (size_t)hsize;
+    img.vsize = (size_t)vsize;
+    img.pixels.resize((size_t)hsize * (size_t)vsize);
+    for (size_t i = 0; i < img.pixels.size(); ++i) img.pixels[i] = rtc::Color{rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]};
+    const std::string s = kind == 0 ? img.ppm() : img.png();
+    if ((int64_t)s.size() <= out_cap) std::memcpy(out, s.data(), s.size());
+    return (int64_t)s.size();
+}
+
+// ObjParser::parse_text on a text buffer -> a JSON description of what the reference's `parse_lines` yields
+// (src/obj.rs:154-184): vertices, normals, fan-triangulated faces (1-based indices, normal indices or null, group),
+// group names in first-seen order, ignored (line number, text) pairs; plus the shape of the Element `parse_obj`
+// builds with the identity transform (src/obj.rs:186-258): triangles per non-empty group and whether they are wrapped.
+int64_t drv_obj_parse(const char* text, int64_t len, char* out, int64_t out_cap, char* err, int errlen) {
+    try {
+        std::istringstream in(std::string(text, (size_t)len));
+        const rtc::ObjData d = rtc::ObjParser::parse_text(in);
+        std::ostringstream o;
+        o.precision(17);
+        auto esc = [](const std::string& s) {
+            std::string r;
+            for (char c : s) {
+                if (c == '"' || c == '\\') { r.push_back('\\'); r.push_back(c); }
+                else if ((unsigned char)c < 0x20) { char b[8]; std::snprintf(b, sizeof b, "\\u%04x", c); r += b; }
+                else r.push_back(c);
+            }
+            return r;
+        };
+        o << "{\"vertices\":[";
+        for (size_t i = 0; i < d.vertices.size(); ++i) o << (i ? "," : "") << "[" << d.vertices[i].x << "," << d.vertices[i].y << "," << d.vertices[i].z << "," << d.vertices[i].w << "]";
+        o << "],\"normals\":[";
+        for (size_t i = 0; i < d.normals.size(); ++i) o << (i ? "," : "") << "[" << d.normals[i].x << "," << d.normals[i].y << "," << d.normals[i].z << "," << d.normals[i].w << "]";
+        o << "],\"triangles\":[";
+        for (size_t i = 0; i < d.triangles.size(); ++i) {
+            const auto& t = d.triangles[i];
+            o << (i ? "," : "") << "{\"p\":[" << t.p[0] << "," << t.p[1] << "," << t.p[2] << "],\"n\":";
+            if (t.has_n) o << "[" << t.n[0] << "," << t.n[1] << "," << t.n[2] << "]"; else o << "null";
+            o << ",\"group\":" << t.group << "}";
+        }
+        o << "],\"groups\":[";
+        for (size_t i = 0; i < d.groups.size(); ++i) o << (i ? "," : "") << "\"" << esc(d.groups[i]) << "\"";
+        o << "],\"ignored\":[";
+        for (size_t i = 0; i < d.ignored.size(); ++i) o << (i ? "," : "") << "[" << d.ignored[i].first << ",\"" << esc(d.ignored[i].second) << "\"]";
+        o << "],\"element\":";
+        if (d.triangles.empty()) o << "null";
+        else {
+            const rtc::Element e = rtc::ObjParser::build(d, rtc::Matrix::id(), rtc::Material{});
+            std::function<void(const rtc::Element&)> dump = [&](const rtc::Element& el) {
+                if (!el.is_group()) {
+                    const rtc::Shape& s = std::get<rtc::Shape>(el.node);
+                    o << "{\"kind\":" << s.kind << ",\"p\":[[" << s.p1.x << "," << s.p1.y << "," << s.p1.z << "],[" << s.p2.x << "," << s.p2.y << "," << s.p2.z << "],[" << s.p3.x << "," << s.p3.y << "," << s.p3.z << "]]}";
+                    return;
+                }
+                const rtc::Group& g = std::get<rtc::Group>(el.node);
+                o << "{\"group\":" << (int)g.kind << ",\"children\":[";
+                for (size_t i = 0; i < g.children.size(); ++i) { if (i) o << ","; dump(g.children[i]); }
+                o << "]}";
+            };
+            dump(e);
+        }
+        o << "}";
+        const std::string s = o.str();
+        if ((int64_t)s.size() <= out_cap) std::memcpy(out, s.data(), s.size());
+        return (int64_t)s.size();
     } catch (const std::exception& e) {
         set_err(err, errlen, e.what());
         return -1;

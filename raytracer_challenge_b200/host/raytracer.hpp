@@ -12,6 +12,7 @@
 // Rust crate would hold; all per-pixel work happens on the GPU behind include/rtc.h.
 #pragma once
 
+#include <algorithm>
 #include <array>
 #include <cmath>
 #include <cstdint>
@@ -723,6 +724,79 @@ class Image {
         }
         out << "\n";
         return out.str();
+    }
+
+    // The reference's bins write `<name>.ppm` and then shell out to `zsh -c "pnmtopng <name>.ppm > <name>.png"`
+    // (e.g. src/bin/chapter15_teapot.rs:96-120); neither zsh nor netpbm exists on the GPU box, so the PNG is encoded
+    // here: 8-bit RGB (colour type 2) of the same Color::clamp triples the PPM holds, rows filtered with "None",
+    // zlib stream of stored (uncompressed) deflate blocks — decodes to exactly the pixels of `pnmtopng`'s output.
+    std::string png() const {
+        std::string raw;
+        raw.reserve(vsize * (1 + 3 * hsize));
+        for (size_t y = 0; y < vsize; ++y) {
+            raw.push_back('\0');
+            for (size_t x = 0; x < hsize; ++x) {
+                const auto q = pixels[y * hsize + x].clamp();
+                raw.push_back((char)q[0]); raw.push_back((char)q[1]); raw.push_back((char)q[2]);
+            }
+        }
+        std::string z;
+        z.push_back((char)0x78); z.push_back((char)0x01);
+        uint32_t a = 1, b = 0;  // Adler-32 of the raw scanlines
+        for (size_t at = 0; at < raw.size() || at == 0;) {
+            const size_t n = std::min<size_t>(65535, raw.size() - at);
+            z.push_back((char)(at + n >= raw.size() ? 1 : 0));
+            z.push_back((char)(n & 0xff)); z.push_back((char)(n >> 8));
+            z.push_back((char)(~n & 0xff)); z.push_back((char)((~n >> 8) & 0xff));
+            for (size_t i = 0; i < n; ++i) {
+                a += (unsigned char)raw[at + i];
+                if (a >= 65521) a -= 65521;
+                b += a;
+                if (b >= 65521) b -= 65521;
+            }
+            z.append(raw, at, n);
+            at += n;
+            if (n == 0) break;
+        }
+        put_be32(z, (b << 16) | a);
+        std::string out("\x89PNG\r\n\x1a\n", 8);
+        std::string ihdr;
+        put_be32(ihdr, (uint32_t)hsize);
+        put_be32(ihdr, (uint32_t)vsize);
+        ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);
+        png_chunk(out, "IHDR", ihdr);
+        png_chunk(out, "IDAT", z);
+        png_chunk(out, "IEND", std::string());
+        return out;
+    }
+
+    // What a bin does after par_render (src/bin/*.rs): `<path>.ppm` as text, `<path>.png` next to it.
+    void save(const std::string& path) const {
+        std::ofstream(path + ".ppm", std::ios::binary) << ppm();
+        std::ofstream(path + ".png", std::ios::binary) << png();
+    }
+
+  private:
+    static void put_be32(std::string& s, uint32_t v) {
+        s.push_back((char)(v >> 24)); s.push_back((char)(v >> 16)); s.push_back((char)(v >> 8)); s.push_back((char)v);
+    }
+    static void png_chunk(std::string& out, const char* tag, const std::string& body) {
+        put_be32(out, (uint32_t)body.size());
+        std::string crc_in(tag, 4);
+        crc_in += body;
+        static const std::array<uint32_t, 256> table = [] {
+            std::array<uint32_t, 256> t{};
+            for (uint32_t i = 0; i < 256; ++i) {
+                uint32_t c = i;
+                for (int k = 0; k < 8; ++k) c = (c >> 1) ^ (0xedb88320u & (0u - (c & 1u)));
+                t[i] = c;
+            }
+            return t;
+        }();
+        uint32_t c = 0xffffffffu;
+        for (unsigned char ch : crc_in) c = table[(c ^ ch) & 0xffu] ^ (c >> 8);
+        out += crc_in;
+        put_be32(out, c ^ 0xffffffffu);
     }
 };
 
