@@ -297,15 +297,18 @@ __device__ __forceinline__ void roots_generic(const Scene& sc, int kind_flags, i
 // two dot products instead of the full Ray::transform, with the same expression order as xf_point / xf_dir, so o.y
 // and d.y are bit-identical.  skip_negative: the caller only wants crossings with t >= 0 (closest hit, shadow), so
 // the division is skipped when the signs of o.y and d.y already say t < 0.
-__device__ __forceinline__ void plane_roots(const Scene& sc, int xform, const Ray& world, bool skip_negative, Roots& out) {
-    const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv + 4);
-    const double2 a = __ldg(q), b = __ldg(q + 1);
-    const double oy = a.x * world.o.x + a.y * world.o.y + b.x * world.o.z + b.y;
-    const double dy = a.x * world.d.x + a.y * world.d.y + b.x * world.d.z;
+__device__ __forceinline__ void plane_roots_row(double r0, double r1, double r2, double r3, const Ray& world, bool skip_negative, Roots& out) {
+    const double oy = r0 * world.o.x + r1 * world.o.y + r2 * world.o.z + r3;
+    const double dy = r0 * world.d.x + r1 * world.d.y + r2 * world.d.z;
     if (approx0(dy)) return;
     if (skip_negative && ((oy > 0.0 && dy > 0.0) || (oy < 0.0 && dy < 0.0))) return;  // -oy / dy < 0
     out.t[0] = -oy / dy;
     out.n = 1;
+}
+__device__ __forceinline__ void plane_roots(const Scene& sc, int xform, const Ray& world, bool skip_negative, Roots& out) {
+    const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv + 4);
+    const double2 a = __ldg(q), b = __ldg(q + 1);
+    plane_roots_row(a.x, a.y, b.x, b.y, world, skip_negative, out);
 }
 
 // HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6).

@@ -109,6 +109,17 @@ struct CsgRoot {
     int32_t prim_begin, prim_end;  // all primitives of the subtree are [prim_begin, prim_end)
 };
 
+// A plane of the always-tested list, held in the kernel parameters (constant bank): row 1 of its transform_inv — all
+// a plane intersection reads (src/shape.rs:622-633) — and its primitive index.  Filled when the always-tested list
+// consists of ungated planes only (every bin of the reference): the per-ray plane loop then issues no global loads,
+// where the general list walks unbounded[] -> prims[] -> xforms[] (three dependent loads per plane).
+constexpr int MAX_FAST_PLANES = 8;
+struct FastPlane {
+    double row[4];
+    int32_t prim;
+    int32_t pad;
+};  // 40 B
+
 struct Scene {
     const Prim* prims;
     const Xform* xforms;
@@ -133,6 +144,9 @@ struct Scene {
     int32_t max_children;    // max over materials of (reflective != 0) + (transparency != 0)
     int32_t n_guards;
     double root_lo[3], root_hi[3];  // f64 bounds of all BVH items (already padded)
+    int32_t n_fast_planes;          // > 0: fast_planes[] IS the always-tested list (unbounded[] is not read)
+    int32_t pad_fast;
+    FastPlane fast_planes[MAX_FAST_PLANES];
 };
 
 }  // namespace rtcdev

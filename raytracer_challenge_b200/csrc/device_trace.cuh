@@ -113,6 +113,12 @@ struct Query {
         if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
         prim_roots<0x02>(sc, p, ray, cache, counters(), skip_negative, r);  // planes are the usual always-tested primitive
     }
+    // crossing of a plane of the always-tested list held in the kernel parameters (ungated by construction)
+    __device__ __forceinline__ void roots_of_fast_plane(const FastPlane& p, Roots& r) {
+        r.n = 0;
+        counters().prims++;
+        plane_roots_row(p.row[0], p.row[1], p.row[2], p.row[3], ray, skip_negative, r);
+    }
     // crossings of a BVH leaf item that is a primitive
     __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
         r.n = 0;
@@ -299,6 +305,19 @@ __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mo
     }
 }
 
+// The always-tested primitives, before the walk.  Returns true if the visitor stopped the query.
+template <class V>
+__device__ __forceinline__ bool visit_unbounded(const Scene& sc, V& v) {
+    if (sc.n_fast_planes > 0) {
+        for (int i = 0; i < sc.n_fast_planes; ++i)
+            if (v.plane(sc.fast_planes[i])) return true;
+        return false;
+    }
+    for (int i = 0; i < sc.n_unbounded; ++i)
+        if (v.item(__ldg(sc.unbounded + i))) return true;
+    return false;
+}
+
 // ---- closest hit ---------------------------------------------------------------------------------
 template <int FEAT>
 struct ClosestVisitor {
@@ -345,6 +364,12 @@ struct ClosestVisitor {
         offer_roots(r, id);
         return false;
     }
+    __device__ __forceinline__ bool plane(const FastPlane& p) {
+        Roots r;
+        q.roots_of_fast_plane(p, r);
+        if (r.n) offer(r.t[0], p.prim, 0.0, 0.0);
+        return false;
+    }
     __device__ __forceinline__ bool leaf(int slot) {
         const LeafItem li = load_leaf(q.sc, slot);
         if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
@@ -359,7 +384,7 @@ template <int FEAT>
 __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, Tally& tally, int* overflow) {
     brute = brute || near_cone_slope<FEAT>(sc, ray);
     ClosestVisitor<FEAT> v(sc, ray, limit, tally, overflow);
-    for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
+    visit_unbounded(sc, v);
     walk_bvh(sc, ray, 0, brute, v, tally);
     return v.best;
 }
@@ -392,6 +417,11 @@ struct AnyVisitor {
         q.roots_of_prim(id, r);
         return test(r);
     }
+    __device__ __forceinline__ bool plane(const FastPlane& p) {
+        Roots r;
+        q.roots_of_fast_plane(p, r);
+        return test(r);
+    }
     __device__ __forceinline__ bool leaf(int slot) {
         const LeafItem li = load_leaf(q.sc, slot);
         if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
@@ -408,8 +438,7 @@ template <int FEAT>
 __device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, Tally& tally, int* overflow) {
     brute = brute || near_cone_slope<FEAT>(sc, ray);
     AnyVisitor<FEAT> v(sc, ray, dist, tally, overflow);
-    for (int i = 0; i < sc.n_unbounded; ++i)
-        if (v.item(__ldg(sc.unbounded + i))) return v.found;
+    if (visit_unbounded(sc, v)) return v.found;
     walk_bvh(sc, ray, 0, brute, v, tally);
     return v.found;
 }
@@ -449,6 +478,11 @@ struct CollectVisitor {
         q.roots_of_prim(id, r);
         return push_roots(r, id);
     }
+    __device__ __forceinline__ bool plane(const FastPlane& p) {
+        Roots r;
+        q.roots_of_fast_plane(p, r);
+        return push_roots(r, p.prim);
+    }
     __device__ __forceinline__ bool leaf(int slot) {
         const LeafItem li = load_leaf(q.sc, slot);
         if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
@@ -471,7 +505,7 @@ __device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit
     double n1, n2;
     Cross xs[MAX_CROSSINGS];
     CollectVisitor<FEAT> v(sc, ray, hit_t, xs, tally, overflow);
-    for (int i = 0; i < sc.n_unbounded; ++i) v.item(__ldg(sc.unbounded + i));
+    visit_unbounded(sc, v);
     walk_bvh(sc, ray, 1, brute, v, tally);
     const int n = v.n;
     for (int i = 1; i < n; ++i) {  // order of the reference's sorted list: by t, ties in depth-first primitive order

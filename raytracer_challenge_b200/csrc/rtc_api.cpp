@@ -360,6 +360,21 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     d.all_cast_shadow = h.all_cast_shadow;
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
+    // always-tested list = ungated planes only -> keep them in the kernel parameters (device_scene.h, FastPlane)
+    d.n_fast_planes = 0;
+    d.pad_fast = 0;
+    std::memset(d.fast_planes, 0, sizeof d.fast_planes);
+    if (!h.unbounded.empty() && h.unbounded.size() <= (size_t)rtcdev::MAX_FAST_PLANES && !std::getenv("RTC_NO_FAST_PLANES")) {
+        bool ok = true;
+        for (int32_t id : h.unbounded) ok = ok && id >= 0 && (h.prims[id].kind_flags & 0xff) == RTC_PLANE && h.prims[id].gate_mask == 0u;
+        if (ok) {
+            for (int32_t id : h.unbounded) {
+                rtcdev::FastPlane& fp = d.fast_planes[d.n_fast_planes++];
+                for (int k = 0; k < 4; ++k) fp.row[k] = h.xforms[h.prims[id].xform].inv[4 + k];
+                fp.prim = id;
+            }
+        }
+    }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
     return 0;
 }
@@ -534,7 +549,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         hit_cap += level_cap;
         if (fan == 2) level_cap *= 2;
     }
-    if (hit_cap * (uint64_t)std::max(L, 1) >= 0xffffffffull) return fail("rtc_render: batch too large");
+    if (hit_cap * (uint64_t)std::max(L, 1) >= 0xf0000000ull) return fail("rtc_render: batch too large");
     const uint64_t n_batches = std::max<uint64_t>((n_slots + batch_pixels - 1) / batch_pixels, 1);
     const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
     const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);

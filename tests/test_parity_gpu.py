@@ -74,7 +74,7 @@ def test_cuda_matches_reference_png_window(built, entry):
 def same_pixels(name, a, b):
     """Bit-identical, except for scenes whose materials both reflect and refract: there several path-tree nodes of one
     pixel sit in the same bounce level and their f64 atomic adds commute only up to the last bit."""
-    if name in ("glass_air_bubble", "csg_noise") or name.startswith("fuzz"):
+    if name in ("glass_air_bubble", "csg_noise", "chapter11_title") or name.startswith("fuzz"):
         return np.allclose(a, b, rtol=0.0, atol=1e-12, equal_nan=False)
     return np.array_equal(a, b)
 
@@ -218,3 +218,18 @@ def test_full_size_teapot_properties(built):
     assert st.rays_shadow == 2 * st.surface_hits
     assert st.rays_ref >= st.rays
     assert np.isfinite(whole).all()
+
+
+@pytest.mark.parametrize("name", ["teapot_low", "chapter11_title", "glass_air_bubble", "three_spheres"])
+def test_planes_in_kernel_parameters_equal_the_general_list(built, name, monkeypatch):
+    """Scenes whose always-tested list is ungated planes keep them in the kernel parameters (device_scene.h,
+    FastPlane); RTC_NO_FAST_PLANES forces the general unbounded[] -> prims[] -> xforms[] walk.  Same expressions, so the
+    frames must be bit-identical (up to the order of the atomic adds where one pixel has several nodes in a level)."""
+    w, h = 96, 54
+    with R.Session(name, w, h, device=0) as s:
+        fast, st = s.render(R.Opts())
+    monkeypatch.setenv("RTC_NO_FAST_PLANES", "1")
+    with R.Session(name, w, h, device=0) as s:
+        general, st2 = s.render(R.Opts())
+    assert same_pixels(name, fast, general)
+    assert (st.rays, st.surface_hits) == (st2.rays, st2.surface_hits)
