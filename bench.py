@@ -42,8 +42,10 @@ F64_PER_PLANE = 2.0      # the teapot scene's only non-triangle primitives are p
 F64_PER_XFORM = 33.0     # affine Ray::transform: 18 mul + 15 add (src/ray.rs:14-19 on rows 0..2)
 F64_PER_HIT = 130.0      # prepare_state + normal (+ schlick when transparent), SURVEY.md §8(d)
 F64_PER_HIT_LIGHT = 95.0 + 18.0  # Phong term + shadow-ray setup, per light
-RAY_RECORD = 64.0        # bytes of one queue entry
-HIT_RECORD = 36.0        # bytes of one hit-list entry (index + t/prim + u/v)
+RAY_RECORD = 64.0        # bytes of one queue entry: origin + direction (48) + throughput (8) + fuel/sample (8)
+HIT_RECORD = 96.0        # bytes of one hit-list entry: over_point, normal, eye (72) + throughput (8) + sample/prim (8) + pad (8)
+SHADOW_READ = 32.0       # a shadow thread reads the over_point of its hit (two 16-byte chunks)
+ACCUM = 24.0             # f64 rgb accumulator of a sample
 
 
 def read_peaks():
@@ -339,13 +341,15 @@ def rooflines(R, prof, world):
     L = 2.0
     hits = float(prof.surface_hits)
     secondary = float(prof.rays_reflected + prof.rays_refracted)
+    levels = FUEL + 1
+    batches = max(int(prof.kernel_launches) // (2 * levels + 2), 1)  # per batch: trace x levels, shadow, shade x levels, resolve
     classes = {
-        # closest-hit traversal: reads the level's ray records, writes the hit list
-        "trace_closest": {"ms": prof.ms_trace, "bytes": 48.0 * secondary + HIT_RECORD * hits},
-        # shadow traversal: per (hit, light) reads ray + hit, writes one byte
-        "trace_shadow": {"ms": prof.ms_shadow, "bytes": L * hits * (48.0 + 32.0 + 1.0)},
-        # shading: reads ray + hit + shadow bytes, read-modify-writes the sample accumulator, writes the child ray
-        "shade": {"ms": prof.ms_shade, "bytes": hits * (RAY_RECORD + HIT_RECORD + L) + 48.0 * hits + RAY_RECORD * secondary},
+        # trace_spawn: reads the level's ray records, writes the hit records and the children (the next level's rays)
+        "trace_spawn": {"ms": prof.ms_trace, "bytes": RAY_RECORD * secondary + HIT_RECORD * hits + RAY_RECORD * secondary, "launches": batches * levels},
+        # trace_shadow: per (hit, light) reads the hit's over_point, writes one byte
+        "trace_shadow": {"ms": prof.ms_shadow, "bytes": L * hits * (SHADOW_READ + 1.0), "launches": batches},
+        # shade: reads the hit record + one shadow byte per light, read-modify-writes the sample accumulator
+        "shade": {"ms": prof.ms_shade, "bytes": hits * (HIT_RECORD + L) + 2.0 * ACCUM * hits, "launches": batches * levels},
     }
     # traversal flops split between the two traversal kernels in proportion to their rays (primary+secondary vs shadow)
     n_closest = float(prof.rays_primary) + secondary
@@ -353,9 +357,10 @@ def rooflines(R, prof, world):
     share = n_closest / max(n_closest + n_shadow, 1.0)
     f32_trav = F32_PER_NODE * prof.bvh_node_visits
     f64_trav = F64_PER_TRIANGLE * prof.triangle_tests + F64_PER_PLANE * prof.primitive_tests + F64_PER_XFORM * prof.ray_transforms
-    classes["trace_closest"].update(f64=f64_trav * share, f32=f32_trav * share)
-    classes["trace_shadow"].update(f64=f64_trav * (1.0 - share) + (F64_PER_HIT + 18.0) * L * hits, f32=f32_trav * (1.0 - share))
-    classes["shade"].update(f64=(F64_PER_HIT + 95.0 * L) * hits, f32=0.0)
+    # trace_spawn also holds prepare_state + normal + the child rays; the shadow kernel the shadow-ray setup; shade the Phong terms
+    classes["trace_spawn"].update(f64=f64_trav * share + F64_PER_HIT * hits, f32=f32_trav * share)
+    classes["trace_shadow"].update(f64=f64_trav * (1.0 - share) + 18.0 * L * hits, f32=f32_trav * (1.0 - share))
+    classes["shade"].update(f64=95.0 * L * hits, f32=0.0)
     dominant = max(classes, key=lambda k: classes[k]["ms"])
     d = classes[dominant]
     sec = max(d["ms"], 1e-9) * 1e-3
@@ -373,14 +378,15 @@ def rooflines(R, prof, world):
     except Exception as e:  # noqa: BLE001
         mb = {"error": str(e)}
     gbs = d["bytes"] / sec / 1e9
-    n_launch = int(prof.kernel_launches // 3)  # trace / shadow / shade launch once per level per batch
+    n_launch = int(d["launches"])
     out["roofline"] = {
         "bound": "hbm", "kernel": dominant, "achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
         "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_source,
         "launches_per_frame": n_launch, "achieved_bytes_per_launch": d["bytes"] / max(n_launch, 1), "ms_per_launch": d["ms"] / max(n_launch, 1), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
         "ms_per_frame_in_this_kernel": d["ms"], "algorithmic_bytes_per_frame": d["bytes"],
         "note": "HBM sees only ray queues, hit lists and the frame buffer (the 1.6 MB scene is L1/L2-resident): this path is bound by "
-                "CUDA-core issue under divergence and by L1/L2 latency on BVH fetches, not by HBM — see roofline_fp64 / roofline_fp32 and DESIGN.md",
+                "CUDA-core issue under divergence and by L1/L2 latency on BVH fetches, not by HBM — see roofline_fp64 / roofline_fp32, "
+                "profiles/README.md (ncu: issue-slot utilisation, active threads per instruction, stall reasons) and DESIGN.md",
         "scope": "rank 0's shard of the frame" if world > 1 else "whole frame",
         "per_class_ms": {k: v["ms"] for k, v in classes.items()},
     }
