@@ -145,7 +145,7 @@ struct Scene {
     int32_t n_guards;
     double root_lo[3], root_hi[3];  // f64 bounds of all BVH items (already padded)
     int32_t n_fast_planes;          // > 0: fast_planes[] IS the always-tested list (unbounded[] is not read)
-    int32_t pad_fast;
+    int32_t plain_only;             // every material's pattern is Plain: shading needs no pattern evaluator
     FastPlane fast_planes[MAX_FAST_PLANES];
 };
 

@@ -331,10 +331,17 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_
 // ---- kernel 3: shading of one level's hits -------------------------------------------------------------------
 // World::shade_hit light loop (src/world.rs:58-64) + Shape::lighting (src/shape.rs:429-463); one launch per level, in
 // level order on the batch's stream, so a sample's contributions are added in a fixed order.
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADE_MIN_BLOCKS) shade(const __grid_constant__ Scene sc, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
-    __shared__ uint8_t s_perm[512];
-    for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
-    __syncthreads();
+// PLAIN: every material of the scene has a Plain pattern (its colour is inlined in the material record), so the
+// pattern evaluator — its frames, the noise code and the shared permutation table — is not compiled in: the kernel
+// fits a register budget that doubles its occupancy (r01f: 96 registers, 27 % of the warp slots occupied, dominant
+// stall long_scoreboard on the hit-record loads).
+template <bool PLAIN>
+__global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS : RTC_SHADE_MIN_BLOCKS) shade(const __grid_constant__ Scene sc, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+    __shared__ uint8_t s_perm[PLAIN ? 1 : 512];
+    if (!PLAIN) {
+        for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
+        __syncthreads();
+    }
 
     uint32_t first[MAX_LEVELS + 1];
     const uint32_t n_all = hit_prefix(hl, first);
@@ -352,7 +359,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_SHADE_MIN_BLOCKS) shade(const _
         const Prim prim = load_prim(sc, (int)(uint32_t)(bits & 0xffffffffu));
         const Material& mat = sc.materials[prim.material];
         Rgb color;
-        if (mat.flags & 1) color = rgb(mat.plain[0], mat.plain[1], mat.plain[2]);
+        if (PLAIN || (mat.flags & 1)) color = rgb(mat.plain[0], mat.plain[1], mat.plain[2]);
         else {
             V3 pp = over_point;
             double pw = 1.0;
@@ -449,7 +456,8 @@ void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const F
 }
 
 void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {
-    shade<<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
+    if (sc.plain_only) shade<true><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
+    else shade<false><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
 }
 
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major) {

@@ -25,6 +25,9 @@
 #ifndef RTC_SHADE_MIN_BLOCKS
 #define RTC_SHADE_MIN_BLOCKS 5
 #endif
+#ifndef RTC_SHADE_PLAIN_MIN_BLOCKS  // scenes without procedural patterns: no evaluator, no permutation table, small register budget
+#define RTC_SHADE_PLAIN_MIN_BLOCKS 8
+#endif
 
 namespace rtcdev {
 

@@ -368,7 +368,9 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
     // always-tested list = ungated planes only -> keep them in the kernel parameters (device_scene.h, FastPlane)
     d.n_fast_planes = 0;
-    d.pad_fast = 0;
+    d.plain_only = 1;
+    for (const rtcdev::Material& m : h.materials) d.plain_only = d.plain_only && (m.flags & 1) != 0;
+    if (std::getenv("RTC_NO_PLAIN_SHADE")) d.plain_only = 0;
     std::memset(d.fast_planes, 0, sizeof d.fast_planes);
     if (!h.unbounded.empty() && h.unbounded.size() <= (size_t)rtcdev::MAX_FAST_PLANES && !std::getenv("RTC_NO_FAST_PLANES")) {
         bool ok = true;
