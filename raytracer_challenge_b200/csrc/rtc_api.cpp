@@ -301,6 +301,11 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
         return off;
     };
 #define PLACE(vec) place((vec).data(), (vec).size() * sizeof((vec)[0]))
+#define BYTES(vec) (((vec).size() * sizeof((vec)[0]) + 16 + 255) & ~(size_t)255)
+    p.blob.reserve(BYTES(h.prims) + BYTES(h.xforms) + BYTES(h.matinvs) + BYTES(h.tri_pe) + BYTES(h.tri_n) + BYTES(h.ranges) + BYTES(h.materials) +
+                   BYTES(h.patterns) + BYTES(h.lights) + BYTES(h.gates) + BYTES(h.bvh) + BYTES(h.leaf_items) + BYTES(h.leaf_tri) + BYTES(h.unbounded) +
+                   BYTES(h.csg_ops) + BYTES(h.csg_roots) + BYTES(h.guards) + 4096);  // one allocation: no regrow-and-copy per section
+#undef BYTES
     p.o_prims = PLACE(h.prims); p.o_xforms = PLACE(h.xforms); p.o_matinvs = PLACE(h.matinvs); p.o_tri_pe = PLACE(h.tri_pe);
     p.o_tri_n = PLACE(h.tri_n); p.o_ranges = PLACE(h.ranges); p.o_materials = PLACE(h.materials); p.o_patterns = PLACE(h.patterns);
     p.o_lights = PLACE(h.lights); p.o_gates = PLACE(h.gates); p.o_bvh = PLACE(h.bvh); p.o_leaf_items = PLACE(h.leaf_items);

@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstddef>
 #include <cstring>
 #include <functional>
 #include <limits>
@@ -68,10 +69,10 @@ void xf_point(const double m[12], const double p[3], double out[3]) {
 // infinite range are unbounded.  A cone with a finite range gets the box of its walls and caps, marked inexact: its
 // single-root branch (src/shape.rs:811-818) has no y-range check, so for the rare rays that take it the crossing is
 // not confined to [min, max] — those rays are detected per query (rtcdev::ConeGuard) and test every item.
-Box prim_bounds(const rtc_prim& p) {
+// fwd: object -> world (invert_affine of p.transform_inv), or null if that matrix is singular
+Box prim_bounds(const rtc_prim& p, const double* fwd) {
     Box b;
-    double fwd[12];
-    if (!invert_affine(p.transform_inv, fwd)) { b.bounded = false; return b; }
+    if (!fwd) { b.bounded = false; return b; }
     double olo[3], ohi[3];
     switch (p.kind) {
         case RTC_SPHERE:
@@ -118,14 +119,29 @@ pad:
     return b;
 }
 
+// Nearest float not above / not below x.  The neighbouring float is reached by stepping the bit pattern (what
+// nextafterf computes, without the libm call: this runs six times per BVH item).
+inline float step_float(float f, bool up) {
+    if (!(std::fabs(f) <= std::numeric_limits<float>::max())) {  // NaN stays; an infinity steps back to the largest finite value
+        if (f > 0.0f && !up) return std::numeric_limits<float>::max();
+        if (f < 0.0f && up) return -std::numeric_limits<float>::max();
+        return f;
+    }
+    if (f == 0.0f) return up ? std::numeric_limits<float>::denorm_min() : -std::numeric_limits<float>::denorm_min();
+    uint32_t u;
+    std::memcpy(&u, &f, 4);
+    u += ((f > 0.0f) == up) ? 1u : (uint32_t)-1;
+    std::memcpy(&f, &u, 4);
+    return f;
+}
 float f32_down(double x) {
     float f = (float)x;
-    if ((double)f > x) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+    if ((double)f > x) f = step_float(f, false);
     return f;
 }
 float f32_up(double x) {
     float f = (float)x;
-    if ((double)f < x) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+    if ((double)f < x) f = step_float(f, true);
     return f;
 }
 
@@ -152,6 +168,8 @@ struct Builder {
     std::vector<Item> items;
     std::vector<BvhNode> nodes;  // build(): slot mid - 1 of the node that splits at `mid` (sparse); compact(): final
     float leaf_weight = 3.0f;    // cost of one exact f64 primitive test relative to one fp32 node visit
+    int small_node = 8;
+    int max_bins = 16;
     int fork_levels = 4;         // the top levels of the tree fork a thread per left subtree (RTC_BUILD_FORK_LEVELS, 0 = sequential)
     std::atomic<int> depth{0};
 
@@ -163,6 +181,8 @@ struct Builder {
             fork_levels = 0;
             while (fork_levels < 4 && (2 << fork_levels) <= cores) fork_levels++;
         }
+        if (const char* w = std::getenv("RTC_BINS")) max_bins = std::min(16, std::max(2, std::atoi(w)));
+        if (const char* w = std::getenv("RTC_SMALL_NODE")) small_node = std::min(8, std::max(2, std::atoi(w)));
         if (const char* w = std::getenv("RTC_BUILD_FORK_LEVELS")) fork_levels = std::min(8, std::max(0, std::atoi(w)));
         items.resize(boxes.size());
         for (size_t i = 0; i < boxes.size(); ++i) {
@@ -285,8 +305,8 @@ struct Builder {
         for (int seen = depth.load(); level > seen && !depth.compare_exchange_weak(seen, level);) {}
         const int n = end - begin;
         if (n <= 1) return leaf_link(begin, n);
-        if (n <= 8) return build_small(begin, end, level, whole);
-        const int NB = std::min(16, n);
+        if (n <= small_node) return build_small(begin, end, level, whole);
+        const int NB = std::min(max_bins, n);
         Bounds cb;  // centroid bounds: the split candidates
         cb.reset();
         for (int i = begin; i < end; ++i) cb.add(items[(size_t)i].c, items[(size_t)i].c);
@@ -476,25 +496,37 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         out.tri_pe.reserve(n_tri * 10);
         out.tri_n.reserve(n_tri * 10);
     }
-    int32_t last_xf = -1, last_mi = -1;  // the triangles of a mesh share their matrices: compare with the previous primitive first
+    // The triangles of a mesh share their three matrices (Element::composite bakes the group transform into every
+    // child, src/shape.rs:47-72): a primitive whose matrices are byte-equal to its predecessor's reuses that one's
+    // validation, transform ids and forward transform — one 384-byte compare instead of 48 finiteness tests, two
+    // record compares and a 3x3 inversion per triangle.
+    int32_t last_xf = -1, last_mi = -1;
+    const rtc_prim* last = nullptr;
+    double fwd[12];
+    bool fwd_ok = false;
     for (int i = 0; i < d.n_prims; ++i) {
         const rtc_prim& p = d.prims[i];
         if (p.kind < RTC_SPHERE || p.kind > RTC_SMOOTH_TRIANGLE) return "prim " + std::to_string(i) + ": unknown kind";
         if (p.material < 0 || p.material >= d.n_materials) return "prim " + std::to_string(i) + ": bad material index";
-        if (!affine(p.transform_inv) || !affine(p.material_inv)) return "prim " + std::to_string(i) + ": non-affine matrix";
-        if (!all_finite(p.transform_inv, 16) || !all_finite(p.transform_inv_tsp, 16) || !all_finite(p.material_inv, 16))
-            return "prim " + std::to_string(i) + ": non-finite matrix";
-        rtcdev::Xform xf{};
-        for (int k = 0; k < 12; ++k) xf.inv[k] = p.transform_inv[k];
-        for (int r = 0; r < 3; ++r)
-            for (int c = 0; c < 3; ++c) xf.tsp[r * 3 + c] = p.transform_inv_tsp[r * 4 + c];
-        rtcdev::MatInv mi{};
-        for (int k = 0; k < 16; ++k) mi.m[k] = p.material_inv[k];
+        static_assert(offsetof(rtc_prim, material_inv) + sizeof(p.material_inv) - offsetof(rtc_prim, transform_inv) == 3 * 16 * sizeof(double), "the three matrices are contiguous");
+        if (!last || std::memcmp(p.transform_inv, last->transform_inv, 3 * 16 * sizeof(double)) != 0) {
+            if (!affine(p.transform_inv) || !affine(p.material_inv)) return "prim " + std::to_string(i) + ": non-affine matrix";
+            if (!all_finite(p.transform_inv, 16) || !all_finite(p.transform_inv_tsp, 16) || !all_finite(p.material_inv, 16))
+                return "prim " + std::to_string(i) + ": non-finite matrix";
+            rtcdev::Xform xf{};
+            for (int k = 0; k < 12; ++k) xf.inv[k] = p.transform_inv[k];
+            for (int r = 0; r < 3; ++r)
+                for (int c = 0; c < 3; ++c) xf.tsp[r * 3 + c] = p.transform_inv_tsp[r * 4 + c];
+            rtcdev::MatInv mi{};
+            for (int k = 0; k < 16; ++k) mi.m[k] = p.material_inv[k];
+            if (last_xf < 0 || std::memcmp(&out.xforms[(size_t)last_xf], &xf, sizeof xf) != 0) last_xf = dedupe(xf_index, out.xforms, xf);
+            if (last_mi < 0 || std::memcmp(&out.matinvs[(size_t)last_mi], &mi, sizeof mi) != 0) last_mi = dedupe(mi_index, out.matinvs, mi);
+            fwd_ok = invert_affine(p.transform_inv, fwd);
+            last = &p;
+        }
         rtcdev::Prim q{};
         q.kind_flags = p.kind | (p.casts_shadow ? 0x100 : 0) | (p.closed ? 0x200 : 0);
         q.material = p.material;
-        if (last_xf < 0 || std::memcmp(&out.xforms[(size_t)last_xf], &xf, sizeof xf) != 0) last_xf = dedupe(xf_index, out.xforms, xf);
-        if (last_mi < 0 || std::memcmp(&out.matinvs[(size_t)last_mi], &mi, sizeof mi) != 0) last_mi = dedupe(mi_index, out.matinvs, mi);
         q.xform = last_xf;
         q.matinv = last_mi;
         q.geom = -1;
@@ -511,7 +543,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         }
         if (!p.casts_shadow) out.all_cast_shadow = 0;
         out.prims.push_back(q);
-        prim_box[(size_t)i] = prim_bounds(p);
+        prim_box[(size_t)i] = prim_bounds(p, fwd_ok ? fwd : nullptr);
         if (p.kind == RTC_CONE && prim_box[(size_t)i].bounded) {  // one guard per distinct linear part
             rtcdev::ConeGuard g{};
             for (int r = 0; r < 3; ++r)
