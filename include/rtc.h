@@ -109,9 +109,16 @@ typedef struct rtc_light {
     double origin[3];
 } rtc_light;
 
+/* rtc_scene_desc.build_flags */
+#define RTC_BUILD_FAST 1u /* the scene is rendered once and destroyed (the call pattern of Image::par_render, src/image.rs:65-81):
+                           * build the BVH on the device (LBVH, tens of microseconds) instead of the host's binned-SAH build
+                           * (1-2 ms for the teapot).  The tree is of lower quality — a frame traces a few per cent slower — and
+                           * the rendered pixels are identical: the BVH only culls. */
+
 typedef struct rtc_scene_desc {
     int32_t abi_version; /* RTC_ABI_VERSION */
     int32_t n_prims, n_nodes, n_children, n_materials, n_patterns, n_lights;
+    uint32_t build_flags; /* RTC_BUILD_*; 0 = default.  (Occupies what was alignment padding: the layout is unchanged.) */
     const rtc_prim* prims;
     const rtc_node* nodes;
     const int32_t* children;

@@ -42,7 +42,8 @@ def build_rtc(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".hpp", ".cuh"))]
     headers.append(os.path.join(ROOT, "include", "rtc.h"))
-    units = [("render_kernels.cu", DEVICE_FLAGS + (["-Xptxas", "-v"] if verbose else [])), ("rtc_api.cpp", HOST_FLAGS), ("scene_build.cpp", HOST_FLAGS),
+    units = [("render_kernels.cu", DEVICE_FLAGS + (["-Xptxas", "-v"] if verbose else [])), ("bvh_build.cu", ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH),
+             ("rtc_api.cpp", HOST_FLAGS), ("scene_build.cpp", HOST_FLAGS),
              ("microbench.cu", ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH)]
     objs = []
     log = ""

@@ -1,0 +1,261 @@
+// Device-side BVH build (LBVH) for scenes that are created, rendered once and destroyed — the call pattern of the
+// reference's Image::par_render (src/image.rs:65-81: every frame starts from a World).  The host's binned-SAH build
+// costs ~1.0-1.9 ms for the teapot's 6 320 triangles (more when the ranks of a multi-GPU run share the host cores);
+// here the GPU, idle during scene creation, does it in a handful of small launches:
+//
+//   morton_keys     item -> 30-bit Morton code of its box centre inside the root box; key = code << 32 | item index
+//                   (unique keys: no duplicate handling in the hierarchy)
+//   sort_keys       one block, bitonic sort of <= 8 192 keys in shared memory
+//   build_hierarchy Karras 2012: internal node i covers a range of sorted keys found by binary searches on the common
+//                   prefix length; children / parents / ranges written in one pass
+//   fit_boxes       bottom-up: each leaf walks towards the root, the second arrival at a node (atomic counter) unites
+//                   the children's boxes
+//   emit_nodes      subtrees of <= leaf_max items collapse into leaves (the traversal's leaf format); the surviving internal
+//                   nodes are numbered by a block-wide prefix sum and written as 64-byte BvhNodes (both child boxes
+//                   + links), exactly what the SAH build produces for the traversal kernels
+//   permute_items   leaf items (header + triangle record) gathered into sorted order, so a leaf's items are contiguous
+//
+// Culling structure only: the boxes are the same padded, outward-rounded fp32 item boxes the host build uses, so the
+// walk stays conservative and the rendered frame is bit-identical to the SAH build's and to brute force (tests).
+// The tree is of lower quality than the SAH tree (more node visits per ray); rtc_scene_desc.build_flags selects it.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "render_kernels.h"
+
+namespace rtcdev {
+
+namespace {
+
+__device__ __forceinline__ uint32_t expand_bits(uint32_t v) {  // 10 bits -> every third bit
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+__global__ void morton_keys(LbvhArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const float4 lo = a.box[2 * i], hi = a.box[2 * i + 1];
+    const float c[3] = {0.5f * lo.x + 0.5f * hi.x, 0.5f * lo.y + 0.5f * hi.y, 0.5f * lo.z + 0.5f * hi.z};
+    uint32_t q[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float u = (c[k] - a.root_lo[k]) * a.root_inv_extent[k];
+        u = fminf(fmaxf(u, 0.0f), 1.0f);  // (NaN -> 0: a degenerate axis has inv_extent 0)
+        q[k] = (uint32_t)fminf(u * 1024.0f, 1023.0f);
+    }
+    const uint32_t code = expand_bits(q[0]) << 2 | expand_bits(q[1]) << 1 | expand_bits(q[2]);
+    a.keys[i] = (unsigned long long)code << 32 | (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(1024) sort_keys(LbvhArgs a, int np2) {
+    extern __shared__ unsigned long long sk[];
+    for (int i = threadIdx.x; i < np2; i += blockDim.x) sk[i] = i < a.n ? a.keys[i] : ~0ull;
+    for (int k = 2; k <= np2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < np2; i += blockDim.x) {
+                const int p = i ^ j;
+                if (p > i) {
+                    const unsigned long long x = sk[i], y = sk[p];
+                    if ((x > y) == ((i & k) == 0)) { sk[i] = y; sk[p] = x; }
+                }
+            }
+        }
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.n; i += blockDim.x) a.keys[i] = sk[i];
+}
+
+// length of the common prefix of keys i and j; -1 outside the array (Karras 2012, section 3)
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, int n, unsigned long long ki, int j) {
+    if (j < 0 || j >= n) return -1;
+    return __clzll((long long)(ki ^ keys[j]));
+}
+
+__global__ void build_hierarchy(LbvhArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = a.n;
+    if (i >= n - 1) return;
+    const unsigned long long* keys = a.keys;
+    const unsigned long long ki = keys[i];
+    const int d = delta(keys, n, ki, i + 1) - delta(keys, n, ki, i - 1) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, ki, i - d);
+    int lmax = 2;
+    while (delta(keys, n, ki, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, ki, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, ki, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, ki, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    const int gamma = i + s * d + (d < 0 ? d : 0);
+    const int first = i < j ? i : j, last = i < j ? j : i;
+    // children: internal node k -> k, sorted leaf p -> ~p.  parent[]: [0, n-1) internal nodes, [n, 2n) leaves.
+    int left, right;
+    if (first == gamma) { left = ~gamma; a.parent[n + gamma] = i; } else { left = gamma; a.parent[gamma] = i; }
+    if (last == gamma + 1) { right = ~(gamma + 1); a.parent[n + gamma + 1] = i; } else { right = gamma + 1; a.parent[gamma + 1] = i; }
+    a.child[i] = make_int2(left, right);
+    a.range[i] = make_int2(first, last);
+    if (i == 0) a.parent[0] = -1;
+}
+
+__device__ __forceinline__ void child_box(const LbvhArgs& a, int c, float4& lo, float4& hi) {
+    if (c < 0) {
+        const uint32_t item = (uint32_t)(a.keys[~c] & 0xffffffffu);
+        lo = a.box[2 * item];
+        hi = a.box[2 * item + 1];
+    } else {  // written by another thread before it bumped this node's counter: read past L1
+        lo = __ldcg(a.nbox + 2 * c);
+        hi = __ldcg(a.nbox + 2 * c + 1);
+    }
+}
+
+__global__ void fit_boxes(LbvhArgs a) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = a.n;
+    if (p >= n) return;
+    int depth = 1;
+    for (int node = a.parent[n + p]; node > 0; node = a.parent[node]) ++depth;
+    atomicMax(a.result + 1, depth);
+    int node = a.parent[n + p];
+    while (node >= 0) {
+        if (atomicAdd(a.counter + node, 1) == 0) return;  // the sibling subtree is not finished: its last thread continues
+        __threadfence();
+        const int2 ch = a.child[node];
+        float4 l0, h0, l1, h1;
+        child_box(a, ch.x, l0, h0);
+        child_box(a, ch.y, l1, h1);
+        a.nbox[2 * node] = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
+        a.nbox[2 * node + 1] = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        __threadfence();
+        node = a.parent[node];
+    }
+}
+
+// One block: numbers the internal nodes that survive the collapse (range of more than leaf_max items) and writes them.
+__global__ void __launch_bounds__(1024) emit_nodes(LbvhArgs a) {
+    __shared__ int s_sum[1024];
+    const int n_int = a.n - 1;
+    const int per = (n_int + (int)blockDim.x - 1) / (int)blockDim.x;
+    const int b0 = (int)threadIdx.x * per, b1 = min(b0 + per, n_int);
+    int mine = 0;
+    for (int i = b0; i < b1; ++i) {
+        const int2 r = a.range[i];
+        mine += (r.y - r.x + 1 > a.leaf_max) ? 1 : 0;
+    }
+    s_sum[threadIdx.x] = mine;
+    __syncthreads();
+    for (int off = 1; off < (int)blockDim.x; off <<= 1) {  // Hillis-Steele inclusive scan
+        const int v = (int)threadIdx.x >= off ? s_sum[threadIdx.x - off] : 0;
+        __syncthreads();
+        s_sum[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int at = s_sum[threadIdx.x] - mine;
+    for (int i = b0; i < b1; ++i) {
+        const int2 r = a.range[i];
+        const bool kept = r.y - r.x + 1 > a.leaf_max;
+        a.dense[i] = kept ? at : -1;
+        at += kept ? 1 : 0;
+    }
+    if (threadIdx.x == blockDim.x - 1) a.result[2] = s_sum[threadIdx.x];  // number of nodes
+    __threadfence_block();
+    __syncthreads();
+    for (int i = b0; i < b1; ++i) {
+        const int me = a.dense[i];
+        if (me < 0) continue;
+        const int2 ch = a.child[i];
+        BvhNode nd;
+        int links[2];
+        float4 lo[2], hi[2];
+        const int c[2] = {ch.x, ch.y};
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            child_box(a, c[k], lo[k], hi[k]);
+            if (c[k] < 0) links[k] = ~((~c[k]) << 2);  // one item
+            else {
+                const int2 r = a.range[c[k]];
+                const int count = r.y - r.x + 1;
+                links[k] = count > a.leaf_max ? a.dense[c[k]] : ~((r.x << 2) | (count - 1));
+            }
+        }
+        nd.lo0[0] = lo[0].x; nd.lo0[1] = lo[0].y; nd.lo0[2] = lo[0].z;
+        nd.hi0[0] = hi[0].x; nd.hi0[1] = hi[0].y; nd.hi0[2] = hi[0].z;
+        nd.lo1[0] = lo[1].x; nd.lo1[1] = lo[1].y; nd.lo1[2] = lo[1].z;
+        nd.hi1[0] = hi[1].x; nd.hi1[1] = hi[1].y; nd.hi1[2] = hi[1].z;
+        nd.c0 = links[0];
+        nd.c1 = links[1];
+        nd.pad0 = 0;
+        nd.pad1 = 0;
+        a.bvh[me] = nd;
+    }
+    if (threadIdx.x == 0) a.result[0] = 0;  // the root is internal node 0, kept (n > leaf_max) and numbered first
+}
+
+// Leaf records in sorted order, so the items of a leaf are contiguous: the 16-byte header the traversal reads instead of
+// prims[], and for triangles the (p1, e1, e2) record next to it.
+__global__ void permute_items(LbvhArgs a) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.n) return;
+    const uint32_t item = (uint32_t)(a.keys[p] & 0xffffffffu);
+    const int32_t id = a.item_ids[item];
+    LeafItem li;
+    li.id = id;
+    li.kind_flags = 0;
+    li.xform = 0;
+    li.geom = -1;
+    double2* d = reinterpret_cast<double2*>(a.leaf_tri + 10 * (size_t)p);
+    bool triangle = false;
+    if (id >= 0) {
+        const Prim pr = a.prims[id];
+        li.kind_flags = pr.kind_flags;
+        li.xform = pr.xform;
+        li.geom = pr.geom;
+        triangle = (pr.kind_flags & 0xff) >= 5;
+        if (triangle) {
+            const double2* s = reinterpret_cast<const double2*>(a.tri_pe + 10 * (size_t)pr.geom);
+#pragma unroll
+            for (int k = 0; k < 5; ++k) d[k] = s[k];
+        }
+    }
+    if (!triangle) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) d[k] = make_double2(0.0, 0.0);
+    }
+    a.leaf_items[p] = li;
+}
+
+}  // namespace
+
+// Enqueues the build on `st`.  a.result (3 ints, zeroed here): [0] root link, [1] depth of the radix tree (an upper
+// bound of the collapsed tree's), [2] node count.  Returns a CUDA error code.
+int build_lbvh(const LbvhArgs& a, cudaStream_t st) {
+    if (a.n < 8 || a.n > LBVH_MAX_ITEMS) return (int)cudaErrorInvalidValue;
+    int np2 = 1;
+    while (np2 < a.n) np2 <<= 1;
+    const size_t smem = (size_t)np2 * sizeof(unsigned long long);
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(sort_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, LBVH_MAX_ITEMS * (int)sizeof(unsigned long long)) != cudaSuccess) return (int)cudaGetLastError();
+        attr_set = true;
+    }
+    cudaMemsetAsync(a.counter, 0, sizeof(int) * (size_t)a.n, st);
+    cudaMemsetAsync(a.result, 0, sizeof(int) * 4, st);
+    const int block = 128, grid = (a.n + block - 1) / block;
+    morton_keys<<<grid, block, 0, st>>>(a);
+    sort_keys<<<1, 1024, smem, st>>>(a, np2);
+    build_hierarchy<<<grid, block, 0, st>>>(a);
+    fit_boxes<<<grid, block, 0, st>>>(a);
+    emit_nodes<<<1, 1024, 0, st>>>(a);
+    permute_items<<<grid, block, 0, st>>>(a);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace rtcdev

@@ -12,6 +12,8 @@ constexpr int MAX_CSG_MARKS = 8;        // CSG nesting depth
 constexpr int MAX_CROSSINGS = 64;       // crossings (t <= t_hit) replayed for n1/n2 (src/intersection.rs:70-103)
 constexpr int MAX_CONTAINERS = 24;      // simultaneously open shapes during that replay
 constexpr int BVH_STACK = 48;
+constexpr int LBVH_MAX_ITEMS = 8192;    // device-side build (bvh_build.cu): one-block shared-memory sort
+constexpr int LBVH_MIN_ITEMS = 64;      // below this the host build costs microseconds
 
 // Kernel feature bits (compile-time variants of the wavefront kernel)
 constexpr int FEAT_TRANSPARENT = 1;  // some material has transparency != 0: n1/n2 replay needed

@@ -84,6 +84,29 @@ void upload_perm(const uint8_t* perm512);
 // Per batch: trace_spawn once per level (a chain), then ONE shadow launch over every hit of the batch, then shade per level.
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
 void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
+// Device-side LBVH build (bvh_build.cu): everything lives in the scene arena.
+struct LbvhArgs {
+    int n;                      // BVH items
+    int leaf_max;               // subtrees of at most this many items (1..4) collapse into one leaf
+    const float4* box;          // 2 per item: (lo.xyz, -), (hi.xyz, -): the padded, outward-rounded fp32 item boxes
+    const int32_t* item_ids;    // per item: primitive index, or ~csg root
+    const Prim* prims;          // the uploaded primitive table (kind, transform id, geometry slot of an item)
+    const double* tri_pe;       // the uploaded triangle records, by geometry slot
+    LeafItem* leaf_items;       // out: leaf order
+    double* leaf_tri;           // out: leaf order
+    BvhNode* bvh;               // out: n - 1 slots
+    unsigned long long* keys;   // n
+    int2* child;                // n - 1
+    int* parent;                // 2 n
+    int2* range;                // n - 1
+    float4* nbox;               // 2 (n - 1)
+    int* counter;               // n
+    int* dense;                 // n
+    int* result;                // 4: root link, radix-tree depth, node count
+    float root_lo[3], root_inv_extent[3];
+};
+int build_lbvh(const LbvhArgs& a, cudaStream_t st);
+
 void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hits);
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major);
 

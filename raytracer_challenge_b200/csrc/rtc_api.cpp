@@ -146,6 +146,7 @@ struct rtc_scene {
     rtcdev::Scene dev{};
     void* arena = nullptr;  // one device allocation holding every scene array
     size_t arena_bytes = 0;
+    int bvh_depth = -1, bvh_nodes = -1;  // device-side build: what the device reported (host build: see HostScene)
 };
 
 extern "C" {
@@ -239,7 +240,12 @@ static int64_t host_stat(const rtchost::HostScene& h, int key) {
     }
 }
 
-int64_t rtc_scene_stat(const rtc_scene* s, int key) { return s && s->host ? host_stat(*s->host, key) : -1; }
+int64_t rtc_scene_stat(const rtc_scene* s, int key) {
+    if (!s || !s->host) return -1;
+    if (s->bvh_depth >= 0 && key == RTC_STAT_BVH_DEPTH) return s->bvh_depth;  // device-side build: what the device reported
+    if (s->bvh_nodes >= 0 && key == RTC_STAT_BVH_NODES) return s->bvh_nodes;
+    return host_stat(*s->host, key);
+}
 
 int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16) {
     if (!desc) return fail("rtc_scene_validate: null argument");
@@ -292,6 +298,9 @@ struct PackedScene {
     std::vector<unsigned char> blob;
     size_t o_prims, o_xforms, o_matinvs, o_tri_pe, o_tri_n, o_ranges, o_materials, o_patterns, o_lights, o_gates, o_bvh, o_leaf_items,
         o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots, o_guards;
+    // device-side BVH build only (HostScene::device_build): staging + scratch sections
+    size_t upload_bytes = 0, total_bytes = 0;  // host -> device copy / arena size
+    size_t o_item_ids = 0, o_box32 = 0, o_keys = 0, o_child = 0, o_parent = 0, o_range = 0, o_nbox = 0, o_counter = 0, o_dense = 0, o_result = 0;
 };
 static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     auto place = [&](const void* src, size_t bytes) -> size_t {
@@ -304,15 +313,42 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
 #define BYTES(vec) (((vec).size() * sizeof((vec)[0]) + 16 + 255) & ~(size_t)255)
     p.blob.reserve(BYTES(h.prims) + BYTES(h.xforms) + BYTES(h.matinvs) + BYTES(h.tri_pe) + BYTES(h.tri_n) + BYTES(h.ranges) + BYTES(h.materials) +
                    BYTES(h.patterns) + BYTES(h.lights) + BYTES(h.gates) + BYTES(h.bvh) + BYTES(h.leaf_items) + BYTES(h.leaf_tri) + BYTES(h.unbounded) +
-                   BYTES(h.csg_ops) + BYTES(h.csg_roots) + BYTES(h.guards) + 4096);  // one allocation: no regrow-and-copy per section
+                   BYTES(h.csg_ops) + BYTES(h.csg_roots) + BYTES(h.guards) + 4096 +
+                   (h.device_build ? BYTES(h.item_ids) + BYTES(h.item_box32) + 4096 : 0));  // one allocation: no regrow-and-copy per section
 #undef BYTES
     p.o_prims = PLACE(h.prims); p.o_xforms = PLACE(h.xforms); p.o_matinvs = PLACE(h.matinvs); p.o_tri_pe = PLACE(h.tri_pe);
     p.o_tri_n = PLACE(h.tri_n); p.o_ranges = PLACE(h.ranges); p.o_materials = PLACE(h.materials); p.o_patterns = PLACE(h.patterns);
     p.o_lights = PLACE(h.lights); p.o_gates = PLACE(h.gates); p.o_bvh = PLACE(h.bvh); p.o_leaf_items = PLACE(h.leaf_items);
     p.o_leaf_tri = PLACE(h.leaf_tri); p.o_unbounded = PLACE(h.unbounded); p.o_csg_ops = PLACE(h.csg_ops); p.o_csg_roots = PLACE(h.csg_roots);
     p.o_guards = PLACE(h.guards);
+    p.upload_bytes = p.blob.size();
+    p.total_bytes = p.blob.size();
+    if (h.device_build) {  // staging for bvh_build.cu, then space the device fills itself (never uploaded)
+        const size_t n = (size_t)h.n_bvh_items;
+        p.o_item_ids = PLACE(h.item_ids);
+        p.o_box32 = PLACE(h.item_box32);
+        p.upload_bytes = p.blob.size();
+        size_t at = p.upload_bytes;
+        auto reserve = [&](size_t bytes) -> size_t {
+            const size_t off = (at + 255) & ~(size_t)255;
+            at = off + std::max<size_t>(bytes, 16);
+            return off;
+        };
+        p.o_bvh = reserve(n * sizeof(rtcdev::BvhNode));
+        p.o_leaf_items = reserve(n * sizeof(rtcdev::LeafItem));
+        p.o_leaf_tri = reserve(n * 80);
+        p.o_keys = reserve(n * 8);
+        p.o_child = reserve(n * 8);
+        p.o_parent = reserve(2 * n * 4);
+        p.o_range = reserve(n * 8);
+        p.o_nbox = reserve(2 * n * 16);
+        p.o_counter = reserve(n * 4);
+        p.o_dense = reserve(n * 4);
+        p.o_result = reserve(16);
+        p.total_bytes = at;
+    }
 #undef PLACE
-    h.device_bytes = (int64_t)p.blob.size();
+    h.device_bytes = (int64_t)p.total_bytes;
 }
 
 // Device half of rtc_scene_create: arena (reused from the device context when one is parked there), copy, pointers.
@@ -323,7 +359,7 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     {
         std::lock_guard<std::mutex> lock(c.mu);
         if (ctx_init(c, device)) { err = g_error; return 1; }
-        if (c.spare_arena && c.spare_arena_bytes >= p.blob.size()) {
+        if (c.spare_arena && c.spare_arena_bytes >= p.total_bytes) {
             s->arena = c.spare_arena;
             s->arena_bytes = c.spare_arena_bytes;
             c.spare_arena = nullptr;
@@ -331,10 +367,10 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
         }
     }
     if (!s->arena) {
-        if (cudaMalloc(&s->arena, p.blob.size()) != cudaSuccess) { err = "cudaMalloc of the scene arena failed"; return 1; }
-        s->arena_bytes = p.blob.size();
+        if (cudaMalloc(&s->arena, p.total_bytes) != cudaSuccess) { err = "cudaMalloc of the scene arena failed"; return 1; }
+        s->arena_bytes = p.total_bytes;
     }
-    if (cudaMemcpy(s->arena, p.blob.data(), p.blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+    if (cudaMemcpy(s->arena, p.blob.data(), p.upload_bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
         err = std::string("scene upload failed: ") + cudaGetErrorString(cudaGetLastError());
         cudaFree(s->arena);
         s->arena = nullptr;
@@ -371,6 +407,48 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     d.all_cast_shadow = h.all_cast_shadow;
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
+    if (h.device_build) {  // build the BVH where the scene now lives (bvh_build.cu); the host only staged the item boxes
+        rtcdev::LbvhArgs a{};
+        a.n = h.n_bvh_items;
+        a.leaf_max = env_int("RTC_LBVH_LEAF", 1, 1, 4);  // (sweep: 1 is the robust choice, the f64 item tests cost more than a node visit)
+        a.box = (const float4*)(base + p.o_box32);
+        a.item_ids = (const int32_t*)(base + p.o_item_ids);
+        a.prims = d.prims;
+        a.tri_pe = d.tri_pe;
+        a.leaf_items = (rtcdev::LeafItem*)(base + p.o_leaf_items);
+        a.leaf_tri = (double*)(base + p.o_leaf_tri);
+        a.bvh = (rtcdev::BvhNode*)(base + p.o_bvh);
+        a.keys = (unsigned long long*)(base + p.o_keys);
+        a.child = (int2*)(base + p.o_child);
+        a.parent = (int*)(base + p.o_parent);
+        a.range = (int2*)(base + p.o_range);
+        a.nbox = (float4*)(base + p.o_nbox);
+        a.counter = (int*)(base + p.o_counter);
+        a.dense = (int*)(base + p.o_dense);
+        a.result = (int*)(base + p.o_result);
+        for (int k = 0; k < 3; ++k) {
+            a.root_lo[k] = (float)h.root_lo[k];
+            const double ext = h.root_hi[k] - h.root_lo[k];
+            a.root_inv_extent[k] = ext > 0.0 ? (float)(1.0 / ext) : 0.0f;
+        }
+        int result[4] = {0, 0, 0, 0};
+        const int rc = rtcdev::build_lbvh(a, nullptr);
+        if (rc != 0 || cudaMemcpy(result, a.result, sizeof result, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            err = std::string("device BVH build failed: ") + cudaGetErrorString(rc != 0 ? (cudaError_t)rc : cudaGetLastError());
+            cudaFree(s->arena);
+            s->arena = nullptr;
+            return 1;
+        }
+        if (result[1] + 2 > rtcdev::BVH_STACK) {
+            err = "device BVH deeper than the traversal stack";
+            cudaFree(s->arena);
+            s->arena = nullptr;
+            return 1;
+        }
+        d.bvh_root = result[0];
+        s->bvh_depth = result[1];
+        s->bvh_nodes = result[2];
+    }
     // always-tested list = ungated planes only -> keep them in the kernel parameters (device_scene.h, FastPlane)
     d.n_fast_planes = 0;
     d.plain_only = 1;
@@ -437,8 +515,8 @@ int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n
         }
     if (std::getenv("RTC_TRACE")) {
         auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
-        std::fprintf(stderr, "rtc_scene_create: host build %.3f ms, pack + upload to %d device(s) %.3f ms (%zu bytes each)\n", ms(t_build0, t_build1), n,
-                     ms(t_build1, std::chrono::steady_clock::now()), packed.blob.size());
+        std::fprintf(stderr, "rtc_scene_create: host build %.3f ms, pack + upload%s to %d device(s) %.3f ms (%zu bytes each)\n", ms(t_build0, t_build1),
+                     host->device_build ? " + device BVH build" : "", n, ms(t_build1, std::chrono::steady_clock::now()), packed.upload_bytes);
     }
     for (int i = 0; i < n; ++i) out[i] = made[(size_t)i].release();
     return 0;

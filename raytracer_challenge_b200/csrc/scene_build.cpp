@@ -702,6 +702,29 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         for (int k = 0; k < 3; ++k) S = std::max({S, std::fabs(root.lo[k]), std::fabs(root.hi[k])});
         // fp32 traversal error bound is ~9 * 2^-24 * S (DESIGN.md "conservative fp32 culling"); pad with margin
         const double pad = 4e-6 * std::max(S, 1e-30);
+        for (int k = 0; k < 3; ++k) { out.root_lo[k] = root.lo[k] - pad; out.root_hi[k] = root.hi[k] + pad; }
+        const int n_items = (int)item_ids.size();
+        const bool fast = (d.build_flags & RTC_BUILD_FAST) != 0 || std::getenv("RTC_DEVICE_BVH") != nullptr;  // (the variable: tests and probes)
+        if (fast && n_items >= rtcdev::LBVH_MIN_ITEMS && n_items <= rtcdev::LBVH_MAX_ITEMS && !std::getenv("RTC_HOST_BVH")) {
+            // The device builds the tree after the upload (bvh_build.cu): hand it the same padded fp32 item boxes the
+            // host build would use, and the leaf records in item order.
+            out.device_build = 1;
+            out.item_box32.resize((size_t)n_items * 8);
+            for (int i = 0; i < n_items; ++i) {
+                float* b = &out.item_box32[(size_t)i * 8];
+                for (int k = 0; k < 3; ++k) {
+                    b[k] = f32_down(item_boxes[(size_t)i].lo[k] - pad);
+                    b[4 + k] = f32_up(item_boxes[(size_t)i].hi[k] + pad);
+                }
+                b[3] = 0.0f;
+                b[7] = 0.0f;
+            }
+            out.item_ids = std::move(item_ids);
+            out.bvh_root = 0;
+            out.bvh_depth = 0;  // known after the device build
+            if (trace) std::fprintf(stderr, "build_host_scene: prims %.3f ms, group tree %.3f ms, device-build staging %.3f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, now()));
+            return "";
+        }
         Builder bld(item_boxes, pad);
         out.bvh_root = bld.compact(bld.build(0, (int)item_ids.size(), 0, bld.range_bounds(0, (int)item_ids.size())));
         out.bvh = std::move(bld.nodes);

@@ -25,6 +25,10 @@ struct HostScene {
     std::vector<rtcdev::BvhNode> bvh;
     std::vector<rtcdev::LeafItem> leaf_items;
     std::vector<double> leaf_tri;
+    std::vector<float> item_box32;      // device_build: 8 floats per BVH item (lo.xyz, 0, hi.xyz, 0), padded and rounded outwards
+    std::vector<int32_t> item_ids;      // device_build: primitive index (or ~csg root) per BVH item
+    int32_t device_build = 0;           // the BVH is built on the device after upload (rtc_scene_desc.build_flags & RTC_BUILD_FAST):
+                                        // bvh / leaf_items / leaf_tri stay empty here, the device fills its own copies
     std::vector<int32_t> unbounded;
     std::vector<rtcdev::ConeGuard> guards;
     std::vector<rtcdev::CsgOp> csg_ops;

@@ -559,9 +559,11 @@ class FlatScene {
         emit_children(0, world.elements);
     }
 
-    rtc_scene_desc desc() const {
+    // build_flags: RTC_BUILD_FAST for a scene that is rendered once and destroyed (Image::par_render)
+    rtc_scene_desc desc(uint32_t build_flags = 0) const {
         rtc_scene_desc d{};
         d.abi_version = RTC_ABI_VERSION;
+        d.build_flags = build_flags;
         d.n_prims = (int32_t)prims.size();
         d.n_nodes = (int32_t)nodes.size();
         d.n_children = (int32_t)children.size();
@@ -675,7 +677,7 @@ class Image {
     // failure (no device, CUDA error, overflow) throws.
     static Image par_render(const Camera& camera, const World& world, const RenderOptions& ro = RenderOptions{}) {
         FlatScene flat(world);
-        const rtc_scene_desc d = flat.desc();
+        const rtc_scene_desc d = flat.desc(RTC_BUILD_FAST);  // one frame, then the scene is released: BVH built on the device
         std::vector<int> devices = ro.devices;
         if (devices.empty()) {
             const int n = rtc_device_count();

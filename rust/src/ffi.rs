@@ -5,6 +5,8 @@
 use std::os::raw::{c_char, c_int};
 
 pub const RTC_ABI_VERSION: i32 = 2;
+/// rtc_scene_desc.build_flags: the scene is rendered once and destroyed -> build the BVH on the device (LBVH)
+pub const RTC_BUILD_FAST: u32 = 1;
 
 #[repr(C)]
 #[derive(Clone, Copy)]
@@ -81,6 +83,8 @@ pub struct rtc_scene_desc {
     pub n_materials: i32,
     pub n_patterns: i32,
     pub n_lights: i32,
+    /// RTC_BUILD_*: 0 = default (host SAH build); occupies the former alignment padding
+    pub build_flags: u32,
     pub prims: *const rtc_prim,
     pub nodes: *const rtc_node,
     pub children: *const i32,

@@ -138,6 +138,7 @@ impl FlatScene {
             abi_version: RTC_ABI_VERSION,
             n_prims: self.prims.len() as i32, n_nodes: self.nodes.len() as i32, n_children: self.children.len() as i32,
             n_materials: self.materials.len() as i32, n_patterns: self.patterns.len() as i32, n_lights: self.lights.len() as i32,
+            build_flags: RTC_BUILD_FAST, // Image::par_render builds, renders once and destroys
             prims: self.prims.as_ptr(), nodes: self.nodes.as_ptr(), children: self.children.as_ptr(),
             materials: self.materials.as_ptr(), patterns: self.patterns.as_ptr(), lights: self.lights.as_ptr(),
         }

@@ -52,6 +52,20 @@ def test_struct_layouts_match_a_c_compiler(built, tmp_path):
     assert sizes[2] == 4 + 4 + 16 * 8 + 3 * 8
 
 
+def test_build_flags_live_in_the_former_padding_of_the_scene_descriptor(built, tmp_path, lib_types):
+    """rtc_scene_desc.build_flags was added where the compiler used to pad (seven int32, then pointers): the size and the
+    pointer offsets of ABI version 2 are unchanged, and descriptors that never heard of the field read as 0 = default."""
+    src = tmp_path / "desc.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "rtc.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(rtc_scene_desc),'
+                   "offsetof(rtc_scene_desc, build_flags), offsetof(rtc_scene_desc, prims));return 0;}\n")
+    exe = tmp_path / "desc"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    size, off_flags, off_prims = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    Desc = lib_types[5]
+    assert (size, off_flags, off_prims) == (32 + 6 * 8, 28, 32)
+    assert (C.sizeof(Desc), Desc.build_flags.offset, Desc.prims.offset) == (size, off_flags, off_prims)
+
+
 def test_no_cuda_device_is_an_error_not_a_fallback(built):
     """The product path has no CPU fallback: opening a scene on a device fails loudly in this GPU-less container."""
     if R.device_count() > 0:
@@ -141,7 +155,7 @@ def lib_types():
 
     class Desc(C.Structure):
         _fields_ = [("abi_version", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("n_children", C.c_int32),
-                    ("n_materials", C.c_int32), ("n_patterns", C.c_int32), ("n_lights", C.c_int32),
+                    ("n_materials", C.c_int32), ("n_patterns", C.c_int32), ("n_lights", C.c_int32), ("build_flags", C.c_uint32),
                     ("prims", C.POINTER(Prim)), ("nodes", C.POINTER(Node)), ("children", C.POINTER(C.c_int32)),
                     ("materials", C.POINTER(Mat)), ("patterns", C.POINTER(Pat)), ("lights", C.POINTER(Light))]
 

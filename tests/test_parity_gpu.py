@@ -233,3 +233,23 @@ def test_planes_in_kernel_parameters_equal_the_general_list(built, name, monkeyp
         general, st2 = s.render(R.Opts())
     assert same_pixels(name, fast, general)
     assert (st.rays, st.surface_hits) == (st2.rays, st2.surface_hits)
+
+
+@pytest.mark.parametrize("name,w,h", [("teapot_low", 96, 54), ("benchmark", 96, 54), ("chapter14_title", 96, 54), ("teapot", 160, 90), ("fuzz:3", 96, 54)])
+def test_device_built_bvh_renders_the_same_frame(built, name, w, h, monkeypatch):
+    """RTC_BUILD_FAST (what Image::par_render passes: the scene lives for one frame) builds the BVH on the device
+    (bvh_build.cu, LBVH) instead of the host's binned-SAH build.  A BVH only culls: the frame must equal the SAH
+    build's and the brute-force scan's bit for bit."""
+    with R.Session(name, w, h, device=0) as s:
+        sah, st = s.render(R.Opts())
+        host_stats = dict(s.build_stats)
+    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
+    with R.Session(name, w, h, device=0) as s:
+        lbvh, st2 = s.render(R.Opts())
+        brute, _ = s.render(R.Opts(flags=1))
+        dev_stats = dict(s.build_stats)
+    assert same_pixels(name, sah, lbvh) and same_pixels(name, lbvh, brute)
+    assert (st.rays, st.surface_hits) == (st2.rays, st2.surface_hits)
+    if host_stats["bvh_items"] >= 64:  # smaller scenes keep the host build
+        assert dev_stats["bvh_depth"] >= 3 and 0 < dev_stats["bvh_nodes"] < dev_stats["bvh_items"]
+        assert dev_stats["device_bytes"] > host_stats["device_bytes"]  # the arena also holds the builder's scratch: the device path ran
