@@ -301,13 +301,14 @@ def run_cuda_inner(args):
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
-                       "l2": "256 MiB device memset between timed frames (L2 flush); per-level ray queues (134 MB per 2 Mi-ray batch) exceed L2 anyway"},
+                       "l2": "256 MiB device memset between timed frames (L2 flush); per-level ray queues (134 MB per 2 Mi-ray batch) exceed L2 anyway",
+                       "scene": "device-resident arm: scene handle created once (host binned-SAH BVH), frames rendered from it; end-to-end arm: scene created and destroyed every step"},
             "frame_ms": ms_per_step, "wall_ms_per_step": wall_ms / args.steps,
             "rays_per_frame": rays_all / args.steps, "ref_equivalent_rays_per_frame": rays_ref_all / args.steps,
             "ref_equivalent_mrays_per_s": rays_ref_all / args.steps / ms_per_step / 1e3,
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h, "frame_ms": e2e_ms_max / args.steps,
-                    "path": "rtc_scene_create + rtc_render (page-locked host f64 rgb, copies overlapped with tracing) + rtc_scene_destroy per step"
+                    "path": "rtc_scene_create (build_flags = RTC_BUILD_FAST as Image::par_render passes: flattening on the host, BVH built on the device) + rtc_render (page-locked host f64 rgb, copies overlapped with tracing) + rtc_scene_destroy per step"
                             + ("" if world == 1 else "; every rank writes its bands into one shared host image, shared-memory barrier per frame")},
             "gpu_launches": int(launches_all),
         }
