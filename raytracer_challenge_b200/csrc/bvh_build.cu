@@ -241,11 +241,10 @@ int build_lbvh(const LbvhArgs& a, cudaStream_t st) {
     int np2 = 1;
     while (np2 < a.n) np2 <<= 1;
     const size_t smem = (size_t)np2 * sizeof(unsigned long long);
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(sort_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, LBVH_MAX_ITEMS * (int)sizeof(unsigned long long)) != cudaSuccess) return (int)cudaGetLastError();
-        attr_set = true;
-    }
+    // (per device and cheap: set on every build rather than tracking which devices have seen it)
+    if (smem > 48u * 1024u &&
+        cudaFuncSetAttribute(sort_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, LBVH_MAX_ITEMS * (int)sizeof(unsigned long long)) != cudaSuccess)
+        return (int)cudaGetLastError();
     cudaMemsetAsync(a.counter, 0, sizeof(int) * (size_t)a.n, st);
     cudaMemsetAsync(a.result, 0, sizeof(int) * 4, st);
     const int block = 128, grid = (a.n + block - 1) / block;

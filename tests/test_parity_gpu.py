@@ -119,6 +119,17 @@ def test_par_render_multi_one_process(built):
     assert np.array_equal(img, one)
 
 
+def test_par_render_multi_full_teapot_uses_the_device_build_on_every_gpu(built):
+    """The 6 320-triangle mesh needs the 64 KB shared-memory sort of the device-side BVH build (an opt-in attribute that is
+    per device): Image::par_render over every visible device must equal a one-device render from a host-built scene."""
+    w, h = 128, 72
+    img, st = R.par_render_multi("teapot", w, h, n_devices=0)
+    with R.Session("teapot", w, h, device=0) as s:
+        one, st1 = s.render(R.Opts())
+    assert np.array_equal(img, one)
+    assert st.rays == st1.rays
+
+
 def test_window_equals_crop(built):
     with R.Session("glass_air_bubble", 80, 60, device=0) as s:
         whole, _ = s.render(R.Opts())
