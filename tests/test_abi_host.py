@@ -74,6 +74,22 @@ def test_no_cuda_device_is_an_error_not_a_fallback(built):
         R.Session("default_world", 16, 16, device=0)
 
 
+@pytest.mark.parametrize("name,items,staged", [("teapot", 6320, True), ("benchmark", 1000, True), ("hexagon", 12, False)])
+def test_fast_build_stages_the_items_for_the_device_and_builds_no_host_tree(built, name, items, staged, monkeypatch):
+    """rtc_scene_desc.build_flags & RTC_BUILD_FAST (here through its test hook RTC_DEVICE_BVH): scenes with 64..8192 BVH
+    items leave the tree to the device (bvh_build.cu), so the host half reports no nodes; tiny scenes keep the host build."""
+    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
+    s = R.Session(name, 64, 36, device=-1)
+    b = s.build_stats
+    s.close()
+    assert b["bvh_items"] == items
+    assert (b["bvh_nodes"] == 0) == staged
+    monkeypatch.delenv("RTC_DEVICE_BVH")
+    s = R.Session(name, 64, 36, device=-1)
+    assert s.build_stats["bvh_nodes"] >= 1
+    s.close()
+
+
 @pytest.mark.parametrize("name", R.SCENES + ["fuzz:1", "fuzz:2", "fuzz:3", "fuzz:7"])
 def test_host_scene_build(built, name):
     """rtc_scene_validate = the host half of rtc_scene_create: flatten, dedupe transforms, classify group boxes, build
