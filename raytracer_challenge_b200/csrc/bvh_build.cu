@@ -10,9 +10,10 @@
 //                   prefix length; children / parents / ranges written in one pass
 //   fit_boxes       bottom-up: each leaf walks towards the root, the second arrival at a node (atomic counter) unites
 //                   the children's boxes
-//   emit_nodes      subtrees of <= leaf_max items collapse into leaves (the traversal's leaf format); the surviving internal
-//                   nodes are numbered by a block-wide prefix sum and written as 64-byte BvhNodes (both child boxes
-//                   + links), exactly what the SAH build produces for the traversal kernels
+//   number_nodes    subtrees of <= leaf_max items collapse into leaves (the traversal's leaf format); the surviving internal
+//                   nodes are numbered by a block-wide prefix sum
+//   emit_nodes      ... and written as 64-byte BvhNodes (both child boxes + links), exactly what the SAH build produces
+//                   for the traversal kernels
 //   permute_items   leaf items (header + triangle record) gathered into sorted order, so a leaf's items are contiguous
 //
 // Culling structure only: the boxes are the same padded, outward-rounded fp32 item boxes the host build uses, so the
@@ -57,12 +58,11 @@ __global__ void __launch_bounds__(1024) sort_keys(LbvhArgs a, int np2) {
     for (int k = 2; k <= np2; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
             __syncthreads();
-            for (int i = threadIdx.x; i < np2; i += blockDim.x) {
-                const int p = i ^ j;
-                if (p > i) {
-                    const unsigned long long x = sk[i], y = sk[p];
-                    if ((x > y) == ((i & k) == 0)) { sk[i] = y; sk[p] = x; }
-                }
+            for (int t = threadIdx.x; t < (np2 >> 1); t += blockDim.x) {  // one compare-exchange per pair (i, i + j)
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int p = i | j;
+                const unsigned long long x = sk[i], y = sk[p];
+                if ((x > y) == ((i & k) == 0)) { sk[i] = y; sk[p] = x; }
             }
         }
     __syncthreads();
@@ -139,64 +139,77 @@ __global__ void fit_boxes(LbvhArgs a) {
     }
 }
 
-// One block: numbers the internal nodes that survive the collapse (range of more than leaf_max items) and writes them.
-__global__ void __launch_bounds__(1024) emit_nodes(LbvhArgs a) {
-    __shared__ int s_sum[1024];
+// One block: numbers the internal nodes that survive the collapse (range of more than leaf_max items), in index order,
+// 1 024 nodes per step: ballot + popc inside a warp, a shuffle scan over the 32 warp totals, a running base.
+__global__ void __launch_bounds__(1024) number_nodes(LbvhArgs a) {
+    __shared__ int s_warp[32];
+    __shared__ int s_base;
     const int n_int = a.n - 1;
-    const int per = (n_int + (int)blockDim.x - 1) / (int)blockDim.x;
-    const int b0 = (int)threadIdx.x * per, b1 = min(b0 + per, n_int);
-    int mine = 0;
-    for (int i = b0; i < b1; ++i) {
-        const int2 r = a.range[i];
-        mine += (r.y - r.x + 1 > a.leaf_max) ? 1 : 0;
-    }
-    s_sum[threadIdx.x] = mine;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_base = 0;
     __syncthreads();
-    for (int off = 1; off < (int)blockDim.x; off <<= 1) {  // Hillis-Steele inclusive scan
-        const int v = (int)threadIdx.x >= off ? s_sum[threadIdx.x - off] : 0;
-        __syncthreads();
-        s_sum[threadIdx.x] += v;
-        __syncthreads();
-    }
-    int at = s_sum[threadIdx.x] - mine;
-    for (int i = b0; i < b1; ++i) {
-        const int2 r = a.range[i];
-        const bool kept = r.y - r.x + 1 > a.leaf_max;
-        a.dense[i] = kept ? at : -1;
-        at += kept ? 1 : 0;
-    }
-    if (threadIdx.x == blockDim.x - 1) a.result[2] = s_sum[threadIdx.x];  // number of nodes
-    __threadfence_block();
-    __syncthreads();
-    for (int i = b0; i < b1; ++i) {
-        const int me = a.dense[i];
-        if (me < 0) continue;
-        const int2 ch = a.child[i];
-        BvhNode nd;
-        int links[2];
-        float4 lo[2], hi[2];
-        const int c[2] = {ch.x, ch.y};
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            child_box(a, c[k], lo[k], hi[k]);
-            if (c[k] < 0) links[k] = ~((~c[k]) << 2);  // one item
-            else {
-                const int2 r = a.range[c[k]];
-                const int count = r.y - r.x + 1;
-                links[k] = count > a.leaf_max ? a.dense[c[k]] : ~((r.x << 2) | (count - 1));
-            }
+    for (int tile = 0; tile < n_int; tile += 1024) {
+        const int i = tile + (int)threadIdx.x;
+        bool kept = false;
+        if (i < n_int) {
+            const int2 r = a.range[i];
+            kept = r.y - r.x + 1 > a.leaf_max;
         }
-        nd.lo0[0] = lo[0].x; nd.lo0[1] = lo[0].y; nd.lo0[2] = lo[0].z;
-        nd.hi0[0] = hi[0].x; nd.hi0[1] = hi[0].y; nd.hi0[2] = hi[0].z;
-        nd.lo1[0] = lo[1].x; nd.lo1[1] = lo[1].y; nd.lo1[2] = lo[1].z;
-        nd.hi1[0] = hi[1].x; nd.hi1[1] = hi[1].y; nd.hi1[2] = hi[1].z;
-        nd.c0 = links[0];
-        nd.c1 = links[1];
-        nd.pad0 = 0;
-        nd.pad1 = 0;
-        a.bvh[me] = nd;
+        const unsigned m = __ballot_sync(0xffffffffu, kept);
+        if (lane == 0) s_warp[warp] = __popc(m);
+        __syncthreads();
+        if (warp == 0) {
+            int v = s_warp[lane];
+            for (int off = 1; off < 32; off <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, v, off);
+                if ((int)lane >= off) v += u;
+            }
+            s_warp[lane] = v;  // inclusive
+        }
+        __syncthreads();
+        const int base = s_base + (warp ? s_warp[warp - 1] : 0);
+        if (i < n_int) a.dense[i] = kept ? base + __popc(m & ((1u << lane) - 1u)) : -1;
+        __syncthreads();
+        if (threadIdx.x == 0) s_base += s_warp[31];
+        __syncthreads();
     }
-    if (threadIdx.x == 0) a.result[0] = 0;  // the root is internal node 0, kept (n > leaf_max) and numbered first
+    if (threadIdx.x == 0) {
+        a.result[2] = s_base;  // number of nodes
+        a.result[0] = 0;       // the root is internal node 0, kept (n > leaf_max) and numbered first
+    }
+}
+
+// Surviving internal node -> 64-byte BvhNode: both child boxes + links (inner node: its number; collapsed subtree or
+// single item: leaf link ~(first << 2 | count - 1)).
+__global__ void emit_nodes(LbvhArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n - 1) return;
+    const int me = a.dense[i];
+    if (me < 0) return;
+    const int2 ch = a.child[i];
+    BvhNode nd;
+    int links[2];
+    float4 lo[2], hi[2];
+    const int c[2] = {ch.x, ch.y};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        child_box(a, c[k], lo[k], hi[k]);
+        if (c[k] < 0) links[k] = ~((~c[k]) << 2);  // one item
+        else {
+            const int2 r = a.range[c[k]];
+            const int count = r.y - r.x + 1;
+            links[k] = count > a.leaf_max ? a.dense[c[k]] : ~((r.x << 2) | (count - 1));
+        }
+    }
+    nd.lo0[0] = lo[0].x; nd.lo0[1] = lo[0].y; nd.lo0[2] = lo[0].z;
+    nd.hi0[0] = hi[0].x; nd.hi0[1] = hi[0].y; nd.hi0[2] = hi[0].z;
+    nd.lo1[0] = lo[1].x; nd.lo1[1] = lo[1].y; nd.lo1[2] = lo[1].z;
+    nd.hi1[0] = hi[1].x; nd.hi1[1] = hi[1].y; nd.hi1[2] = hi[1].z;
+    nd.c0 = links[0];
+    nd.c1 = links[1];
+    nd.pad0 = 0;
+    nd.pad1 = 0;
+    a.bvh[me] = nd;
 }
 
 // Leaf records in sorted order, so the items of a leaf are contiguous: the 16-byte header the traversal reads instead of
@@ -252,7 +265,8 @@ int build_lbvh(const LbvhArgs& a, cudaStream_t st) {
     sort_keys<<<1, 1024, smem, st>>>(a, np2);
     build_hierarchy<<<grid, block, 0, st>>>(a);
     fit_boxes<<<grid, block, 0, st>>>(a);
-    emit_nodes<<<1, 1024, 0, st>>>(a);
+    number_nodes<<<1, 1024, 0, st>>>(a);
+    emit_nodes<<<grid, block, 0, st>>>(a);
     permute_items<<<grid, block, 0, st>>>(a);
     return (int)cudaGetLastError();
 }
