@@ -385,7 +385,7 @@ def rooflines(R, prof, world):
         "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_source,
         "launches_per_frame": n_launch, "achieved_bytes_per_launch": d["bytes"] / max(n_launch, 1), "ms_per_launch": d["ms"] / max(n_launch, 1), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
         "ms_per_frame_in_this_kernel": d["ms"], "algorithmic_bytes_per_frame": d["bytes"],
-        "note": "HBM sees only ray queues, hit lists and the frame buffer (the 1.6 MB scene is L1/L2-resident): this path is bound by "
+        "note": "HBM sees only ray queues, hit lists and the frame buffer (the 2.1 MB scene is L1/L2-resident): this path is bound by "
                 "CUDA-core issue under divergence and by L1/L2 latency on BVH fetches, not by HBM — see roofline_fp64 / roofline_fp32, "
                 "profiles/README.md (ncu: issue-slot utilisation, active threads per instruction, stall reasons) and DESIGN.md",
         "scope": "rank 0's shard of the frame" if world > 1 else "whole frame",

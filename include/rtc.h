@@ -177,7 +177,8 @@ typedef struct rtc_scene rtc_scene;
 /* Number of CUDA devices visible (0 or negative status on failure -> rtc_last_error). */
 int rtc_device_count(void);
 
-/* Copies and uploads the scene to CUDA device `device`, building the BVH.  0 = ok. */
+/* Copies and uploads the scene to CUDA device `device`, building the BVH (on the host — binned SAH — or, with
+ * desc->build_flags & RTC_BUILD_FAST and 64..8192 bounded items, on the device after the upload).  0 = ok. */
 int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
 
 /* The same for `n` distinct devices at once: ONE host build (validation, flattening, BVH), one upload per device
