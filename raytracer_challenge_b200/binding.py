@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_DIR = os.path.join(ROOT, "raytracer_challenge_b200", "lib")
 DATA_DIR = os.path.join(ROOT, "data")
 SCENES = ["default_world", "three_spheres", "glass_air_bubble", "hexagon", "benchmark", "teapot", "teapot_low", "csg_noise",
-          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope"]
+          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope", "axis_aligned", "no_shadow_flat"]
 
 
 class RtcError(RuntimeError):

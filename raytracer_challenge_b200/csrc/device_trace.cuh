@@ -199,18 +199,32 @@ struct Walk {
     float tlo;   // lower end of the admissible interval, relative to te
 };
 
+// Inverse direction component of the fp32 walk.  A slab plane sits at fma(plane, i, -o * i): with an INFINITE i (a
+// direction component that is zero, or below ~1e-38 in fp32) the two planes of that axis become inf - inf = NaN when
+// the plane and the origin have the same sign and -+inf otherwise, and the min / max chain then culls boxes that
+// straddle 0 on that axis although the ray runs inside the slab.  So |i| is clamped to 2^60: multiplying by a power
+// of two is exact, hence fma(plane, i, -o * i) = (plane - o) * 2^60 rounded once, its sign is exactly the sign of
+// plane - o, and its magnitude — at least 2^60 * (the padding of the boxes, 4e-6 x scene extent) for a ray inside the
+// true box — is beyond any t a query can ask for.  Geometrically the clamped axis is a ray tilted by < 2^-60: over the
+// scene's extent that is far inside the padding, so the walk stays conservative ("conservative fp32 culling").
+__device__ __forceinline__ float walk_inverse(double d) {
+    const float i = 1.0f / (float)d;
+    const float big = 1152921504606846976.0f;  // 2^60
+    return fabsf(i) <= big ? i : copysignf(big, i);  // (a NaN direction lands here too: any finite value will do)
+}
+
 // mode 0: hits with t >= 0 (closest / shadow); mode 1: every crossing up to tmax (also negative t).
 // Returns false if the ray cannot touch any BVH item.
 __device__ __forceinline__ bool walk_setup(const Scene& sc, const Ray& ray, int mode, Walk& w) {
     // The root-box interval only decides where the fp32 walk is re-originated and whether the ray can be dropped
     // without a walk — culling, not parity — so it is computed in fp32 (three f64 divisions less per query) and a ray
     // is dropped only when it misses by more than the fp32 error of the interval ends (relative 2^-22 is ~10x the
-    // error of a subtract-convert-multiply chain).  The root box is padded like every other box.  Infinite or NaN
-    // ends (zero direction components) never reject: comparisons with NaN are false, fminf / fmaxf ignore NaN.
+    // error of a subtract-convert-multiply chain).  The root box is padded like every other box.  NaN ends (a NaN
+    // ray) never reject: comparisons with NaN are false, fminf / fmaxf ignore NaN.
     const double o[3] = {ray.o.x, ray.o.y, ray.o.z}, d[3] = {ray.d.x, ray.d.y, ray.d.z};
-    w.ix = 1.0f / (float)d[0];
-    w.iy = 1.0f / (float)d[1];
-    w.iz = 1.0f / (float)d[2];
+    w.ix = walk_inverse(d[0]);
+    w.iy = walk_inverse(d[1]);
+    w.iz = walk_inverse(d[2]);
     const float inv[3] = {w.ix, w.iy, w.iz};
     float tn = -CUDART_INF_F, tf = CUDART_INF_F;
 #pragma unroll
@@ -232,8 +246,7 @@ __device__ __forceinline__ bool walk_setup(const Scene& sc, const Ray& ray, int 
     if (!(fabs(w.te) <= 1.7e38)) { w.te = 0.0; w.tlo = mode == 0 ? 0.0f : -CUDART_INF_F; }
     // One fused multiply-add per plane instead of a subtract and a multiply (explicit: the build has -fmad=false for
     // the f64 code).  The extra rounding of p is <= 2^-24 |o| in distance, far inside the padding of the boxes
-    // ("conservative fp32 culling").  A zero direction component gives inf - inf = NaN, which the
-    // min / max chain ignores: that axis then rejects nothing, which is still a superset.
+    // ("conservative fp32 culling").  Zero direction components: see walk_inverse.
     w.px = (float)(o[0] + w.te * d[0]) * w.ix;
     w.py = (float)(o[1] + w.te * d[1]) * w.iy;
     w.pz = (float)(o[2] + w.te * d[2]) * w.iz;

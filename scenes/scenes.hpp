@@ -30,7 +30,7 @@ inline std::string& data_dir() {
     return d;
 }
 
-// Binary mesh fixture written by tools/make_mesh_fixture.py from an OBJ file:
+// Binary mesh fixture written by oracle/obj2mesh.cpp (`make -C oracle fixtures`) from an OBJ file:
 //   "RTCMESH1" | u32 nv, nvn, ntri, ngroups | nv*3 f64 | nvn*3 f64 |
 //   ntri * (u32 p1,p2,p3,n1,n2,n3 (1-based; n = 0 when absent), u32 group) | ngroups * (u32 len, bytes)
 template <class A>
@@ -814,11 +814,78 @@ Scene<A> cone_slope(size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- authored: rays with direction components that are exactly zero -------------------------------------------
+// The camera sits OFF the origin and looks exactly along +z, so with hsize == 1 every primary ray has d.x == 0.0
+// (world_x = half_width - 0.5 * (2 * half_width) = 0 exactly, src/camera.rs:40-50) and with vsize == 1 every ray has
+// d.y == 0.0; a light sits exactly above the camera column, so the shadow rays of hits with x == 1 also have
+// d.x == 0.0.  The 27 items form a BVH whose inner boxes straddle 0 on x and y while the ray origins do not: the case
+// an fp32 slab test with infinite inverse directions gets wrong (walk_inverse in device_trace.cuh).
+template <class A>
+Scene<A> axis_aligned(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, -0.25, 0.0),
+                                        material_with<A>(P::checkers(M::id(), P::plain(C::make(0.8, 0.8, 0.8)), P::plain(C::make(0.3, 0.3, 0.35))), {{'s', 0.0}, {'r', 0.3}}))));
+    int k = 0;
+    for (int ix = 0; ix < 3; ix++)
+        for (int iy = 0; iy < 3; iy++)
+            for (int iz = 0; iz < 3; iz++, k++) {
+                const auto mat = material_with<A>(P::plain(C::make(0.2 + 0.3 * ix, 0.9 - 0.3 * iy, 0.3 + 0.25 * iz)), {{'r', (k % 3 == 0) ? 0.4 : 0.0}});
+                const auto args = shape_args<A>(M::translation(-0.5 + 1.5 * ix, 0.5 + 1.5 * iy, 1.5 * iz) * M::scaling(0.45, 0.45, 0.45), mat);
+                el.push_back((k & 1) ? E::cube(args) : E::sphere(args));
+            }
+    s.world.lights.push_back({C::make(0.8, 0.8, 0.8), V::point(1.0, 12.0, -6.0)});
+    s.world.lights.push_back({C::make(0.3, 0.3, 0.3), V::point(-7.0, 2.0, -6.0)});
+    s.camera = A::Camera::make(hsize, vsize, 0.8,
+                               A::Camera::transform(V::point(1.0, 2.0, -6.0), V::point(1.0, 2.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- authored: shapes that do not cast shadows, and flat triangles ---------------------------------------------
+// World::is_shadowed looks at the NEAREST crossing only (src/world.rs:40-47): a shape with casts_shadow == false in
+// front of a casting one removes the shadow, so shadow queries cannot stop at the first crossing they meet.  The
+// pyramid and the tilted quad are flat triangles (Geometry::Triangle, one precomputed normal, src/shape.rs:369-385),
+// which no example binary uses.
+template <class A>
+Scene<A> no_shadow_flat(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.9, 0.9, 0.85)), {{'s', 0.0}}))));
+    // a casting cube with a non-casting sphere between it and the light, and a non-casting sphere on its own
+    el.push_back(E::cube(shape_args<A>(M::translation(-1.5, 1.0, 0.5) * M::scaling(0.6, 1.0, 0.6), material_with<A>(P::plain(C::make(0.8, 0.3, 0.2)), {}))));
+    auto ghost = shape_args<A>(M::translation(-2.6, 2.6, -0.9) * M::scaling(0.7, 0.7, 0.7), material_with<A>(P::plain(C::make(0.3, 0.8, 0.9)), {{'r', 0.2}}));
+    ghost.casts_shadow = false;
+    el.push_back(E::sphere(ghost));
+    auto ghost2 = shape_args<A>(M::translation(2.4, 0.6, -1.0) * M::scaling(0.6, 0.6, 0.6), material_with<A>(P::plain(C::make(0.9, 0.8, 0.2)), {}));
+    ghost2.casts_shadow = false;
+    el.push_back(E::sphere(ghost2));
+    // flat-triangle pyramid (4 sides) inside a group, and a tilted quad of two flat triangles
+    const V apex = V::point(0.0, 1.6, 0.0);
+    const V base[4] = {V::point(-0.8, 0.0, -0.8), V::point(0.8, 0.0, -0.8), V::point(0.8, 0.0, 0.8), V::point(-0.8, 0.0, 0.8)};
+    std::vector<E> sides;
+    for (int i = 0; i < 4; i++)
+        sides.push_back(E::triangle(shape_args<A>(M::id(), material_with<A>(P::stripes(M::scaling(0.2, 0.2, 0.2), P::plain(C::make(0.9, 0.6, 0.1)), P::plain(C::make(0.3, 0.2, 0.5))), {})),
+                                    base[i], base[(i + 1) % 4], apex));
+    el.push_back(E::composite(M::translation(0.6, 0.0, 0.4) * M::rotation_y(0.5), std::nullopt, G::Aggregation, std::move(sides)));
+    auto quad = shape_args<A>(M::translation(0.5, 0.0, 2.5) * M::rotation_x(-0.4), material_with<A>(P::plain(C::make(0.5, 0.5, 0.9)), {{'r', 0.3}}));
+    el.push_back(E::triangle(quad, V::point(-2.0, 0.0, 0.0), V::point(2.0, 0.0, 0.0), V::point(2.0, 2.5, 0.0)));
+    el.push_back(E::triangle(quad, V::point(-2.0, 0.0, 0.0), V::point(2.0, 2.5, 0.0), V::point(-2.0, 2.5, 0.0)));
+    s.world.lights.push_back({C::make(0.9, 0.9, 0.9), V::point(-6.0, 7.0, -5.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.0,
+                               A::Camera::transform(V::point(0.5, 3.0, -7.0), V::point(0.0, 1.0, 0.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
-                                               "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope"};
+                                               "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope",
+                                               "axis_aligned", "no_shadow_flat"};
     return n;
 }
 
@@ -839,6 +906,8 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "chapter14_title") return chapter14_title<A>(hsize, vsize);
     if (name == "cover") return cover<A>(hsize, vsize);
     if (name == "cone_slope") return cone_slope<A>(hsize, vsize);
+    if (name == "axis_aligned") return axis_aligned<A>(hsize, vsize);
+    if (name == "no_shadow_flat") return no_shadow_flat<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");
 }

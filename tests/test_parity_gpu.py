@@ -23,6 +23,12 @@ CASES = [
     ("chapter14_title", 192, 100),      # open cones and cylinders in nested groups, four lights
     ("cover", 128, 128),                # glass sphere + 17 cubes in nested groups, two lights
     ("cone_slope", 33, 33),             # rays along a cone's slope: the single-root branch without y-range check (src/shape.rs:811-818)
+    # direction components that are exactly zero (walk_inverse): hsize == 1 -> d.x == 0, vsize == 1 -> d.y == 0
+    ("axis_aligned", 1, 48),
+    ("axis_aligned", 48, 1),
+    ("axis_aligned", 1, 1),
+    ("axis_aligned", 65, 37),
+    ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
 
 
@@ -204,6 +210,54 @@ def test_ppm_through_the_host_api(built):
     vals = np.array(" ".join(body).split(), dtype=np.int64).reshape(h, w, 3)
     ref, _, _ = oracle_render("default_world", w, h)
     assert np.array_equal(vals, oracle_quantize(ref))
+
+
+# ---- BASELINE.json sizes: oracle-checked windows inside the full-size frame of every config -------------------------
+# (C1's 11x11 and C4's 3840x2160 are covered by test_known_answer_pixel / test_full_size_teapot_properties.)
+BASELINE_WINDOWS = [
+    # C2: chapter 11 glass air bubble, 1920x1080, fuel 5
+    ("glass_air_bubble", 1920, 1080, (1, 1), [(952, 536, 16, 8), (700, 420, 16, 8), (1100, 300, 16, 8)]),
+    # C3: chapter 14 hexagon (silhouette edge, jittered stripes) and benchmark (sphere block, backdrop), 3840x2160
+    ("hexagon", 3840, 2160, (1, 1), [(2160, 540, 16, 8), (2640, 945, 16, 8), (1200, 675, 16, 8)]),
+    ("benchmark", 3840, 2160, (1, 1), [(1900, 1000, 16, 8), (1560, 520, 16, 8)]),
+    # C5: CSG + Simplex / fractal noise, 7680x4320 with 4x4 supersampling: a CSG edge, the glass lens (edge, inside), the
+    # fractal-noise floor, the cone-union-sphere tower
+    ("csg_noise", 7680, 4320, (4, 4), [(1600, 1120, 16, 8), (4160, 1350, 16, 8), (4480, 1350, 16, 8), (3840, 3840, 16, 8), (6000, 1280, 16, 8)]),
+]
+
+
+@pytest.mark.parametrize("name,w,h,spp,windows", BASELINE_WINDOWS, ids=[c[0] for c in BASELINE_WINDOWS])
+def test_windows_at_the_baseline_size_match_the_oracle(built, name, w, h, spp, windows):
+    with R.Session(name, w, h, device=0) as s:
+        for win in windows:
+            ref, counts, _ = oracle_render(name, w, h, window=win, spp=spp)
+            img, st = s.render(R.Opts(window=win, spp=spp))
+            rep = compare_images(img, ref)
+            assert rep["ok"] and rep["max_abs_f64"] < 1e-9, (win, rep)
+            assert st.rays_ref == int(counts.sum()), (win, st.as_dict(), counts)
+
+
+def test_full_size_config5_properties(built):
+    """7680x4320 x (4x4) samples per pixel = 531 M primary rays (BASELINE.json configs[4]): the frame assembled from 8 band
+    shards equals the unsharded frame; windows of the full frame equal the same windows rendered alone (which
+    test_windows_at_the_baseline_size_match_the_oracle ties to the oracle); ray-count identities."""
+    from raytracer_challenge_b200 import sharding
+
+    w, h, spp = 7680, 4320, (4, 4)
+    with R.Session("csg_noise", w, h, device=0) as s:
+        whole, st = s.render(R.Opts(spp=spp))
+        assert st.rays_primary == w * h * 16
+        assert st.rays_shadow == 2 * st.surface_hits  # two lights
+        assert st.rays_ref >= st.rays
+        assert np.isfinite(whole).all()
+        for win in [(1600, 1120, 16, 8), (4480, 1350, 16, 8), (7664, 4312, 16, 8), (0, 0, 16, 8)]:
+            alone, _ = s.render(R.Opts(window=win, spp=spp))
+            x, y, ww, wh = win
+            assert same_pixels("csg_noise", whole[y:y + wh, x:x + ww], alone), win
+        frame = np.full((h, w, 3), np.nan)
+        for r in range(8):
+            s.render(sharding.band_opts(w, r, 8, spp=spp), out=frame)
+        assert same_pixels("csg_noise", frame, whole)
 
 
 # ---- full-size properties (BASELINE.json sizes; the brute-force oracle cannot finish these in seconds) -----------
