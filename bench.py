@@ -1,12 +1,14 @@
 #!/usr/bin/env python
-"""Headline benchmark: BASELINE.json's metric (Mrays/s and frame ms) on the teapot config.
+"""Headline benchmark: BASELINE.json's metric (Mrays/s and frame ms).
 
-  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU)
-  python bench.py --impl reference --steps K --warmup W    # the reference algorithm on the host cores (oracle port)
+  python bench.py --gpus N --steps K --warmup W [--config c4]   # this repo's CUDA path (one process per GPU)
+  python bench.py --impl reference --steps K --warmup W         # the reference algorithm on the host cores (oracle port)
 
-A "step" is one frame: chapter15 teapot (6 320 smooth triangles, 3 reflective planes, 2 lights) at 3840x2160,
-fuel 5 (BASELINE.json configs[3], the config north_star's target is quoted on).  At N > 1 the frame's bands of four
-pixel rows are dealt round-robin to the ranks (strong scaling: the frame is fixed); no collective is on the data path.
+A "step" is one frame.  Default config c4 = BASELINE.json configs[3], the one north_star's target is quoted on:
+chapter15 teapot (6 320 smooth triangles, 3 reflective planes, 2 lights) at 3840x2160, fuel 5.  --config c5 is
+configs[4] (CSG + Simplex / fractal noise, 7680x4320 with 4x4 supersampling); c2 / c3h / c3b are the other full-size
+configs.  At N > 1 the frame's bands of four pixel rows are dealt round-robin to the ranks (strong scaling: the frame is
+fixed); no collective is on the data path.
 
   value  : whole-job Mrays/s with the scene resident in HBM and the frame left in HBM; rays = rays actually traced
            (primary + shadow + reflected + refracted, R_uniq of SURVEY.md §8(d)); time = CUDA events on the
@@ -28,17 +30,34 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-SCENE = "teapot"
-WIDTH, HEIGHT, FUEL = 3840, 2160, 5
-WORKLOAD = "chapter15_teapot (teapot_high.obj, 6320 smooth triangles + 3 reflective planes, 2 lights) 3840x2160 fuel 5"
-CPU_WINDOW = (1664, 952, 512, 256)  # bounded CPU sample: a 512x256 window at the frame centre (on the teapot)
 METRIC = "Mrays/s (primary+secondary+shadow)"
+
+# BASELINE.json configs at their full sizes.  c4 (configs[3]) is the one north_star's target is quoted on: the default,
+# and the line the driver records.  cpu_window: the bounded CPU sample of the same frame (x0, y0, w, h).
+# f64_per_prim: flops of the scene's usual non-triangle intersection (plane through one matrix row: 11 + 2; sphere 32;
+# mixed CSG scenes ~40); f64_per_pattern: flops of the pattern evaluation per (hit, light) (plain 0; a mixture ~32; jittered
+# patterns ~3 Simplex evaluations = ~400), SURVEY.md §8(d).
+CONFIGS = {
+    "c2": dict(scene="glass_air_bubble", w=1920, h=1080, spp=(1, 1), fuel=5, lights=1, f64_per_prim=32.0, f64_per_pattern=32.0, cpu_window=(704, 412, 512, 256),
+               workload="chapter11_glass_air_bubble (two concentric glass spheres over a checkered plane, 1 light) 1920x1080 fuel 5"),
+    "c3h": dict(scene="hexagon", w=3840, h=2160, spp=(1, 1), fuel=5, lights=1, f64_per_prim=40.0, f64_per_pattern=400.0, cpu_window=(0, 0, 3840, 2160),
+                workload="chapter14_hexagon (6 spheres + 6 open cylinders in nested groups, Simplex point-jitter stripes, 1 light) 3840x2160 fuel 5"),
+    "c3b": dict(scene="benchmark", w=3840, h=2160, spp=(1, 1), fuel=5, lights=1, f64_per_prim=32.0, f64_per_pattern=32.0, cpu_window=(1408, 824, 1024, 512),
+                workload="chapter14_benchmark (1000 spheres in 8 groups + backdrop plane, 1 light) 3840x2160 fuel 5"),
+    "c4": dict(scene="teapot", w=3840, h=2160, spp=(1, 1), fuel=5, lights=2, f64_per_prim=13.0, f64_per_pattern=0.0, cpu_window=(1664, 952, 512, 256),
+               workload="chapter15_teapot (teapot_high.obj, 6320 smooth triangles + 3 reflective planes, 2 lights) 3840x2160 fuel 5"),
+    "c5": dict(scene="csg_noise", w=7680, h=4320, spp=(4, 4), fuel=5, lights=2, f64_per_prim=40.0, f64_per_pattern=400.0, cpu_window=(3712, 2096, 256, 128),
+               workload="CSG (nested difference / intersection / union, glass lens) + Simplex / fractal-noise patterns, 2 lights, 7680x4320 with 4x4 supersampling (530.8 M primary rays), fuel 5"),
+}
+CFG = CONFIGS["c4"]  # set by main()
 
 # Algorithmic cost model (DESIGN.md "Roofline"): flops per unit of traversal work, counted from the reference's
 # arithmetic; the units themselves are counted by the kernels (rtc_stats).
 F32_PER_NODE = 24.0      # two slab tests: 6 sub + 6 mul each (min/max/compare = 0)
+NODE_BYTES = 64.0        # one BVH node visit: both child boxes + links, from L1/L2
+TRI_TEST_BYTES = 96.0    # one triangle test: 16 B leaf header + 80 B (p1, e1, e2) record, from L1/L2
+HIT_FETCH_BYTES = 480.0  # per surface hit: primitive + material + both matrices + triangle normals (384 + 96)
 F64_PER_TRIANGLE = 46.0  # Moller-Trumbore, src/shape.rs:824-860
-F64_PER_PLANE = 2.0      # the teapot scene's only non-triangle primitives are planes, src/shape.rs:622-633
 F64_PER_XFORM = 33.0     # affine Ray::transform: 18 mul + 15 add (src/ray.rs:14-19 on rows 0..2)
 F64_PER_HIT = 130.0      # prepare_state + normal (+ schlick when transparent), SURVEY.md §8(d)
 F64_PER_HIT_LIGHT = 95.0 + 18.0  # Phong term + shadow-ray setup, per light
@@ -104,12 +123,28 @@ class ClockSampler:
         return out
 
 
+def cpu_sample_text():
+    x0, y0, w, h = CFG["cpu_window"]
+    spp = CFG["spp"][0] * CFG["spp"][1]
+    return (f"window {w}x{h} at ({x0},{y0}) of the {CFG['w']}x{CFG['h']} frame" + (f" x {spp} samples per pixel" if spp > 1 else "") +
+            "; rays = World::intersect queries of the reference algorithm (R_ref, with its per-light duplication of secondary rays)")
+
+
 def cpu_reference_step(threads=0):
     """One bounded sample of the workload with the reference algorithm (oracle port of the Rust code)."""
     from common import oracle_render  # tests/common.py: ctypes access to build/liboracle.so
 
-    img, counts, sec = oracle_render(SCENE, WIDTH, HEIGHT, window=CPU_WINDOW, fuel=FUEL, threads=threads)
+    img, counts, sec = oracle_render(CFG["scene"], CFG["w"], CFG["h"], window=CFG["cpu_window"], fuel=CFG["fuel"], spp=CFG["spp"], threads=threads)
     return int(counts.sum()), sec
+
+
+def cpu_baseline_entry(rays, sec, steps=1):
+    x0, y0, w, h = CFG["cpu_window"]
+    px = w * h
+    ms = sec / steps * 1e3
+    return {"value": rays / sec / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port", "sample": cpu_sample_text() + f", {sec / steps:.1f} s per sample",
+            "rays": "R_ref (the GPU arm's comparable figure is ref_equivalent_mrays_per_s; its `value` counts R_uniq)",
+            "ms_per_sample_pixel": ms / px, "frame_ms_scaled_by_pixels": ms / px * CFG["w"] * CFG["h"]}
 
 
 def run_reference(args):
@@ -119,7 +154,6 @@ def run_reference(args):
     from raytracer_challenge_b200 import _build
 
     _build.build_oracle()
-    cores = os.cpu_count() or 1
     for _ in range(args.warmup):
         cpu_reference_step()
     rays, secs = 0, 0.0
@@ -128,15 +162,11 @@ def run_reference(args):
         rays += r
         secs += s
     value = rays / secs / 1e6
-    px = CPU_WINDOW[2] * CPU_WINDOW[3]
-    sample = (f"window {CPU_WINDOW[2]}x{CPU_WINDOW[3]} at ({CPU_WINDOW[0]},{CPU_WINDOW[1]}) of the 3840x2160 frame per step; rays = World::intersect "
-              "queries of the reference algorithm (R_ref, with its per-light duplication of secondary rays)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample,
-                         "ms_per_sample_pixel": secs / args.steps * 1e3 / px, "frame_ms_scaled_by_pixels": secs / args.steps * 1e3 / px * WIDTH * HEIGHT},
+        "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text()},
+        "cpu_baseline": cpu_baseline_entry(rays, secs, args.steps),
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -198,9 +228,10 @@ def run_cuda_inner(args):
         return float(t.item())
 
     MAX, SUM = (dist.ReduceOp.MAX, dist.ReduceOp.SUM) if world > 1 else (None, None)
+    W, H, SPP, FUEL = CFG["w"], CFG["h"], CFG["spp"], CFG["fuel"]
     warmup = max(args.warmup, 3)
-    opts = sharding.band_opts(WIDTH, rank, world, fuel=FUEL)
-    sess = R.Session(SCENE, WIDTH, HEIGHT, device=local)
+    opts = sharding.band_opts(W, rank, world, fuel=FUEL, spp=SPP)
+    sess = R.Session(CFG["scene"], W, H, device=local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     # ---- device-resident arm: `value` ----
@@ -230,7 +261,7 @@ def run_cuda_inner(args):
     value = rays_all / args.steps / ms_per_step / 1e3  # Mrays/s
 
     # ---- one profiled frame (launches serialised, CUDA events around each): time per kernel class + work tallies ----
-    popts = sharding.band_opts(WIDTH, rank, world, fuel=FUEL, flags=R.FLAG_PROFILE)
+    popts = sharding.band_opts(W, rank, world, fuel=FUEL, spp=SPP, flags=R.FLAG_PROFILE)
     sess.render_device(popts)
     _, _, prof = sess.render_device(popts)
 
@@ -241,17 +272,17 @@ def run_cuda_inner(args):
     frame = None
     pinned_ptr = None
     if world == 1:
-        pinned, pinned_ptr = R.pinned_array((HEIGHT, WIDTH, 3))
+        pinned, pinned_ptr = R.pinned_array((H, W, 3))
         out_ptr = pinned.ctypes.data
         host_image = pinned
     else:
         names = [None]
         if rank == 0:
-            frame = sharding.SharedFrame(HEIGHT, WIDTH, create=True)
+            frame = sharding.SharedFrame(H, W, create=True)
             names[0] = frame.name
         dist.broadcast_object_list(names, src=0)
         if rank != 0:
-            frame = sharding.SharedFrame(HEIGHT, WIDTH, name=names[0], create=False)
+            frame = sharding.SharedFrame(H, W, name=names[0], create=False)
         frame.pin()
         out_ptr = frame.ptr
         host_image = frame.array
@@ -291,7 +322,7 @@ def run_cuda_inner(args):
     e2e_rays_all = reduce(float(e2e_rays), SUM)
     e2e_value = e2e_rays_all / e2e_ms_max / 1e3
     h2d = reduce(float(sess.build_stats["device_bytes"]), SUM)
-    d2h = WIDTH * HEIGHT * 3 * 8
+    d2h = W * H * 3 * 8
 
     line = None
     if rank == 0:
@@ -300,26 +331,26 @@ def run_cuda_inner(args):
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
-                       "l2": "256 MiB device memset between timed frames (L2 flush); per-level ray queues (134 MB per 2 Mi-ray batch) exceed L2 anyway",
+            "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text(),
+                       "sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
+                       "l2": "256 MiB device memset between timed frames (L2 flush); the per-level ray queues of a batch exceed L2 anyway",
                        "scene": "device-resident arm: scene handle created once (host binned-SAH BVH), frames rendered from it; end-to-end arm: scene created and destroyed every step"},
             "frame_ms": ms_per_step, "wall_ms_per_step": wall_ms / args.steps,
-            "rays_per_frame": rays_all / args.steps, "ref_equivalent_rays_per_frame": rays_ref_all / args.steps,
+            "rays_per_frame": rays_all / args.steps, "value_rays": "R_uniq: rays actually traced (secondary sub-trees deduplicated across lights)",
+            "ref_equivalent_rays_per_frame": rays_ref_all / args.steps,
             "ref_equivalent_mrays_per_s": rays_ref_all / args.steps / ms_per_step / 1e3,
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": d2h, "frame_ms": e2e_ms_max / args.steps,
+                    "ref_equivalent_mrays_per_s": e2e_value * rays_ref_all / max(rays_all, 1.0),
                     "path": "rtc_scene_create (build_flags = RTC_BUILD_FAST as Image::par_render passes: flattening on the host, BVH built on the device) + rtc_render (page-locked host f64 rgb, copies overlapped with tracing) + rtc_scene_destroy per step"
                             + ("" if world == 1 else "; every rank writes its bands into one shared host image, shared-memory barrier per frame")},
             "gpu_launches": int(launches_all),
         }
-        line.update(rooflines(R, prof, world))
+        line.update(rooflines(R, prof, world, args.config))
         if world == 1 and not args.no_cpu:
             _build.build_oracle()
             r, s = cpu_reference_step()
-            px = CPU_WINDOW[2] * CPU_WINDOW[3]
-            line["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
-                                    "sample": f"one {CPU_WINDOW[2]}x{CPU_WINDOW[3]} window at ({CPU_WINDOW[0]},{CPU_WINDOW[1]}) of the same frame, reference algorithm (R_ref rays), {s:.1f} s",
-                                    "frame_ms_scaled_by_pixels": s * 1e3 / px * WIDTH * HEIGHT}
+            line["cpu_baseline"] = cpu_baseline_entry(r, s)
         else:
             line["cpu_baseline"] = None
     if frame is not None:
@@ -333,73 +364,109 @@ def run_cuda_inner(args):
     return line
 
 
-def rooflines(R, prof, world):
+def kernel_source_hash():
+    """Hash of the device code the traffic capture was taken on (profiles/roofline_traffic.json records it): a capture of
+    other kernels than the ones being timed is stale and is not reported."""
+    import hashlib
+
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "raytracer_challenge_b200", "csrc")
+    for name in sorted(os.listdir(csrc)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            with open(os.path.join(csrc, name), "rb") as f:
+                h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()[:16]
+
+
+def rooflines(R, prof, world, config_id):
     """Roofline figures of the dominant kernel class, from one profiled frame of rank 0 (its shard of the frame):
     algorithmic flops / bytes (cost model above x the work units the kernels counted) over the CUDA-event time of
-    that class, against measured peaks (MEASURED_PEAKS.json for HBM; rtc_microbench for the CUDA-core issue rates,
-    which that file does not carry)."""
+    that class, against measured peaks (MEASURED_PEAKS.json for HBM; rtc_microbench for the CUDA-core issue rates
+    and the L2 read bandwidth, which that file does not carry).  `roofline` is the bound with the largest fraction."""
     peak_hbm, peak_kind = read_peaks()
-    L = 2.0
+    L = float(CFG["lights"])
     hits = float(prof.surface_hits)
     secondary = float(prof.rays_reflected + prof.rays_refracted)
-    levels = FUEL + 1
-    batches = max(int(prof.kernel_launches) // (2 * levels + 2), 1)  # per batch: trace x levels, shadow, shade x levels, resolve
-    classes = {
-        # trace_spawn: reads the level's ray records, writes the hit records and the children (the next level's rays)
-        "trace_spawn": {"ms": prof.ms_trace, "bytes": RAY_RECORD * secondary + HIT_RECORD * hits + RAY_RECORD * secondary, "launches": batches * levels},
-        # trace_shadow: per (hit, light) reads the hit's over_point, writes one byte
-        "trace_shadow": {"ms": prof.ms_shadow, "bytes": L * hits * (SHADOW_READ + 1.0), "launches": batches},
-        # shade: reads the hit record + one shadow byte per light, read-modify-writes the sample accumulator
-        "shade": {"ms": prof.ms_shade, "bytes": hits * (HIT_RECORD + L) + 2.0 * ACCUM * hits, "launches": batches * levels},
-    }
-    # traversal flops split between the two traversal kernels in proportion to their rays (primary+secondary vs shadow)
+    levels = CFG["fuel"] + 1
+    batches = max(int(prof.kernel_launches) // (2 * levels + 3), 1)  # per batch: trace_spawn x levels, shadow_setup, walk_shadow, light x levels, resolve
+    # traversal work split between the two traversal kernels in proportion to their rays (primary+secondary vs shadow)
     n_closest = float(prof.rays_primary) + secondary
     n_shadow = float(prof.rays_shadow)
     share = n_closest / max(n_closest + n_shadow, 1.0)
-    f32_trav = F32_PER_NODE * prof.bvh_node_visits
-    f64_trav = F64_PER_TRIANGLE * prof.triangle_tests + F64_PER_PLANE * prof.primitive_tests + F64_PER_XFORM * prof.ray_transforms
-    # trace_spawn also holds prepare_state + normal + the child rays; the shadow kernel the shadow-ray setup; shade the Phong terms
-    classes["trace_spawn"].update(f64=f64_trav * share + F64_PER_HIT * hits, f32=f32_trav * share)
-    classes["trace_shadow"].update(f64=f64_trav * (1.0 - share) + 18.0 * L * hits, f32=f32_trav * (1.0 - share))
-    classes["shade"].update(f64=95.0 * L * hits, f32=0.0)
+    nodes, tris, prims, xforms = float(prof.bvh_node_visits), float(prof.triangle_tests), float(prof.primitive_tests), float(prof.ray_transforms)
+    f32_trav = F32_PER_NODE * nodes
+    f64_trav = F64_PER_TRIANGLE * tris + CFG["f64_per_prim"] * prims + F64_PER_XFORM * xforms
+    l2_trav = NODE_BYTES * nodes + TRI_TEST_BYTES * tris
+    classes = {
+        # trace_spawn: reads the level's ray records, writes the hit records and the children (the next level's rays);
+        # also holds prepare_state + normal + the child rays
+        "trace_spawn": {"ms": prof.ms_trace, "launches": batches * levels,
+                        "hbm": RAY_RECORD * secondary + HIT_RECORD * hits + RAY_RECORD * secondary,
+                        "f64": f64_trav * share + F64_PER_HIT * hits, "f32": f32_trav * share},
+        # trace_shadow: per (hit, light) reads the hit's over_point, writes one byte; holds the shadow-ray setup
+        "trace_shadow": {"ms": prof.ms_shadow, "launches": batches,
+                         "hbm": L * hits * (SHADOW_READ + 1.0), "f64": f64_trav * (1.0 - share) + 18.0 * L * hits, "f32": f32_trav * (1.0 - share)},
+        # shade: reads the hit record + one shadow byte per light, read-modify-writes the sample accumulator; the Phong terms
+        "shade": {"ms": prof.ms_shade, "launches": batches * levels,
+                  "hbm": hits * (HIT_RECORD + L) + 2.0 * ACCUM * hits, "f64": (95.0 + CFG["f64_per_pattern"]) * L * hits, "f32": 0.0},
+    }
+    # bytes the class moves through L1/L2 (SURVEY.md §8(d) BYTES(L1/L2)): its HBM records + the scene data it fetches
+    classes["trace_spawn"]["l2"] = classes["trace_spawn"]["hbm"] + l2_trav * share + HIT_FETCH_BYTES * hits
+    classes["trace_shadow"]["l2"] = classes["trace_shadow"]["hbm"] + l2_trav * (1.0 - share)
+    classes["shade"]["l2"] = classes["shade"]["hbm"] + (32.0 + 96.0) * hits  # primitive + material record per hit
+    classes = {k: v for k, v in classes.items() if v["ms"] > 0.0}
     dominant = max(classes, key=lambda k: classes[k]["ms"])
     d = classes[dominant]
     sec = max(d["ms"], 1e-9) * 1e-3
-    traffic = None
+    n_launch = max(int(d["launches"]), 1)
+    traffic, traffic_source, traffic_note = None, None, None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    traffic_source = None
     if os.path.exists(tpath):  # per-launch DRAM bytes of the same kernel from the committed `ncu --set full` capture
         with open(tpath) as f:
             t = json.load(f)
-        traffic = t.get("per_launch_dram_bytes", {}).get(dominant)
-        traffic_source = t.get("source")
-    out = {}
+        entry = t.get(config_id)
+        if entry is None:
+            traffic_note = f"no ncu capture for config {config_id} in profiles/roofline_traffic.json"
+        elif entry.get("kernel_source_hash") != kernel_source_hash():
+            traffic_note = "profiles/roofline_traffic.json was captured on other kernel sources than the ones timed here (stale): not reported"
+        else:
+            traffic = entry.get("per_launch_dram_bytes", {}).get(dominant)
+            traffic_source = entry.get("source")
     try:
         mb = R.microbench()
     except Exception as e:  # noqa: BLE001
         mb = {"error": str(e)}
-    gbs = d["bytes"] / sec / 1e9
-    n_launch = int(d["launches"])
-    out["roofline"] = {
-        "bound": "hbm", "kernel": dominant, "achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
-        "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_source,
-        "launches_per_frame": n_launch, "achieved_bytes_per_launch": d["bytes"] / max(n_launch, 1), "ms_per_launch": d["ms"] / max(n_launch, 1), "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
-        "ms_per_frame_in_this_kernel": d["ms"], "algorithmic_bytes_per_frame": d["bytes"],
-        "note": "HBM sees only ray queues, hit lists and the frame buffer (the 2.1 MB scene is L1/L2-resident): this path is bound by "
-                "CUDA-core issue under divergence and by L1/L2 latency on BVH fetches, not by HBM — see roofline_fp64 / roofline_fp32, "
-                "profiles/README.md (ncu: issue-slot utilisation, active threads per instruction, stall reasons) and DESIGN.md",
+    bounds = {"hbm": {"achieved": d["hbm"] / sec / 1e9, "peak": peak_hbm, "unit": "GB/s", "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                      "what": "algorithmic HBM bytes of the class: ray queue records read and written, hit records, shadow bytes, accumulators"}}
+    if "error" not in mb:
+        bounds["l2"] = {"achieved": d["l2"] / sec / 1e9, "peak": mb["l2_read_gbs"], "unit": "GB/s", "peak_source": "rtc_microbench L2-resident read (measured in this run)",
+                        "what": "SURVEY.md §8(d) BYTES(L1/L2): the HBM records plus BVH nodes, triangle records and per-hit scene fetches"}
+        bounds["fp64"] = {"achieved": d["f64"] / sec / 1e12, "peak": mb["fp64_mul_add_tflops"], "unit": "TFLOP/s", "peak_source": "rtc_microbench (measured in this run)",
+                          "what": "f64 CUDA-core issue, unfused mul / add (-fmad=false keeps f64 results bit-identical to the reference)"}
+        bounds["fp32"] = {"achieved": d["f32"] / sec / 1e12, "peak": mb["fp32_mul_add_tflops"], "unit": "TFLOP/s", "peak_source": "rtc_microbench (measured in this run)",
+                          "what": "fp32 CUDA-core issue, unfused mul / add (BVH slab tests)"}
+    for b in bounds.values():
+        b["frac"] = b["achieved"] / b["peak"]
+        b["kernel"] = dominant
+    top = max(bounds, key=lambda k: bounds[k]["frac"])
+    out = {}
+    out["roofline"] = dict(bounds[top])
+    out["roofline"].update({
+        "bound": top, "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_source,
+        "launches_per_frame": n_launch, "achieved_bytes_per_launch": d["hbm" if top == "hbm" else "l2"] / n_launch if top in ("hbm", "l2") else None,
+        "algorithmic_hbm_bytes_per_launch": d["hbm"] / n_launch, "ms_per_launch": d["ms"] / n_launch,
+        "ms_per_frame_in_this_kernel": d["ms"], "class_ms_source": "one serialised RTC_FLAG_PROFILE frame (one stream, CUDA events around every kernel class of every batch); "
+                                                                   "the timed frames overlap several batch pipelines, so the class times sum to more than ms_per_step",
+        "note": "the bound reported is the one with the largest fraction of {hbm, l2, fp64, fp32}; all four are listed under roofline_*.  The 2 MB scene is L1/L2-resident and the path "
+                "is latency- and divergence-bound (profiles/README.md: issue-slot utilisation, active threads per instruction, stall reasons), so every fraction is far from 1",
         "scope": "rank 0's shard of the frame" if world > 1 else "whole frame",
         "per_class_ms": {k: v["ms"] for k, v in classes.items()},
-    }
+    })
+    if traffic_note:
+        out["roofline"]["traffic_note"] = traffic_note
+    for k, b in bounds.items():
+        out["roofline_" + k] = b
     if "error" not in mb:
-        t64 = d["f64"] / sec / 1e12
-        t32 = d["f32"] / sec / 1e12
-        out["roofline_fp64"] = {"bound": "fp64 CUDA-core issue, unfused mul/add (-fmad=false keeps f64 results bit-identical to the reference)",
-                                "kernel": dominant, "achieved": t64, "peak": mb["fp64_mul_add_tflops"], "unit": "TFLOP/s",
-                                "frac": t64 / mb["fp64_mul_add_tflops"], "peak_source": "rtc_microbench (measured in this run)"}
-        out["roofline_fp32"] = {"bound": "fp32 CUDA-core issue, unfused mul/add (BVH slab tests)", "kernel": dominant, "achieved": t32,
-                                "peak": mb["fp32_mul_add_tflops"], "unit": "TFLOP/s", "frac": t32 / mb["fp32_mul_add_tflops"],
-                                "peak_source": "rtc_microbench (measured in this run)"}
         out["measured_peaks"] = mb
     out["work_per_frame"] = {"surface_hits": prof.surface_hits, "bvh_node_visits": prof.bvh_node_visits, "triangle_tests": prof.triangle_tests,
                              "primitive_tests": prof.primitive_tests, "ray_transforms": prof.ray_transforms, "rays": prof.rays}
@@ -407,13 +474,18 @@ def rooflines(R, prof, world):
 
 
 def main():
+    global CFG
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=0, help="timed frames (default: 10; 3 for c5, whose frame takes over a second)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    CFG = CONFIGS[args.config]
+    if args.steps <= 0:
+        args.steps = 3 if args.config == "c5" else 10
     if args.impl == "reference":
         return run_reference(args)
     return run_cuda(args)

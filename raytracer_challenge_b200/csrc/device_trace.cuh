@@ -101,6 +101,11 @@ struct Query {
         cache.xform = -1;
     }
     static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
+    // a persistent kernel hands the query object its next ray (`ray` refers to the caller's variable, already reassigned)
+    __device__ __forceinline__ void restart() {
+        passed = gates_passed<FEAT>(sc, ray);
+        cache.xform = -1;
+    }
     __device__ __forceinline__ Tally& counters() { return kTally ? tally : scratch; }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
         if (!(FEAT & FEAT_GATES)) return true;
@@ -268,53 +273,104 @@ __device__ __forceinline__ float walk_thi(double tmax, double te) { return __dou
 
 // Visitor protocol:  bool V::leaf(int slot) -> true stops the walk;  double V::tmax() -> current upper bound on t
 // (re-read only after a leaf was visited: it cannot change in between).
+//
+// The walk is resumable: a cursor holds everything between two steps, so that a kernel can either run a query to its
+// end (walk_bvh, below) or interleave the queries of a warp's lanes and hand a lane whose query has ended the next
+// ray of a queue (the persistent walk kernels of render_kernels.cu).
+constexpr int WALK_DONE = (int)0x80000000;  // never a leaf link: ~enc with enc >= 0 is > INT_MIN
+struct WalkCursor {
+    Walk w;
+    float thi;       // upper end of the admissible interval, relative to the re-origin
+    int link;        // >= 0: inner node; WALK_DONE: the query is over; any other negative value: a leaf link
+    int sp;
+    int brute_next;  // >= 0: brute-force scan (RTC_FLAG_BRUTE_FORCE, cone guards), the next item to test; -1: BVH walk
+    int stack[BVH_STACK];
+};
+
+// Starts a query.  Returns false (link = WALK_DONE) when the ray cannot touch any BVH item.
+__device__ __forceinline__ bool walk_begin(const Scene& sc, const Ray& ray, int mode, bool brute, double tmax, WalkCursor& c) {
+    c.sp = 0;
+    c.brute_next = -1;
+    c.link = WALK_DONE;
+    if (sc.n_bvh_items == 0) return false;
+    if (brute) {
+        c.link = ~0;  // the leaf holding item 0 alone
+        c.brute_next = 1;
+        return true;
+    }
+    if (!walk_setup(sc, ray, mode, c.w)) return false;
+    c.link = sc.bvh_root;
+    c.thi = walk_thi(tmax, c.w.te);
+    return true;
+}
+
+// Node phase: descends through inner nodes until this lane stands on a leaf (or its query is over).
+// "while-while" (Aila & Laine): every lane first descends until it stands on a leaf, THEN the warp runs the leaf code
+// once for all of them.  With a single if/else loop almost every iteration has some lane on a leaf, so every
+// iteration pays for the (4-5x more expensive, f64) leaf code.
+// top / n_top: the first n_top nodes staged in shared memory by the caller (persistent kernels), or (nullptr, 0).
+template <bool TALLY>
+__device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, Tally& tally, const BvhNode* __restrict__ top, int n_top) {
+    int link = c.link, sp = c.sp;
+    const float thi = c.thi;
+    while (link >= 0) {
+        if (TALLY) tally.nodes++;
+        float4 q0, q1, q2, q3;
+        if (link < n_top) {
+            const float4* q = reinterpret_cast<const float4*>(top + link);
+            q0 = q[0]; q1 = q[1]; q2 = q[2]; q3 = q[3];
+        } else {
+            const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
+            q0 = __ldg(q); q1 = __ldg(q + 1); q2 = __ldg(q + 2); q3 = __ldg(q + 3);
+        }
+        float n0, n1;
+        const bool h0 = slab(c.w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
+        const bool h1 = slab(c.w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
+        const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
+        if (h0 && h1) {
+            const bool first0 = n0 <= n1;
+            c.stack[sp++] = first0 ? c1 : c0;
+            link = first0 ? c0 : c1;
+        } else if (h0) {
+            link = c0;
+        } else if (h1) {
+            link = c1;
+        } else {
+            link = sp ? c.stack[--sp] : WALK_DONE;
+        }
+    }
+    c.link = link;
+    c.sp = sp;
+}
+
+// Leaf phase: tests the items of the leaf this lane stands on, then moves to the next pending subtree.
+// Returns true when the query is over (the visitor stopped it, or nothing is left to visit).
+template <class V>
+__device__ __forceinline__ bool walk_leaf(const Scene& sc, WalkCursor& c, V& v) {
+    const int enc = ~c.link;
+    const int first = enc >> 2, count = (enc & 3) + 1;
+    for (int i = 0; i < count; ++i)
+        if (v.leaf(first + i)) { c.link = WALK_DONE; return true; }
+    if (c.brute_next >= 0) {
+        if (c.brute_next >= sc.n_bvh_items) { c.link = WALK_DONE; return true; }
+        c.link = ~(c.brute_next << 2);
+        c.brute_next++;
+        return false;
+    }
+    c.thi = walk_thi(v.tmax(), c.w.te);
+    if (c.sp == 0) { c.link = WALK_DONE; return true; }
+    c.link = c.stack[--c.sp];
+    return false;
+}
+
 template <class V>
 __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v, Tally& tally) {
-    if (sc.n_bvh_items == 0) return;
-    if (brute) {
-        for (int i = 0; i < sc.n_bvh_items; ++i)
-            if (v.leaf(i)) return;
-        return;
-    }
-    Walk w;
-    if (!walk_setup(sc, ray, mode, w)) return;
-    int stack[BVH_STACK];
-    int sp = 0;
-    int link = sc.bvh_root;
-    float thi = walk_thi(v.tmax(), w.te);
-    // "while-while" (Aila & Laine): every lane first descends through inner nodes until it stands on a leaf, THEN the
-    // warp runs the leaf code once for all of them.  With a single if/else loop almost every iteration has some lane
-    // on a leaf, so every iteration pays for the (4-5x more expensive, f64) leaf code.
-    constexpr int WALK_DONE = (int)0x80000000;  // never a leaf link: ~enc with enc >= 0 is > INT_MIN
+    WalkCursor c;
+    if (!walk_begin(sc, ray, mode, brute, v.tmax(), c)) return;
     for (;;) {
-        while (link >= 0) {
-            if (V::kTally) tally.nodes++;
-            const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
-            const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-            float n0, n1;
-            const bool h0 = slab(w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
-            const bool h1 = slab(w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
-            const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
-            if (h0 && h1) {
-                const bool first0 = n0 <= n1;
-                stack[sp++] = first0 ? c1 : c0;
-                link = first0 ? c0 : c1;
-            } else if (h0) {
-                link = c0;
-            } else if (h1) {
-                link = c1;
-            } else {
-                link = sp ? stack[--sp] : WALK_DONE;
-            }
-        }
-        if (link == WALK_DONE) return;
-        const int enc = ~link;
-        const int first = enc >> 2, count = (enc & 3) + 1;
-        for (int i = 0; i < count; ++i)
-            if (v.leaf(first + i)) return;
-        thi = walk_thi(v.tmax(), w.te);
-        if (sp == 0) return;
-        link = stack[--sp];
+        walk_descend<V::kTally>(sc, c, tally, nullptr, 0);
+        if (c.link == WALK_DONE) return;
+        if (walk_leaf(sc, c, v)) return;
     }
 }
 
@@ -342,6 +398,12 @@ struct ClosestVisitor {
         best.t = 0.0; best.prim = -1; best.u = 0.0; best.v = 0.0;
     }
     __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : limit; }
+    // next ray of a persistent kernel: its limit and the nearest crossing already known (prim0 < 0: none)
+    __device__ __forceinline__ void restart(double lim, double t0, int prim0) {
+        q.restart();
+        limit = lim;
+        best.t = t0; best.prim = prim0; best.u = 0.0; best.v = 0.0;
+    }
     __device__ __forceinline__ void offer(double t, int prim, double u, double v) {
         if (t >= 0.0 && t < limit && (best.prim < 0 || t < best.t || (t == best.t && prim < best.prim))) {
             best.t = t; best.prim = prim; best.u = u; best.v = v;
@@ -411,6 +473,11 @@ struct AnyVisitor {
     bool found;
     __device__ __forceinline__ AnyVisitor(const Scene& sc, const Ray& ray, double d, Tally& tl, int* ovf) : q(sc, ray, tl, ovf, !(FEAT & FEAT_CSG)), dist(d), found(false) {}
     __device__ __forceinline__ double tmax() const { return dist; }
+    __device__ __forceinline__ void restart(double d) {  // next ray of a persistent kernel
+        q.restart();
+        dist = d;
+        found = false;
+    }
     __device__ __forceinline__ bool test(const Roots& r) {
         for (int k = 0; k < r.n; ++k)
             if (r.t[k] >= 0.0 && r.t[k] < dist) { found = true; return true; }
@@ -455,6 +522,25 @@ __device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double 
     walk_bvh(sc, ray, 0, brute, v, tally);
     return v.found;
 }
+
+// The query a shadow ray runs (World::is_shadowed, src/world.rs:26-48): any crossing in [0, distance) when every shape
+// casts shadows; otherwise the nearest crossing below `distance`, which shadows iff its shape casts shadows.
+template <int FEAT, bool ANYHIT>
+struct ShadowVisitor;
+template <int FEAT>
+struct ShadowVisitor<FEAT, true> {
+    using type = AnyVisitor<FEAT>;
+    __device__ __forceinline__ static void restart(type& v, double dist, double, int) { v.restart(dist); }
+    __device__ __forceinline__ static bool shadowed(const Scene&, const type& v) { return v.found; }
+};
+template <int FEAT>
+struct ShadowVisitor<FEAT, false> {
+    using type = ClosestVisitor<FEAT>;
+    __device__ __forceinline__ static void restart(type& v, double dist, double t0, int prim0) { v.restart(dist, t0, prim0); }
+    __device__ __forceinline__ static bool shadowed(const Scene& sc, const type& v) {
+        return v.best.prim >= 0 && (__ldg(&sc.prims[v.best.prim].kind_flags) & 0x100) != 0;
+    }
+};
 
 // ---- n1 / n2: replay of the container walk of Intersection::prepare_state (src/intersection.rs:70-103) ----
 template <int FEAT>

@@ -1,25 +1,32 @@
 // Wavefront kernels of the render path.  The recursion of World::color_at -> shade_hit -> reflected_color /
 // refracted_color (src/world.rs:50-149) becomes, per batch of samples:
 //
-//   trace_spawn  x (fuel + 1), a chain: one thread per ray of the level (level 0: Camera::ray_at_pixel,
-//                  src/camera.rs:39-55, generated in-kernel; level k > 0: the queue level k-1 wrote) -> closest hit
-//                  (World::intersect + sort + hit, src/world.rs:18-24, src/intersection.rs:123-132), n1/n2 for
-//                  transparent hits (src/intersection.rs:70-103), the surface frame of prepare_state
-//                  (src/intersection.rs:50-68) -> hit record appended to the level's segment of the hit list, and the
-//                  reflected / refracted children (scalar throughput, remaining fuel; src/world.rs:66-132) pushed to
-//                  the next level's queue
-//   trace_shadow x 1: one thread per (hit, light) over the hits of ALL levels, light-major: World::is_shadowed
-//                  (src/world.rs:26-48) -> one byte per (hit, light)
-//   shade        x (fuel + 1), in level order: pattern colour, Phong term per light (src/shape.rs:429-463),
-//                  throughput * surface colour added to the sample
+//   trace_spawn  x (fuel + 1), a chain down the bounce levels: one thread per ray of the level (level 0:
+//                  Camera::ray_at_pixel, src/camera.rs:39-55, generated in-kernel; level k > 0: the queue level k-1
+//                  wrote) -> closest hit (World::intersect + sort + hit, src/world.rs:18-24,
+//                  src/intersection.rs:123-132), n1/n2 for transparent hits (src/intersection.rs:70-103), the surface
+//                  frame of prepare_state (src/intersection.rs:50-68) -> hit record appended to the level's segment of
+//                  the hit list, and the reflected / refracted children (src/world.rs:84-132) pushed to the next
+//                  level's queue.  A ray that misses stores black where its parent will look for its colour.
+//   shadow_setup x 1, uniform: one thread per (hit, light) over the hits of ALL levels, light-major: the shadow ray of
+//                  World::is_shadowed (src/world.rs:26-48), the always-tested primitives and the root box of the BVH.
+//                  Most shadow rays are decided here (one byte per (hit, light)); the others are appended to the
+//                  shadow walker queue.
+//   walk_shadow  x 1, persistent: warps walk the BVH for the queued shadow rays; a lane whose ray is decided takes
+//                  the next ray of the queue at once, so the node loop and the f64 leaf tests run on full warps
+//                  (before: 10 of 32 lanes, profiles/README.md r02a).
+//   light        x (fuel + 1), a chain UP the levels (deepest first): World::shade_hit for every hit of the level —
+//                  pattern colour, Shape::lighting per light (src/shape.rs:429-463), plus the colours its children
+//                  stored, combined in the reference's own order (src/world.rs:58-79) — stored where the parent
+//                  will look for it (level 0: the sample).  No atomics, no weights: every colour has one writer, so
+//                  frames are bit-reproducible, and the sum has the reference's association.
 //
 // Each kernel holds one BVH traversal (or none), so its instruction footprint stays small (profiles/README.md, r01a);
-// the level-to-level dependency is the trace chain only, the shadow rays of a batch are one fat launch instead of one
-// thin launch per level, and neither the shadow nor the shading kernel gathers from the ray queue or recomputes the
-// surface frame: everything they need is in the hit record (96 B, coalesced).
+// neither the shadow nor the lighting kernels gather from the ray queue or recompute the surface frame: everything
+// they need is in the hit record (96 B, coalesced).
 //
-// The reference evaluates the secondary rays once per light inside the light loop (src/world.rs:58-79), i.e. a
-// child's colour is added L times; here each child is traced once with its weight multiplied by L.
+// The reference evaluates the secondary rays once per light inside the light loop (src/world.rs:58-79); here each
+// child is traced once and its colour is added once per light.
 // Built with -fmad=false: see device_math.cuh.
 #include "device_pattern.cuh"
 #include "device_trace.cuh"
@@ -80,28 +87,29 @@ __device__ __forceinline__ Ray camera_ray(const FrameParams& f, int px, int py, 
 }
 
 // Ray `idx` of the level's input.  Returns false for the padding slots of a partial tile (primary level only).
+// parent: the record (level 0: the sample) that waits for this ray's colour; kind: HIT_KIND_REFRACTED or 0.
 template <bool PRIMARY>
-__device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams& lv, uint32_t idx, Ray& ray, double& w, uint32_t& sample, int& fuel) {
+__device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams& lv, uint32_t idx, Ray& ray, uint32_t& parent, uint32_t& kind, int& fuel) {
     if (PRIMARY) {
         const uint32_t s = (uint32_t)lv.first_sample + idx;
         uint32_t pix = s, sub = 0;
         if (f.spp > 1) { pix = s / (uint32_t)f.spp; sub = s - pix * (uint32_t)f.spp; }
         int px, py;
         tile_pixel(f, pix, px, py);
+        parent = idx;
+        kind = 0;
+        fuel = f.fuel;
         if (px >= f.win_w || py >= f.win_h) return false;
         ray = camera_ray(f, px, py, (int)sub);
-        w = 1.0;
-        sample = idx;
-        fuel = f.fuel;
         return true;
     }
     const double2 a = lv.in_q0[idx], b = lv.in_q1[idx], c = lv.in_q2[idx], e = lv.in_q3[idx];
     ray.o = mk(a.x, a.y, b.x);
     ray.d = mk(b.y, c.x, c.y);
-    w = e.x;
-    const uint64_t bits = (uint64_t)__double_as_longlong(e.y);
-    sample = (uint32_t)(bits & 0xffffffffu);
-    fuel = (int)(bits >> 32);
+    const uint64_t bits = (uint64_t)__double_as_longlong(e.x);
+    parent = (uint32_t)(bits & 0xffffffffu);
+    fuel = (int)((bits >> 32) & 0xffu);
+    kind = (uint32_t)((bits >> 40) & 1u);
     return true;
 }
 
@@ -149,11 +157,23 @@ __device__ __forceinline__ uint32_t hit_prefix(const HitList& hl, uint32_t* firs
     return total;
 }
 
+// Where the colour of the `kind` child of record `rec` is stored (HitList::child_rgb).
+__device__ __forceinline__ double* child_slot(const HitList& hl, uint32_t rec, uint32_t kind) {
+    return hl.child_rgb + 3 * (hl.fan == 2 ? 2 * (size_t)rec + kind : (size_t)rec);
+}
+// A ray's colour goes to its parent's child slot, or — primary rays — to the sample.
+__device__ __forceinline__ void store_ray_color(const HitList& hl, const LevelParams& lv, int level, uint32_t parent, uint32_t kind, double r, double g, double b) {
+    double* dst = level == 0 ? lv.accum + 3 * (size_t)parent : child_slot(hl, parent, kind);
+    dst[0] = r;
+    dst[1] = g;
+    dst[2] = b;
+}
+
 // ---- kernel 1: closest hit + surface frame + children --------------------------------------------------------
 // One thread per ray of the level.  For a hit it computes the geometric half of prepare_state once, appends the hit
 // record to this level's segment of the hit list and pushes the reflected / refracted children to the next level's
-// queue (src/world.rs:66-78,84-132) — so the next level depends on this kernel only, and the shadow / shading work
-// of all levels is done afterwards in two fat launches.
+// queue (src/world.rs:66-78,84-132) — so the next level depends on this kernel only, and the shadow / lighting work
+// of all levels is done afterwards.
 template <int FEAT, bool PRIMARY>
 __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_BLOCKS_CSG : (FEAT & FEAT_TRANSPARENT) ? RTC_TRACE_MIN_BLOCKS_TRANSPARENT : RTC_TRACE_MIN_BLOCKS) trace_spawn(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
@@ -173,15 +193,14 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
         Ray ray;
-        double w = 0.0;
-        uint32_t sample = 0;
+        uint32_t parent = 0, kind = 0;
         int fuel = 0;
-        const bool active = idx < n_in && load_ray<PRIMARY>(f, lv, idx, ray, w, sample, fuel);
+        const bool active = idx < n_in && load_ray<PRIMARY>(f, lv, idx, ray, parent, kind, fuel);
         Hit hit;
         hit.prim = -1;
         bool push_refl = false, push_refr = false;
         Ray r_refl, r_refr;
-        double w_refl = 0.0, w_refr = 0.0;
+        double reflectance = 0.0;
         Surface s;
         if (active) {
             if (PRIMARY) c_active++;
@@ -192,18 +211,17 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                 const Prim prim = load_prim(sc, hit.prim);
                 const Material& mat = sc.materials[prim.material];
                 const double reflective = mat.reflective, transparency = mat.transparency;
-                double n1 = 1.0, n2 = 1.0, reflectance = 0.0;
+                double n1 = 1.0, n2 = 1.0;
                 if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0)
                     refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, tally, lv.overflow);
                 s = surface_at(sc, prim, ray, hit.t, hit.u, hit.v);
                 if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) reflectance = schlick(s.eye, s.normal, n1, n2);
+                // With no light World::shade_hit adds nothing at all (src/world.rs:58): the children would be traced for nothing.
                 if (fuel > 0 && L > 0) {
-                    const bool both = reflective > 0.0 && transparency > 0.0;
                     if (reflective != 0.0) {
                         push_refl = true;
                         r_refl.o = s.over_point;
                         r_refl.d = reflect(ray.d, s.normal);
-                        w_refl = w * (double)L * reflective * (both ? reflectance : 1.0);
                     }
                     if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) {
                         const double n_ratio = n1 / n2;
@@ -214,10 +232,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                             push_refr = true;
                             r_refr.o = s.point - (s.normal * RTC_EPSILON);
                             r_refr.d = s.normal * (n_ratio * cos_i - cos_t) - s.eye * n_ratio;
-                            w_refr = w * (double)L * transparency * (both ? (1.0 - reflectance) : 1.0);
                         }
                     }
                 }
+            } else {
+                store_ray_color(hl, lv, lv.level, parent, kind, 0.0, 0.0, 0.0);  // World::color_at: a miss is black (src/world.rs:146-148)
             }
         }
         const unsigned below = (1u << lane) - 1u;
@@ -237,29 +256,39 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
         hit_base = __shfl_sync(0xffffffffu, hit_base, 0);
         base = __shfl_sync(0xffffffffu, base, 0);
         // ---- hit record ----
+        uint32_t record = 0;
         if (is_hit) {
             const uint64_t slot = hit_base + (uint64_t)__popc(m & below);
             if (slot < seg_cap) {
                 const size_t at = (size_t)seg + slot;
+                record = (uint32_t)at;
+                const uint32_t bits = kind | (push_refl ? HIT_SPAWNED_REFLECTED : 0u) | (push_refr ? HIT_SPAWNED_REFRACTED : 0u);
                 hl.a[at] = make_double2(s.over_point.x, s.over_point.y);
                 hl.b[at] = make_double2(s.over_point.z, s.normal.x);
                 hl.c[at] = make_double2(s.normal.y, s.normal.z);
                 hl.d[at] = make_double2(s.eye.x, s.eye.y);
-                hl.e[at] = make_double2(s.eye.z, w);
-                hl.f[at] = make_double2(__longlong_as_double((long long)((uint64_t)sample << 32 | (uint32_t)hit.prim)), 0.0);
-            } else *lv.overflow = 2;
+                hl.e[at] = make_double2(s.eye.z, reflectance);
+                hl.f[at] = make_double2(__longlong_as_double((long long)((uint64_t)parent << 32 | (uint32_t)hit.prim)), __longlong_as_double((long long)bits));
+            } else {
+                *lv.overflow = 2;
+                push_refl = false;
+                push_refr = false;
+            }
         }
         // ---- children: warp-aggregated compaction into the next level's queue ----
         if (n_push) {
-            const uint64_t packed_fuel = (uint64_t)(uint32_t)(fuel - 1) << 32 | sample;
+            const uint64_t link = (uint64_t)(uint32_t)(fuel - 1) << 32 | record;
             if (push_refl) {
                 const uint64_t slot = base + (uint64_t)__popc(m_refl & below);
                 if (slot < lv.out_capacity) {
                     lv.out_q0[slot] = make_double2(r_refl.o.x, r_refl.o.y);
                     lv.out_q1[slot] = make_double2(r_refl.o.z, r_refl.d.x);
                     lv.out_q2[slot] = make_double2(r_refl.d.y, r_refl.d.z);
-                    lv.out_q3[slot] = make_double2(w_refl, __longlong_as_double((long long)packed_fuel));
-                } else *lv.overflow = 2;
+                    lv.out_q3[slot] = make_double2(__longlong_as_double((long long)link), 0.0);
+                } else {
+                    *lv.overflow = 2;
+                    store_ray_color(hl, lv, lv.level + 1, record, 0u, 0.0, 0.0, 0.0);
+                }
                 if (SPLIT) c_refl++;
             }
             if ((FEAT & FEAT_TRANSPARENT) && push_refr) {
@@ -268,8 +297,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                     lv.out_q0[slot] = make_double2(r_refr.o.x, r_refr.o.y);
                     lv.out_q1[slot] = make_double2(r_refr.o.z, r_refr.d.x);
                     lv.out_q2[slot] = make_double2(r_refr.d.y, r_refr.d.z);
-                    lv.out_q3[slot] = make_double2(w_refr, __longlong_as_double((long long)packed_fuel));
-                } else *lv.overflow = 2;
+                    lv.out_q3[slot] = make_double2(__longlong_as_double((long long)(link | (uint64_t)HIT_KIND_REFRACTED << 40)), 0.0);
+                } else {
+                    *lv.overflow = 2;
+                    store_ray_color(hl, lv, lv.level + 1, record, HIT_KIND_REFRACTED, 0.0, 0.0, 0.0);
+                }
                 if (SPLIT) c_refr++;
             }
         }
@@ -289,75 +321,206 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
     }
 }
 
-// ---- kernel 2: World::is_shadowed for every (hit, light) of the batch, all levels in one launch ----------------
-// Light-major: consecutive threads take consecutive hits towards the SAME light, so a warp's rays start next to each
-// other and head the same way.  Reads 24 B (over_point) per thread, coalesced; writes one byte.
+// ---- kernel 2: World::is_shadowed, uniform half -----------------------------------------------------------------
+// One thread per (hit, light) of the batch, all levels in one launch, light-major: consecutive threads take consecutive
+// hits towards the SAME light.  Builds the shadow ray (src/world.rs:33-40), tests the always-tested primitives and the
+// root box of the BVH: every lane runs the same straight-line code.  A ray that is decided stores its byte; a ray that has
+// to walk the BVH is appended to the shadow walker queue (one atomic per warp).
+// ANYHIT: every shape casts shadows, so "nearest crossing < distance" <=> "any crossing in [0, distance)".  Otherwise the
+// nearest crossing decides (src/world.rs:43-47) and the walk is a closest-hit query below `distance`.
 template <int FEAT, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) trace_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
-    const bool brute = (f.flags & 1u) != 0;
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) shadow_setup(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+    const bool brute_all = (f.flags & 1u) != 0;
     uint32_t first[MAX_LEVELS + 1];
     const uint32_t n_hits = hit_prefix(hl, first);
     const uint32_t L = (uint32_t)sc.n_lights;
     const uint32_t total = n_hits * L;  // < 2^32: checked by the host (hit capacity * lights)
     const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (total + 31u) & ~31u;
+    const unsigned lane = threadIdx.x & 31u;
     Tally tally = {0u, 0u, 0u, 0u};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        const uint32_t li = i / n_hits;
-        const uint32_t j = i - li * n_hits;  // packed hit index over all levels
-        int k = 0;
-        while (k + 1 < hl.n_levels && j >= first[k + 1]) ++k;
-        const size_t at = (size_t)hl.seg_off[k] + (j - first[k]);
-        const double2 a = hl.a[at];
-        const double oz = hl.b[at].x;
-        const V3 over_point = mk(a.x, a.y, oz);
-        const Light& light = sc.lights[li];
-        const V3 to_light = mk(light.origin[0], light.origin[1], light.origin[2]) - over_point;
-        const double distance = magnitude(to_light);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        bool walk = false, brute = false;
         Ray sray;
-        sray.o = over_point;
-        sray.d = normalize(to_light);
-        bool shadowed;
-        if (ANYHIT) {
-            shadowed = any_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
-        } else {  // some shape does not cast shadows: the nearest crossing decides (src/world.rs:43-47)
-            const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
-            shadowed = sh.prim >= 0 && (__ldg(&sc.prims[sh.prim].kind_flags) & 0x100) != 0;
+        double distance = 0.0, t0 = 0.0;
+        int prim0 = -1;
+        uint32_t flag_at = 0;
+        if (i < total) {
+            const uint32_t li = i / n_hits;
+            const uint32_t j = i - li * n_hits;  // packed hit index over all levels
+            int k = 0;
+            while (k + 1 < hl.n_levels && j >= first[k + 1]) ++k;
+            const size_t at = (size_t)hl.seg_off[k] + (j - first[k]);
+            flag_at = li * hl.total_cap + (uint32_t)at;
+            const double2 a = hl.a[at];
+            const double oz = hl.b[at].x;
+            const V3 over_point = mk(a.x, a.y, oz);
+            const Light& light = sc.lights[li];
+            const V3 to_light = mk(light.origin[0], light.origin[1], light.origin[2]) - over_point;
+            distance = magnitude(to_light);
+            sray.o = over_point;
+            sray.d = normalize(to_light);
+            brute = brute_all || near_cone_slope<FEAT>(sc, sray);
+            bool shadowed = false;
+            if (ANYHIT) {
+                AnyVisitor<FEAT> v(sc, sray, distance, tally, lv.overflow);
+                if (visit_unbounded(sc, v)) shadowed = v.found;
+                else if (sc.n_bvh_items > 0) {
+                    Walk w;
+                    walk = brute || walk_setup(sc, sray, 0, w);
+                }
+            } else {
+                ClosestVisitor<FEAT> v(sc, sray, distance, tally, lv.overflow);
+                visit_unbounded(sc, v);
+                t0 = v.best.t;
+                prim0 = v.best.prim;
+                if (sc.n_bvh_items > 0) {
+                    Walk w;
+                    walk = brute || walk_setup(sc, sray, 0, w);
+                }
+                if (!walk) shadowed = prim0 >= 0 && (__ldg(&sc.prims[prim0].kind_flags) & 0x100) != 0;
+            }
+            if (!walk) lv.shadow[flag_at] = shadowed ? 1 : 0;
         }
-        lv.shadow[i] = shadowed ? 1 : 0;
+        const unsigned m = __ballot_sync(0xffffffffu, walk);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(lv.sw_count, (unsigned long long)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (walk) {
+                const uint64_t slot = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
+                if (slot < lv.sw_capacity) {
+                    lv.sw0[slot] = make_double2(sray.o.x, sray.o.y);
+                    lv.sw1[slot] = make_double2(sray.o.z, sray.d.x);
+                    lv.sw2[slot] = make_double2(sray.d.y, sray.d.z);
+                    lv.sw3[slot] = make_double2(distance, __longlong_as_double((long long)((uint64_t)flag_at | (brute ? 1ull << 63 : 0ull))));
+                    if (!ANYHIT) lv.sw4[slot] = make_double2(t0, __longlong_as_double((long long)prim0));
+                } else *lv.overflow = 2;
+            }
+        }
     }
-    if (FEAT & FEAT_TALLY) flush_tally(tally, lv.stats, threadIdx.x & 31u);
+    if (FEAT & FEAT_TALLY) flush_tally(tally, lv.stats, lane);
 }
 
-// ---- kernel 3: shading of one level's hits -------------------------------------------------------------------
-// World::shade_hit light loop (src/world.rs:58-64) + Shape::lighting (src/shape.rs:429-463); one launch per level, in
-// level order on the batch's stream, so a sample's contributions are added in a fixed order.
+// ---- kernel 3: World::is_shadowed, the BVH walks ------------------------------------------------------------------
+// Persistent warps over the shadow walker queue.  Every lane owns one query at a time (a resumable WalkCursor); the warp
+// alternates a node phase (each lane descends to its next leaf) and a leaf phase (the exact f64 item tests), and before
+// each round the lanes whose query has ended take the next rays of the queue.  The queue is claimed in chunks (one
+// atomic per RTC_WALK_CHUNK rays and warp), so a refill is a few loads and the fp32 walk setup — the uniform, expensive
+// part of a shadow ray (normalisation, always-tested primitives) was done at full width by shadow_setup.
+#ifndef RTC_WALK_CHUNK
+#define RTC_WALK_CHUNK 128
+#endif
+#ifndef RTC_WALK_REFILL_MIN  // refill once this many lanes are idle (or all of them)
+#define RTC_WALK_REFILL_MIN 4
+#endif
+template <int FEAT, bool ANYHIT>
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_WALK_MIN_BLOCKS_CSG : RTC_WALK_MIN_BLOCKS) walk_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv) {
+    constexpr bool TALLY = (FEAT & FEAT_TALLY) != 0;
+    constexpr unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned long long pushed = *lv.sw_count;
+    const uint32_t n_total = (uint32_t)(pushed < lv.sw_capacity ? pushed : lv.sw_capacity);
+    uint32_t next = 0, end = 0;  // this warp's chunk of the queue (warp-uniform)
+    bool exhausted = n_total == 0;
+    bool busy = false;
+    Ray ray;
+    ray.o = mk(0.0, 0.0, 0.0);
+    ray.d = mk(0.0, 0.0, 1.0);
+    uint32_t flag_at = 0;
+    Tally tally = {0u, 0u, 0u, 0u};
+    WalkCursor c;
+    c.link = WALK_DONE;
+    typename ShadowVisitor<FEAT, ANYHIT>::type v(sc, ray, 0.0, tally, lv.overflow);
+    for (;;) {
+        const unsigned idle = __ballot_sync(FULL, !busy);
+        if (idle != 0u && !exhausted && (idle == FULL || __popc(idle) >= RTC_WALK_REFILL_MIN)) {
+            if (next == end) {
+                uint32_t base = 0;
+                if (lane == 0) base = (uint32_t)atomicAdd(lv.sw_head, (unsigned long long)RTC_WALK_CHUNK);
+                base = __shfl_sync(FULL, base, 0);
+                if (base >= n_total) exhausted = true;
+                else { next = base; end = min(base + (uint32_t)RTC_WALK_CHUNK, n_total); }
+            }
+            if (!exhausted) {
+                const uint32_t avail = end - next;
+                const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+                if (!busy && rank < avail) {
+                    const uint32_t i = next + rank;
+                    const double2 s0 = lv.sw0[i], s1 = lv.sw1[i], s2 = lv.sw2[i], s3 = lv.sw3[i];
+                    ray.o = mk(s0.x, s0.y, s1.x);
+                    ray.d = mk(s1.y, s2.x, s2.y);
+                    const uint64_t bits = (uint64_t)__double_as_longlong(s3.y);
+                    flag_at = (uint32_t)(bits & 0xffffffffu);
+                    if (ANYHIT) ShadowVisitor<FEAT, ANYHIT>::restart(v, s3.x, 0.0, -1);
+                    else {
+                        const double2 s4 = lv.sw4[i];
+                        ShadowVisitor<FEAT, ANYHIT>::restart(v, s3.x, s4.x, (int)__double_as_longlong(s4.y));
+                    }
+                    busy = walk_begin(sc, ray, 0, (bits >> 63) != 0, v.tmax(), c);
+                    if (!busy) lv.shadow[flag_at] = ShadowVisitor<FEAT, ANYHIT>::shadowed(sc, v) ? 1 : 0;
+                }
+                next += min(avail, (uint32_t)__popc(idle));
+            }
+        }
+        if (__ballot_sync(FULL, busy) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        if (busy) walk_descend<TALLY>(sc, c, tally, nullptr, 0);
+        if (busy && (c.link == WALK_DONE || walk_leaf(sc, c, v))) {
+            lv.shadow[flag_at] = ShadowVisitor<FEAT, ANYHIT>::shadowed(sc, v) ? 1 : 0;
+            busy = false;
+        }
+    }
+    if (TALLY) flush_tally(tally, lv.stats, lane);
+}
+
+// ---- kernel 4: World::shade_hit for the hits of one level ---------------------------------------------------------
+// One launch per level, deepest level first, so the colours of a hit's children (HitList::child_rgb) are final when the
+// hit is lit.  Per hit: the pattern colour at over_point, Shape::lighting per light (src/shape.rs:429-463) with the
+// shadow bytes, and the light loop of World::shade_hit with its own association (src/world.rs:56-79):
+//     color = black;  for each light:  color += surface + (both ? reflected * R + refracted * (1 - R) : reflected + refracted)
+// where reflected = color_at(child) * reflective and refracted = color_at(child) * transparency (src/world.rs:100,129).
+// The result is stored where the parent looks for it (level 0: the sample): one writer per colour, no atomics.
 // PLAIN: every material of the scene has a Plain pattern (its colour is inlined in the material record), so the
-// pattern evaluator — its frames, the noise code and the shared permutation table — is not compiled in: the kernel
-// fits a register budget that doubles its occupancy (r01f: 96 registers, 27 % of the warp slots occupied, dominant
-// stall long_scoreboard on the hit-record loads).
+// pattern evaluator — its frames, the noise code and the shared permutation table — is not compiled in.
 template <bool PLAIN>
-__global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS : RTC_SHADE_MIN_BLOCKS) shade(const __grid_constant__ Scene sc, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+__global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS : RTC_SHADE_MIN_BLOCKS) light(const __grid_constant__ Scene sc, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     __shared__ uint8_t s_perm[PLAIN ? 1 : 512];
     if (!PLAIN) {
         for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
         __syncthreads();
     }
-
-    uint32_t first[MAX_LEVELS + 1];
-    const uint32_t n_all = hit_prefix(hl, first);
-    const uint32_t n_hits = first[lv.level + 1] - first[lv.level];
-    const uint32_t seg = hl.seg_off[lv.level];
+    const unsigned long long counted = hl.counts[lv.level];
+    const uint32_t seg = hl.seg_off[lv.level], seg_cap = hl.seg_cap[lv.level];
+    const uint32_t n_hits = (uint32_t)(counted < seg_cap ? counted : seg_cap);
     const int L = sc.n_lights;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n_hits; h += stride) {
         const size_t at = (size_t)seg + h;
-        const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at], d = hl.d[at], e = hl.e[at];
-        const uint64_t bits = (uint64_t)__double_as_longlong(hl.f[at].x);
+        const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at], d = hl.d[at], e = hl.e[at], fr = hl.f[at];
+        const uint64_t link = (uint64_t)__double_as_longlong(fr.x);
+        const uint32_t bits = (uint32_t)(uint64_t)__double_as_longlong(fr.y);
         const V3 over_point = mk(a.x, a.y, b.x), normal = mk(b.y, c.x, c.y), eye = mk(d.x, d.y, e.x);
-        const double w = e.y;
-        const uint32_t sample = (uint32_t)(bits >> 32);
-        const Prim prim = load_prim(sc, (int)(uint32_t)(bits & 0xffffffffu));
+        const double reflectance = e.y;
+        const uint32_t parent = (uint32_t)(link >> 32);
+        const Prim prim = load_prim(sc, (int)(uint32_t)(link & 0xffffffffu));
         const Material& mat = sc.materials[prim.material];
+        // ---- what the children returned (src/world.rs:84-132) ----
+        Rgb reflected = rgb(0.0, 0.0, 0.0), refracted = rgb(0.0, 0.0, 0.0);
+        if (bits & HIT_SPAWNED_REFLECTED) {
+            const double* q = child_slot(hl, (uint32_t)at, 0u);
+            reflected = rgb(q[0], q[1], q[2]) * mat.reflective;
+        }
+        if (bits & HIT_SPAWNED_REFRACTED) {
+            const double* q = child_slot(hl, (uint32_t)at, HIT_KIND_REFRACTED);
+            refracted = rgb(q[0], q[1], q[2]) * mat.transparency;
+        }
+        Rgb bounce;
+        if (mat.reflective > 0.0 && mat.transparency > 0.0) bounce = reflected * reflectance + refracted * (1.0 - reflectance);
+        else bounce = reflected + refracted;
+        // ---- the light loop ----
         Rgb color;
         if (PLAIN || (mat.flags & 1)) color = rgb(mat.plain[0], mat.plain[1], mat.plain[2]);
         else {
@@ -373,7 +536,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS 
             const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
             const Rgb intensity = rgb(light.intensity[0], light.intensity[1], light.intensity[2]);
             const V3 lightv = normalize(lpos - over_point);
-            const bool shadowed = lv.shadow[(uint32_t)li * n_all + first[lv.level] + h] != 0;
+            const bool shadowed = lv.shadow[(uint32_t)li * hl.total_cap + (uint32_t)at] != 0;
             const Rgb effective = color * intensity;
             Rgb surface = effective * mat.ambient;
             const double light_dot_normal = dot(lightv, normal);
@@ -387,12 +550,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS 
             } else {
                 surface = surface + rgb(0.0, 0.0, 0.0) + rgb(0.0, 0.0, 0.0);
             }
-            sum = sum + surface;
+            sum = sum + (surface + bounce);
         }
-        double* acc = lv.accum + 3 * (size_t)sample;
-        atomicAdd(acc + 0, sum.r * w);
-        atomicAdd(acc + 1, sum.g * w);
-        atomicAdd(acc + 2, sum.b * w);
+        store_ray_color(hl, lv, lv.level, parent, bits & HIT_KIND_REFRACTED, sum.r, sum.g, sum.b);
     }
 }
 
@@ -439,25 +599,42 @@ void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene
 }
 
 template <int TALLY>
-static void launch_shadow_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+static void launch_shadow_setup_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
     if (sc.all_cast_shadow) {
-        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else trace_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) shadow_setup<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else shadow_setup<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     } else {
-        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else trace_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) shadow_setup<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else shadow_setup<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     }
 }
-void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+void launch_shadow_setup(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     if (sc.n_lights == 0) return;
-    if (feat & FEAT_TALLY) launch_shadow_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv, hl);
-    else launch_shadow_tally<0>(feat, grid, st, sc, f, lv, hl);
+    if (feat & FEAT_TALLY) launch_shadow_setup_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv, hl);
+    else launch_shadow_setup_tally<0>(feat, grid, st, sc, f, lv, hl);
 }
 
-void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {
-    if (sc.plain_only) shade<true><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
-    else shade<false><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
+template <int TALLY>
+static void launch_walk_shadow_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
+    const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
+    if (sc.all_cast_shadow) {
+        if (full) walk_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
+        else walk_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
+    } else {
+        if (full) walk_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
+        else walk_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
+    }
+}
+void launch_walk_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
+    if (sc.n_lights == 0 || sc.n_bvh_items == 0) return;
+    if (feat & FEAT_TALLY) launch_walk_shadow_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv);
+    else launch_walk_shadow_tally<0>(feat, grid, st, sc, f, lv);
+}
+
+void launch_light(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {
+    if (sc.plain_only) light<true><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
+    else light<false><<<grid, RTC_BLOCK, 0, st>>>(sc, lv, hl);
 }
 
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major) {

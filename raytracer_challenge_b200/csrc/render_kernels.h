@@ -22,6 +22,12 @@
 #ifndef RTC_SHADOW_MIN_BLOCKS_CSG
 #define RTC_SHADOW_MIN_BLOCKS_CSG 8
 #endif
+#ifndef RTC_WALK_MIN_BLOCKS  // persistent walk kernels: cursor + visitor + the f64 leaf tests
+#define RTC_WALK_MIN_BLOCKS 6
+#endif
+#ifndef RTC_WALK_MIN_BLOCKS_CSG
+#define RTC_WALK_MIN_BLOCKS_CSG 4
+#endif
 #ifndef RTC_SHADE_MIN_BLOCKS
 #define RTC_SHADE_MIN_BLOCKS 5
 #endif
@@ -47,22 +53,37 @@ struct FrameParams {
 };
 
 // Hit list of one batch: structure-of-arrays of 16-byte chunks (a warp's accesses are whole 512-byte lines), one
-// segment per bounce level at a static offset.  Everything the shadow and shading kernels need is in the record, so
-// neither of them gathers from the ray queue or recomputes the surface frame:
-//   a = (over_point.x, over_point.y)   b = (over_point.z, normal.x)   c = (normal.y, normal.z)
-//   d = (eye.x, eye.y)                 e = (eye.z, throughput)        f = (primitive | sample << 32, unused)
+// segment per bounce level at a static offset.  Written by trace_spawn, read by shadow_setup (a, b) and light:
+//     a = (over_point.x, over_point.y)   b = (over_point.z, normal.x)   c = (normal.y, normal.z)
+//     d = (eye.x, eye.y)                 e = (eye.z, reflectance)       f = (primitive | parent << 32, HIT_* bits)
+// parent: level 0 -> the sample of the batch; level k > 0 -> index of the parent's record in the whole list (its level's
+// seg_off + slot).
+// child_rgb: the colour World::color_at returned for the reflected (kind 0) and refracted (kind 1) ray a hit spawned,
+// 3 doubles per slot; slot = record * 2 + kind if some material both reflects and refracts (fan == 2), else = record.
+// Every spawned ray stores its colour exactly once: black when it misses (trace_spawn), the shaded colour when it
+// hits (light) — so the array needs no clearing, and no atomics.
+constexpr uint32_t HIT_KIND_REFRACTED = 1u;  // this hit's ray is the refracted child of its parent (else the reflected one)
+constexpr uint32_t HIT_SPAWNED_REFLECTED = 2u, HIT_SPAWNED_REFRACTED = 4u;  // the children this hit spawned (src/world.rs:84-132)
 struct HitList {
     double2 *a, *b, *c, *d, *e, *f;
+    double* child_rgb;
     const unsigned long long* counts;  // hits per level (device counters)
     uint32_t seg_off[MAX_LEVELS];      // first record of each level's segment
     uint32_t seg_cap[MAX_LEVELS];
     int32_t n_levels;
+    uint32_t total_cap;                // all segments together = stride of the per-light shadow flag planes
+    int32_t fan;                       // child slots per record (1 or 2)
     int32_t pad;
 };
 
 // One bounce level of one batch.
 //   ray queue (64 B per ray):  q0 = (origin.x, origin.y)  q1 = (origin.z, dir.x)  q2 = (dir.y, dir.z)
-//                              q3 = (throughput, fuel<<32 | sample)
+//                              q3 = (parent record | fuel << 32 | child kind << 40, unused)
+//   shadow walkers (64 / 80 B): the shadow rays that have to walk the BVH (shadow_setup -> walk_shadow)
+//                              s0 = (origin.x, origin.y)  s1 = (origin.z, dir.x)  s2 = (dir.y, dir.z)
+//                              s3 = (distance to the light, flag index | brute-force bit 63)
+//                              s4 = (nearest crossing among the always-tested primitives: t, primitive) — only read by
+//                                   scenes with shapes that cast no shadow
 struct LevelParams {
     const double2 *in_q0, *in_q1, *in_q2, *in_q3;
     double2 *out_q0, *out_q1, *out_q2, *out_q3;
@@ -74,16 +95,23 @@ struct LevelParams {
     int32_t level;
     int32_t pad;
     unsigned long long* hit_count;  // this level's counter (= hits.counts + level)
-    uint8_t* shadow;            // [light][all hits of the batch, level segments packed]: 1 = occluded
-    double* accum;              // 3 doubles per sample of the batch
+    uint8_t* shadow;            // [light][hits.total_cap]: 1 = occluded
+    double* accum;              // 3 doubles per sample of the batch: the colour of its primary ray
     unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms, [7] most node visits of one closest-hit query
     int* overflow;
+    double2 *sw0, *sw1, *sw2, *sw3, *sw4;  // shadow walker queue
+    unsigned long long* sw_count;          // walkers pushed by shadow_setup
+    unsigned long long* sw_head;           // walkers claimed by walk_shadow
+    uint64_t sw_capacity;
 };
 
 void upload_perm(const uint8_t* perm512);
-// Per batch: trace_spawn once per level (a chain), then ONE shadow launch over every hit of the batch, then shade per level.
+// Per batch: trace_spawn once per level (a chain); then over every hit of the batch shadow_setup (uniform: one thread per
+// (hit, light)) and walk_shadow (persistent: the shadow rays that walk the BVH); then light per level, deepest first.
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
-void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
+void launch_shadow_setup(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
+void launch_walk_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+void launch_light(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hits);
 // Device-side LBVH build (bvh_build.cu): everything lives in the scene arena.
 struct LbvhArgs {
     int n;                      // BVH items
@@ -107,7 +135,6 @@ struct LbvhArgs {
 };
 int build_lbvh(const LbvhArgs& a, cudaStream_t st);
 
-void launch_shade(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hits);
 void launch_resolve(cudaStream_t st, const FrameParams& f, const double* accum, uint64_t first_pixel, uint64_t n_pixels, double* out, int row_major);
 
 }  // namespace rtcdev

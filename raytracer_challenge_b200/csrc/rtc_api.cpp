@@ -46,7 +46,7 @@ const uint8_t kPerm[256] = {
 
 constexpr int MAX_PIPES = 8;
 constexpr int MAX_DEVICES = 64;
-constexpr int COUNTERS_PER_BATCH = 64;  // [0..15] queue counts per level, [16..31] hit counts per level, [32..34] stats
+constexpr int COUNTERS_PER_BATCH = 64;  // [0..15] queue counts per level, [16..31] hit counts per level, [32..39] stats, [40] shadow walkers pushed, [41] claimed
 
 // Scratch of one pipeline (= one CUDA stream working through batches): ray queues (ping-pong), hit list, shadow
 // bytes, sample accumulators.
@@ -56,9 +56,11 @@ struct Pipe {
     cudaEvent_t done = nullptr;
     double2* q[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     double2* hit[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    double* child_rgb = nullptr;  // colours the children of a hit returned (HitList::child_rgb)
+    double2* sw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // shadow walker queue (LevelParams::sw0..sw4)
     uint8_t* shadow = nullptr;
     double* accum = nullptr;
-    uint64_t q_capacity = 0, hit_capacity = 0, shadow_bytes = 0, accum_samples = 0;
+    uint64_t q_capacity = 0, hit_capacity = 0, child_doubles = 0, sw_capacity = 0, shadow_bytes = 0, accum_samples = 0;
 };
 
 // Per-device render context: streams, events and scratch memory.  It outlives scenes, so that the drop-in call
@@ -91,9 +93,11 @@ void free_pipe(Pipe& p) {
     for (int a = 0; a < 2; ++a)
         for (int b = 0; b < 4; ++b) { cudaFree(p.q[a][b]); p.q[a][b] = nullptr; }
     for (auto& h : p.hit) { cudaFree(h); h = nullptr; }
+    for (auto& w : p.sw) { cudaFree(w); w = nullptr; }
+    cudaFree(p.child_rgb); p.child_rgb = nullptr;
     cudaFree(p.shadow); p.shadow = nullptr;
     cudaFree(p.accum); p.accum = nullptr;
-    p.q_capacity = p.hit_capacity = p.shadow_bytes = p.accum_samples = 0;
+    p.q_capacity = p.hit_capacity = p.child_doubles = p.sw_capacity = p.shadow_bytes = p.accum_samples = 0;
 }
 
 int env_int(const char* name, int fallback, int lo, int hi);
@@ -527,7 +531,7 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     return rtc_scene_create_multi(desc, &device, 1, out);
 }
 
-static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t shadow_bytes, uint64_t accum_samples) {
+static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t child_doubles, uint64_t sw_capacity, uint64_t shadow_bytes, uint64_t accum_samples) {
     if (q_capacity > p.q_capacity) {
         for (int a = 0; a < 2; ++a)
             for (int c = 0; c < 4; ++c) {
@@ -543,6 +547,17 @@ static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint
         p.hit_capacity = 0;
         for (auto& h : p.hit) CU(cudaMalloc((void**)&h, hit_capacity * sizeof(double2)));
         p.hit_capacity = hit_capacity;
+    }
+    if (child_doubles > p.child_doubles) {
+        cudaFree(p.child_rgb); p.child_rgb = nullptr; p.child_doubles = 0;
+        CU(cudaMalloc((void**)&p.child_rgb, child_doubles * sizeof(double)));
+        p.child_doubles = child_doubles;
+    }
+    if (sw_capacity > p.sw_capacity) {
+        for (auto& w : p.sw) { cudaFree(w); w = nullptr; }
+        p.sw_capacity = 0;
+        for (auto& w : p.sw) CU(cudaMalloc((void**)&w, sw_capacity * sizeof(double2)));
+        p.sw_capacity = sw_capacity;
     }
     if (shadow_bytes > p.shadow_bytes) {
         cudaFree(p.shadow); p.shadow = nullptr; p.shadow_bytes = 0;
@@ -641,6 +656,9 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         if (fan == 2) level_cap *= 2;
     }
     if (hit_cap * (uint64_t)std::max(L, 1) >= 0xf0000000ull) return fail("rtc_render: batch too large");
+    hits.total_cap = (uint32_t)hit_cap;
+    hits.fan = fan;
+    const uint64_t sw_cap = hit_cap * (uint64_t)std::max(L, 1);  // worst case: every shadow ray walks the BVH
     // Batch schedule: (first pixel slot, slots).  Device-resident frames use equal batches.  When each finished batch is
     // copied to the host, the copy of the LAST batch cannot overlap any kernel, so the tail of the schedule is tapered
     // (..., B, B/2, B/4, B/4): the exposed copy shrinks from 1/6 to 1/24 of the frame (teapot 4K: 0.6 -> 0.15 ms).
@@ -667,7 +685,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
     const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
     for (int p = 0; p < n_pipes; ++p)
-        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
+        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)fan * 3, s->dev.n_bvh_items > 0 ? sw_cap : 1, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
     if (n_out > ctx.out_pixels) {
         cudaFree(ctx.out); ctx.out = nullptr; ctx.out_pixels = 0;
         CU(cudaMalloc((void**)&ctx.out, std::max<uint64_t>(n_out, 1) * 3 * sizeof(double)));
@@ -693,6 +711,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     CU(cudaEventRecord(ctx.ev[0], st0));
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
+    const int grid_walk = ctx.sm_count * env_int("RTC_WALK_BLOCKS_PER_SM", 8, 1, 32);  // persistent: about what is resident
     const int feat = s->feat | (profile ? rtcdev::FEAT_TALLY : 0);  // the work tallies are counted under RTC_FLAG_PROFILE only
     uint64_t launches = 0;
     const bool timeline = std::getenv("RTC_TIMELINE") != nullptr;  // debugging aid: when each batch's kernels / copy finished
@@ -716,7 +735,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         const uint64_t npix = schedule[b].second;
         if (!npix) break;
         unsigned long long* cnt = ctx.counters + b * COUNTERS_PER_BATCH;
-        CU(cudaMemsetAsync(p.accum, 0, npix * f.spp * 3 * sizeof(double), st));
+        CU(cudaMemsetAsync(p.accum, 0, npix * f.spp * 3 * sizeof(double), st));  // (padding slots of partial tiles are never written)
+        hits.child_rgb = p.child_rgb;
         hits.a = p.hit[0]; hits.b = p.hit[1]; hits.c = p.hit[2]; hits.d = p.hit[3]; hits.e = p.hit[4]; hits.f = p.hit[5];
         hits.counts = cnt + 16;
         auto level_params = [&](int level) {
@@ -736,6 +756,10 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
             lv.accum = p.accum;
             lv.stats = cnt + 32;
             lv.overflow = ctx.overflow;
+            lv.sw0 = p.sw[0]; lv.sw1 = p.sw[1]; lv.sw2 = p.sw[2]; lv.sw3 = p.sw[3]; lv.sw4 = p.sw[4];
+            lv.sw_count = cnt + 40;
+            lv.sw_head = cnt + 41;
+            lv.sw_capacity = p.sw_capacity;
             return lv;
         };
         const int grid0 = (int)std::min<uint64_t>((uint64_t)grid_full, (npix * f.spp + RTC_BLOCK - 1) / RTC_BLOCK);
@@ -743,12 +767,13 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         for (int level = 0; level <= o.fuel; ++level)  // the chain: level k+1 depends on level k only
             rtcdev::launch_trace(feat, level == 0, level == 0 ? grid0 : grid_full, st, s->dev, f, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
-        rtcdev::launch_shadow(feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
+        rtcdev::launch_shadow_setup(feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
+        rtcdev::launch_walk_shadow(feat, grid_walk, st, s->dev, f, level_params(0));        // ... and the ones that walk the BVH
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
-        for (int level = 0; level <= o.fuel; ++level)  // in level order: a sample's terms are added in a fixed order
-            rtcdev::launch_shade(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
+        for (int level = o.fuel; level >= 0; --level)  // deepest first: a hit is lit when its children's colours are final
+            rtcdev::launch_light(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
-        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0);
+        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0) + (L > 0 && s->dev.n_bvh_items > 0 ? 1 : 0);
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
         launches++;
         if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, st)); tl_events.push_back(e); }

@@ -43,7 +43,7 @@ def test_scene_matches_oracle(built, name, w, h):
     # tolerance above is the contract; in practice the f64 device path agrees to rounding noise
     assert rep["max_abs_f64"] < 1e-9, rep
     # BVH culling must not change anything relative to testing every primitive
-    assert np.array_equal(img, brute) or compare_images(img, brute)["hist"]["0"] == w * h
+    assert np.array_equal(img, brute)
     # R_ref: the GPU's count of reference-equivalent World::intersect queries equals the oracle's own count
     assert st.rays_ref == int(counts.sum()), (st.as_dict(), counts)
 
@@ -78,10 +78,9 @@ def test_cuda_matches_reference_png_window(built, entry):
 
 # ---- sharding, windows, supersampling, profiling: same pixels whichever way they are produced -------------------
 def same_pixels(name, a, b):
-    """Bit-identical, except for scenes whose materials both reflect and refract: there several path-tree nodes of one
-    pixel sit in the same bounce level and their f64 atomic adds commute only up to the last bit."""
-    if name in ("glass_air_bubble", "csg_noise", "chapter11_title") or name.startswith("fuzz"):
-        return np.allclose(a, b, rtol=0.0, atol=1e-12, equal_nan=False)
+    """Bit-identical for every scene: each colour of the path tree has exactly one writer (render_kernels.cu: a ray's
+    colour is stored where its parent looks for it, no atomic accumulation), so neither sharding, batching, windows nor
+    the order in which warps run can change a bit."""
     return np.array_equal(a, b)
 
 
