@@ -151,7 +151,9 @@ typedef struct rtc_opts {
 } rtc_opts;
 
 typedef struct rtc_stats {
-    uint64_t rays_primary, rays_shadow, rays_reflected, rays_refracted; /* R_uniq: rays actually traced */
+    uint64_t rays_primary, rays_shadow, rays_reflected, rays_refracted; /* R_uniq: the reference's World::intersect queries answered, secondary
+                                                                         * sub-trees deduplicated across lights.  rays_shadow = one is_shadowed query per
+                                                                         * (hit, light); shadow_queries_culled of them were answered without a traversal */
     uint64_t rays_ref;       /* R_ref: World::intersect queries the reference would issue for the same image */
     uint64_t kernel_launches;
     uint64_t pixels;         /* pixels produced by this call (shard) */
@@ -170,6 +172,8 @@ typedef struct rtc_stats {
     /* RTC_FLAG_PROFILE only: CUDA-event time per kernel class, launches serialised on one stream */
     double ms_trace, ms_shadow, ms_shade;
     uint64_t max_node_visits; /* the longest single closest-hit traversal of the call (BVH node visits of one ray) */
+    uint64_t shadow_queries_culled; /* is_shadowed queries whose light lies behind the surface: Shape::lighting ignores their answer
+                                     * (src/shape.rs:449), so nothing is traced for them; included in rays_shadow */
 } rtc_stats;
 
 typedef struct rtc_scene rtc_scene;

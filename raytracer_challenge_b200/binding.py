@@ -41,7 +41,8 @@ class Stats(C.Structure):  # rtc_stats
                 ("ms_trace_shade", C.c_double), ("ms_d2h", C.c_double), ("overflow", C.c_int32), ("reserved", C.c_int32),
                 ("surface_hits", C.c_uint64), ("bvh_node_visits", C.c_uint64), ("triangle_tests", C.c_uint64),
                 ("primitive_tests", C.c_uint64), ("ray_transforms", C.c_uint64),
-                ("ms_trace", C.c_double), ("ms_shadow", C.c_double), ("ms_shade", C.c_double), ("max_node_visits", C.c_uint64)]
+                ("ms_trace", C.c_double), ("ms_shadow", C.c_double), ("ms_shade", C.c_double), ("max_node_visits", C.c_uint64),
+                ("shadow_queries_culled", C.c_uint64)]
 
     @property
     def rays(self):

@@ -305,6 +305,20 @@ __device__ __forceinline__ void plane_roots_row(double r0, double r1, double r2,
     out.t[0] = -oy / dy;
     out.n = 1;
 }
+// The same crossing left as a fraction, t = -oy / dy, for queries that can often decide without the division (below).
+// Returns false when there is no crossing to consider.
+__device__ __forceinline__ bool plane_fraction(double r0, double r1, double r2, double r3, const Ray& world, bool skip_negative, double& oy, double& dy) {
+    oy = r0 * world.o.x + r1 * world.o.y + r2 * world.o.z + r3;
+    dy = r0 * world.d.x + r1 * world.d.y + r2 * world.d.z;
+    if (approx0(dy)) return false;
+    if (skip_negative && ((oy > 0.0 && dy > 0.0) || (oy < 0.0 && dy < 0.0))) return false;
+    return true;
+}
+// Is t = -oy / dy (as the reference rounds it) certainly above `bound`?  |oy| > |bound * dy| with a margin of 1e-14
+// (the product and the quotient are each rounded once, 1.1e-16) means the exact quotient exceeds bound by more than any
+// rounding can undo.  Only meaningful for crossings with t >= 0 and bound >= 0; NaN operands answer false.
+__device__ __forceinline__ bool plane_certainly_above(double oy, double dy, double bound) { return fabs(oy) > fabs(bound * dy) * (1.0 + 1e-14); }
+__device__ __forceinline__ bool plane_certainly_below(double oy, double dy, double bound) { return fabs(oy) < fabs(bound * dy) * (1.0 - 1e-14); }
 __device__ __forceinline__ void plane_roots(const Scene& sc, int xform, const Ray& world, bool skip_negative, Roots& out) {
     const double2* q = reinterpret_cast<const double2*>(sc.xforms[xform].inv + 4);
     const double2 a = __ldg(q), b = __ldg(q + 1);

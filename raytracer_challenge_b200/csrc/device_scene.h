@@ -33,7 +33,8 @@ struct MatInv {
     double m[16];  // world -> pattern space, full row-major 4x4: pattern space carries w (see device_pattern.cuh)
 };
 
-// kind_flags: bits 0..7 kind (rtc_prim_kind), bit 8 casts_shadow, bit 9 closed
+// kind_flags: bits 0..7 kind (rtc_prim_kind), bit 8 casts_shadow, bit 9 closed, bit 10 PRIM_IN_BVH
+constexpr int32_t PRIM_IN_BVH = 0x400;  // reached through the BVH (an item, or part of a CSG item), not through the always-tested list
 struct Prim {
     int32_t kind_flags;
     int32_t material;

@@ -213,7 +213,11 @@ struct Walk {
 // true box — is beyond any t a query can ask for.  Geometrically the clamped axis is a ray tilted by < 2^-60: over the
 // scene's extent that is far inside the padding, so the walk stays conservative ("conservative fp32 culling").
 __device__ __forceinline__ float walk_inverse(double d) {
-    const float i = 1.0f / (float)d;
+    // rcp.approx (one MUFU, <= 1 ulp) instead of an IEEE division (r02b: the three divisions were 10 % of the uniform
+    // shadow stage): a relative error of 2^-23 in i moves a slab plane by <= 2^-23 x (distance travelled), far inside
+    // the padding of the boxes, and culling — all this feeds — stays conservative.  ftz: a denormal d gives inf -> clamped.
+    float i;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(i) : "f"((float)d));
     const float big = 1152921504606846976.0f;  // 2^60
     return fabsf(i) <= big ? i : copysignf(big, i);  // (a NaN direction lands here too: any finite value will do)
 }
@@ -274,9 +278,10 @@ __device__ __forceinline__ float walk_thi(double tmax, double te) { return __dou
 // Visitor protocol:  bool V::leaf(int slot) -> true stops the walk;  double V::tmax() -> current upper bound on t
 // (re-read only after a leaf was visited: it cannot change in between).
 //
-// The walk is resumable: a cursor holds everything between two steps, so that a kernel can either run a query to its
-// end (walk_bvh, below) or interleave the queries of a warp's lanes and hand a lane whose query has ended the next
-// ray of a queue (the persistent walk kernels of render_kernels.cu).
+// The walk is resumable: a cursor holds everything between two steps (walk_begin / walk_descend / walk_leaf); walk_bvh
+// runs a query to its end.  (r02b tried persistent warps that hand a lane whose query has ended the next ray of a queue:
+// 14 instead of 10 of 32 lanes in the node loop, no fewer instructions in total, worse overlap between the batch
+// pipelines — profiles/README.md.)
 constexpr int WALK_DONE = (int)0x80000000;  // never a leaf link: ~enc with enc >= 0 is > INT_MIN
 struct WalkCursor {
     Walk w;
@@ -284,7 +289,12 @@ struct WalkCursor {
     int link;        // >= 0: inner node; WALK_DONE: the query is over; any other negative value: a leaf link
     int sp;
     int brute_next;  // >= 0: brute-force scan (RTC_FLAG_BRUTE_FORCE, cone guards), the next item to test; -1: BVH walk
-    int stack[BVH_STACK];
+};
+// The pending subtrees live in a separate array (local memory: it is indexed dynamically); keeping it out of the cursor
+// lets the cursor's scalars stay in registers (r02b: with the array inside, the node loop reloaded the walk constants
+// from local memory on every iteration).
+struct WalkStack {
+    int at[BVH_STACK];
 };
 
 // Starts a query.  Returns false (link = WALK_DONE) when the ray cannot touch any BVH item.
@@ -310,9 +320,10 @@ __device__ __forceinline__ bool walk_begin(const Scene& sc, const Ray& ray, int 
 // iteration pays for the (4-5x more expensive, f64) leaf code.
 // top / n_top: the first n_top nodes staged in shared memory by the caller (persistent kernels), or (nullptr, 0).
 template <bool TALLY>
-__device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, Tally& tally, const BvhNode* __restrict__ top, int n_top) {
+__device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, WalkStack& stack, Tally& tally, const BvhNode* __restrict__ top, int n_top) {
     int link = c.link, sp = c.sp;
     const float thi = c.thi;
+    const Walk w = c.w;
     while (link >= 0) {
         if (TALLY) tally.nodes++;
         float4 q0, q1, q2, q3;
@@ -324,19 +335,19 @@ __device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, Tal
             q0 = __ldg(q); q1 = __ldg(q + 1); q2 = __ldg(q + 2); q3 = __ldg(q + 3);
         }
         float n0, n1;
-        const bool h0 = slab(c.w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
-        const bool h1 = slab(c.w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
+        const bool h0 = slab(w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
+        const bool h1 = slab(w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
         const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
         if (h0 && h1) {
             const bool first0 = n0 <= n1;
-            c.stack[sp++] = first0 ? c1 : c0;
+            stack.at[sp++] = first0 ? c1 : c0;
             link = first0 ? c0 : c1;
         } else if (h0) {
             link = c0;
         } else if (h1) {
             link = c1;
         } else {
-            link = sp ? c.stack[--sp] : WALK_DONE;
+            link = sp ? stack.at[--sp] : WALK_DONE;
         }
     }
     c.link = link;
@@ -346,7 +357,7 @@ __device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, Tal
 // Leaf phase: tests the items of the leaf this lane stands on, then moves to the next pending subtree.
 // Returns true when the query is over (the visitor stopped it, or nothing is left to visit).
 template <class V>
-__device__ __forceinline__ bool walk_leaf(const Scene& sc, WalkCursor& c, V& v) {
+__device__ __forceinline__ bool walk_leaf(const Scene& sc, WalkCursor& c, WalkStack& stack, V& v) {
     const int enc = ~c.link;
     const int first = enc >> 2, count = (enc & 3) + 1;
     for (int i = 0; i < count; ++i)
@@ -359,18 +370,19 @@ __device__ __forceinline__ bool walk_leaf(const Scene& sc, WalkCursor& c, V& v) 
     }
     c.thi = walk_thi(v.tmax(), c.w.te);
     if (c.sp == 0) { c.link = WALK_DONE; return true; }
-    c.link = c.stack[--c.sp];
+    c.link = stack.at[--c.sp];
     return false;
 }
 
 template <class V>
 __device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v, Tally& tally) {
     WalkCursor c;
+    WalkStack stack;
     if (!walk_begin(sc, ray, mode, brute, v.tmax(), c)) return;
     for (;;) {
-        walk_descend<V::kTally>(sc, c, tally, nullptr, 0);
+        walk_descend<V::kTally>(sc, c, stack, tally, nullptr, 0);
         if (c.link == WALK_DONE) return;
-        if (walk_leaf(sc, c, v)) return;
+        if (walk_leaf(sc, c, stack, v)) return;
     }
 }
 
@@ -440,9 +452,13 @@ struct ClosestVisitor {
         return false;
     }
     __device__ __forceinline__ bool plane(const FastPlane& p) {
-        Roots r;
-        q.roots_of_fast_plane(p, r);
-        if (r.n) offer(r.t[0], p.prim, 0.0, 0.0);
+        // t = -oy / dy costs an IEEE division (~30 instructions); a plane that certainly lies beyond the nearest crossing
+        // found so far (or beyond the query's limit) is dropped on a product instead — the result is unchanged.
+        double oy, dy;
+        q.counters().prims++;
+        if (!plane_fraction(p.row[0], p.row[1], p.row[2], p.row[3], q.ray, q.skip_negative, oy, dy)) return false;
+        if (plane_certainly_above(oy, dy, tmax())) return false;
+        offer(-oy / dy, p.prim, 0.0, 0.0);
         return false;
     }
     __device__ __forceinline__ bool leaf(int slot) {
@@ -498,9 +514,17 @@ struct AnyVisitor {
         return test(r);
     }
     __device__ __forceinline__ bool plane(const FastPlane& p) {
-        Roots r;
-        q.roots_of_fast_plane(p, r);
-        return test(r);
+        // "0 <= -oy / dy < dist" without the division unless the crossing is within 1e-14 (relative) of the light
+        double oy, dy;
+        q.counters().prims++;
+        if (!plane_fraction(p.row[0], p.row[1], p.row[2], p.row[3], q.ray, true, oy, dy)) return false;  // (no crossing, or t < 0)
+        if (plane_certainly_above(oy, dy, dist)) return false;
+        if (!plane_certainly_below(oy, dy, dist)) {
+            const double t = -oy / dy;
+            if (!(t >= 0.0 && t < dist)) return false;
+        }
+        found = true;
+        return true;
     }
     __device__ __forceinline__ bool leaf(int slot) {
         const LeafItem li = load_leaf(q.sc, slot);

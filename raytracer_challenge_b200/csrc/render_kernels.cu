@@ -8,13 +8,8 @@
 //                  frame of prepare_state (src/intersection.rs:50-68) -> hit record appended to the level's segment of
 //                  the hit list, and the reflected / refracted children (src/world.rs:84-132) pushed to the next
 //                  level's queue.  A ray that misses stores black where its parent will look for its colour.
-//   shadow_setup x 1, uniform: one thread per (hit, light) over the hits of ALL levels, light-major: the shadow ray of
-//                  World::is_shadowed (src/world.rs:26-48), the always-tested primitives and the root box of the BVH.
-//                  Most shadow rays are decided here (one byte per (hit, light)); the others are appended to the
-//                  shadow walker queue.
-//   walk_shadow  x 1, persistent: warps walk the BVH for the queued shadow rays; a lane whose ray is decided takes
-//                  the next ray of the queue at once, so the node loop and the f64 leaf tests run on full warps
-//                  (before: 10 of 32 lanes, profiles/README.md r02a).
+//   trace_shadow x 1: one thread per (hit, light) over the hits of ALL levels, light-major: World::is_shadowed
+//                  (src/world.rs:26-48) -> one byte per (hit, light)
 //   light        x (fuel + 1), a chain UP the levels (deepest first): World::shade_hit for every hit of the level —
 //                  pattern colour, Shape::lighting per light (src/shape.rs:429-463), plus the colours its children
 //                  stored, combined in the reference's own order (src/world.rs:58-79) — stored where the parent
@@ -25,12 +20,21 @@
 // neither the shadow nor the lighting kernels gather from the ray queue or recompute the surface frame: everything
 // they need is in the hit record (96 B, coalesced).
 //
+// Ray queues and hit lists are compacted with ballot + popc and one atomic per warp and counter.  Nothing depends on
+// the order of a queue — every ray carries the record that waits for its colour — so a scene may ask for TWO bins
+// (FrameParams::two_bins): rays that leave a BVH item and rays that leave an always-tested primitive (the planes).
+// The former start inside the BVH's root box and walk it, most of the latter pass it by.  Measured (profiles/README.md,
+// r02c): -10 % frame time where a BVH item is expensive to test (CSG programs), +-2 % on the mesh and sphere scenes
+// (their walkers' path lengths differ too much for a warp of walkers to stay full), so only CSG scenes use it.
+//
 // The reference evaluates the secondary rays once per light inside the light loop (src/world.rs:58-79); here each
 // child is traced once and its colour is added once per light.
 // Built with -fmad=false: see device_math.cuh.
 #include "device_pattern.cuh"
 #include "device_trace.cuh"
 #include "render_kernels.h"
+
+#include <algorithm>
 
 namespace rtcdev {
 
@@ -89,7 +93,7 @@ __device__ __forceinline__ Ray camera_ray(const FrameParams& f, int px, int py, 
 // Ray `idx` of the level's input.  Returns false for the padding slots of a partial tile (primary level only).
 // parent: the record (level 0: the sample) that waits for this ray's colour; kind: HIT_KIND_REFRACTED or 0.
 template <bool PRIMARY>
-__device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams& lv, uint32_t idx, Ray& ray, uint32_t& parent, uint32_t& kind, int& fuel) {
+__device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams& lv, uint32_t idx, uint32_t n_front, Ray& ray, uint32_t& parent, uint32_t& kind, int& fuel) {
     if (PRIMARY) {
         const uint32_t s = (uint32_t)lv.first_sample + idx;
         uint32_t pix = s, sub = 0;
@@ -103,7 +107,9 @@ __device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams
         ray = camera_ray(f, px, py, (int)sub);
         return true;
     }
-    const double2 a = lv.in_q0[idx], b = lv.in_q1[idx], c = lv.in_q2[idx], e = lv.in_q3[idx];
+    // front bin: slots 0 .. n_front-1; back bin: the last slots of the queue, downwards
+    const size_t at = idx < n_front ? (size_t)idx : (size_t)lv.in_capacity - 1u - (idx - n_front);
+    const double2 a = lv.in_q0[at], b = lv.in_q1[at], c = lv.in_q2[at], e = lv.in_q3[at];
     ray.o = mk(a.x, a.y, b.x);
     ray.d = mk(b.y, c.x, c.y);
     const uint64_t bits = (uint64_t)__double_as_longlong(e.x);
@@ -113,11 +119,14 @@ __device__ __forceinline__ bool load_ray(const FrameParams& f, const LevelParams
     return true;
 }
 
+// Rays of the level's input: both bins of the queue (n_front of them in the front bin).
 template <bool PRIMARY>
-__device__ __forceinline__ uint32_t level_rays(const LevelParams& lv) {
-    if (PRIMARY) return (uint32_t)lv.n_primary;
-    const unsigned long long n = *lv.in_count;
-    return (uint32_t)(n < lv.in_capacity ? n : lv.in_capacity);
+__device__ __forceinline__ uint32_t level_rays(const LevelParams& lv, uint32_t& n_front) {
+    if (PRIMARY) { n_front = (uint32_t)lv.n_primary; return n_front; }
+    const unsigned long long nf = *lv.in_count, nb = *lv.in_count_back;
+    n_front = (uint32_t)(nf < lv.in_capacity ? nf : lv.in_capacity);
+    const uint64_t room = lv.in_capacity - n_front;
+    return n_front + (uint32_t)(nb < room ? nb : room);
 }
 
 // Adds a thread's tally to the batch counters: warp reduce, one atomic per counter per warp.
@@ -145,16 +154,49 @@ __device__ __forceinline__ Surface surface_at(const Scene& sc, const Prim& prim,
     return s;
 }
 
-// prefix sums of the per-level hit counts: first[k] = hits of the levels before k, first[n_levels] = all hits
-__device__ __forceinline__ uint32_t hit_prefix(const HitList& hl, uint32_t* first) {
+// The hits of a batch, enumerated bin by bin: the front bins (hits on BVH items) of all levels, then the back bins
+// (hits on always-tested primitives).  Range r covers packed indices [first[r], first[r + 1]); its records sit at
+// base[r] + step[r] * k (front bins grow up from the start of the level's segment, back bins down from its end).
+struct HitRanges {
+    uint32_t first[2 * MAX_LEVELS + 1];
+    uint32_t base[2 * MAX_LEVELS];
+    int n;
+};
+__device__ __forceinline__ void level_bins(const HitList& hl, int level, uint32_t& n_front, uint32_t& n_back) {
+    const uint32_t cap = hl.seg_cap[level];
+    const unsigned long long cf = hl.counts[level], cb = hl.counts_back[level];
+    n_front = (uint32_t)(cf < cap ? cf : cap);
+    n_back = (uint32_t)(cb < cap - n_front ? cb : cap - n_front);
+}
+__device__ __forceinline__ uint32_t hit_ranges(const HitList& hl, HitRanges& hr) {
     uint32_t total = 0;
+    hr.n = 2 * hl.n_levels;
     for (int k = 0; k < hl.n_levels; ++k) {
-        first[k] = total;
-        const unsigned long long n = hl.counts[k];
-        total += (uint32_t)(n < hl.seg_cap[k] ? n : hl.seg_cap[k]);
+        uint32_t nf, nb;
+        level_bins(hl, k, nf, nb);
+        hr.first[k] = nf;                  // (counts for now: prefix sums below)
+        hr.first[hl.n_levels + k] = nb;
+        hr.base[k] = hl.seg_off[k];
+        hr.base[hl.n_levels + k] = hl.seg_off[k] + hl.seg_cap[k] - 1u;
     }
-    first[hl.n_levels] = total;
+    for (int r = 0; r < hr.n; ++r) {
+        const uint32_t n = hr.first[r];
+        hr.first[r] = total;
+        total += n;
+    }
+    hr.first[hr.n] = total;
     return total;
+}
+__device__ __forceinline__ size_t hit_at(const HitRanges& hr, uint32_t j) {
+    const int half = hr.n >> 1;
+    int r = j >= hr.first[half] ? half : 0;  // front bins of all levels, then back bins
+    while (r + 1 < hr.n && j >= hr.first[r + 1]) ++r;
+    const uint32_t k = j - hr.first[r];
+    return r < (hr.n >> 1) ? (size_t)hr.base[r] + k : (size_t)hr.base[r] - k;
+}
+// Record of hit h of one level (light): front bin first.
+__device__ __forceinline__ size_t level_hit_at(const HitList& hl, int level, uint32_t n_front, uint32_t h) {
+    return h < n_front ? (size_t)hl.seg_off[level] + h : (size_t)hl.seg_off[level] + hl.seg_cap[level] - 1u - (h - n_front);
 }
 
 // Where the colour of the `kind` child of record `rec` is stored (HitList::child_rgb).
@@ -177,7 +219,8 @@ __device__ __forceinline__ void store_ray_color(const HitList& hl, const LevelPa
 template <int FEAT, bool PRIMARY>
 __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_BLOCKS_CSG : (FEAT & FEAT_TRANSPARENT) ? RTC_TRACE_MIN_BLOCKS_TRANSPARENT : RTC_TRACE_MIN_BLOCKS) trace_spawn(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
-    const uint32_t n_in = level_rays<PRIMARY>(lv);
+    uint32_t n_front_in = 0;
+    const uint32_t n_in = level_rays<PRIMARY>(lv, n_front_in);
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
     const int L = sc.n_lights;
@@ -195,10 +238,10 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
         Ray ray;
         uint32_t parent = 0, kind = 0;
         int fuel = 0;
-        const bool active = idx < n_in && load_ray<PRIMARY>(f, lv, idx, ray, parent, kind, fuel);
+        const bool active = idx < n_in && load_ray<PRIMARY>(f, lv, idx, n_front_in, ray, parent, kind, fuel);
         Hit hit;
         hit.prim = -1;
-        bool push_refl = false, push_refr = false;
+        bool push_refl = false, push_refr = false, front = false, front_q = false;
         Ray r_refl, r_refr;
         double reflectance = 0.0;
         Surface s;
@@ -209,6 +252,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
             if (TALLY) longest = max(longest, tally.nodes - nodes_before);
             if (hit.prim >= 0) {
                 const Prim prim = load_prim(sc, hit.prim);
+                front = f.two_bins != 0 && (prim.kind_flags & PRIM_IN_BVH) != 0;
+                front_q = front;
                 const Material& mat = sc.materials[prim.material];
                 const double reflective = mat.reflective, transparency = mat.transparency;
                 double n1 = 1.0, n2 = 1.0;
@@ -240,27 +285,36 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
             }
         }
         const unsigned below = (1u << lane) - 1u;
-        // Slots for the hit records and for the children: one atomic per warp and counter, both issued by lane 0
-        // back to back so that their round trips to L2 overlap (r01f: the two dependent round trips were 6-12 % of
-        // the kernel's stall samples).
+        // Slots for the hit records and for the children, per bin (front: the hit primitive is a BVH item): one atomic
+        // per warp, bin and counter, all issued by lane 0 back to back so that their round trips to L2 overlap (r01f:
+        // dependent round trips were 6-12 % of the kernel's stall samples).
         const bool is_hit = active && hit.prim >= 0;
         const unsigned m = __ballot_sync(0xffffffffu, is_hit);
+        const unsigned m_front = __ballot_sync(0xffffffffu, is_hit && front);
+        const unsigned q_front = __ballot_sync(0xffffffffu, is_hit && front_q);
         const unsigned m_refl = __ballot_sync(0xffffffffu, push_refl);
         const unsigned m_refr = (FEAT & FEAT_TRANSPARENT) ? __ballot_sync(0xffffffffu, push_refr) : 0u;
-        const int n_push = __popc(m_refl) + __popc(m_refr);
-        unsigned long long hit_base = 0, base = 0;
+        const unsigned hf = m & m_front, hb = m & ~m_front;
+        const int n_qf = __popc(m_refl & q_front) + __popc(m_refr & q_front), n_qb = __popc(m_refl & ~q_front) + __popc(m_refr & ~q_front);
+        unsigned long long base_hf = 0, base_hb = 0, base_qf = 0, base_qb = 0;
         if (lane == 0) {
-            if (m) hit_base = atomicAdd(lv.hit_count, (unsigned long long)__popc(m));
-            if (n_push) base = atomicAdd(lv.out_count, (unsigned long long)n_push);
+            if (hf) base_hf = atomicAdd(lv.hit_count, (unsigned long long)__popc(hf));
+            if (hb) base_hb = atomicAdd(lv.hit_count_back, (unsigned long long)__popc(hb));
+            if (n_qf) base_qf = atomicAdd(lv.out_count, (unsigned long long)n_qf);
+            if (n_qb) base_qb = atomicAdd(lv.out_count_back, (unsigned long long)n_qb);
         }
-        hit_base = __shfl_sync(0xffffffffu, hit_base, 0);
-        base = __shfl_sync(0xffffffffu, base, 0);
+        base_hf = __shfl_sync(0xffffffffu, base_hf, 0);
+        base_hb = __shfl_sync(0xffffffffu, base_hb, 0);
+        base_qf = __shfl_sync(0xffffffffu, base_qf, 0);
+        base_qb = __shfl_sync(0xffffffffu, base_qb, 0);
+        const unsigned mine = front ? m_front : ~m_front;  // the lanes of this lane's bin
         // ---- hit record ----
         uint32_t record = 0;
         if (is_hit) {
-            const uint64_t slot = hit_base + (uint64_t)__popc(m & below);
-            if (slot < seg_cap) {
-                const size_t at = (size_t)seg + slot;
+            // the two bins grow towards each other inside the level's segment, which is sized for "every ray hits"
+            const uint64_t k = (front ? base_hf : base_hb) + (uint64_t)__popc(m & mine & below);
+            if (k < seg_cap) {
+                const size_t at = front ? (size_t)seg + k : (size_t)seg + seg_cap - 1u - k;
                 record = (uint32_t)at;
                 const uint32_t bits = kind | (push_refl ? HIT_SPAWNED_REFLECTED : 0u) | (push_refr ? HIT_SPAWNED_REFRACTED : 0u);
                 hl.a[at] = make_double2(s.over_point.x, s.over_point.y);
@@ -275,12 +329,15 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                 push_refr = false;
             }
         }
-        // ---- children: warp-aggregated compaction into the next level's queue ----
-        if (n_push) {
+        // ---- children: warp-aggregated compaction into the next level's queue, same bin as their parent's record ----
+        if (push_refl || push_refr) {
             const uint64_t link = (uint64_t)(uint32_t)(fuel - 1) << 32 | record;
+            const uint64_t base = front_q ? base_qf : base_qb;
+            const unsigned mine_q = front_q ? q_front : ~q_front;
             if (push_refl) {
-                const uint64_t slot = base + (uint64_t)__popc(m_refl & below);
-                if (slot < lv.out_capacity) {
+                const uint64_t k = base + (uint64_t)__popc(m_refl & mine_q & below);
+                if (k < lv.out_capacity) {
+                    const size_t slot = front_q ? (size_t)k : (size_t)lv.out_capacity - 1u - k;
                     lv.out_q0[slot] = make_double2(r_refl.o.x, r_refl.o.y);
                     lv.out_q1[slot] = make_double2(r_refl.o.z, r_refl.d.x);
                     lv.out_q2[slot] = make_double2(r_refl.d.y, r_refl.d.z);
@@ -292,8 +349,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                 if (SPLIT) c_refl++;
             }
             if ((FEAT & FEAT_TRANSPARENT) && push_refr) {
-                const uint64_t slot = base + (uint64_t)__popc(m_refl) + (uint64_t)__popc(m_refr & below);
-                if (slot < lv.out_capacity) {
+                const uint64_t k = base + (uint64_t)__popc(m_refl & mine_q) + (uint64_t)__popc(m_refr & mine_q & below);
+                if (k < lv.out_capacity) {
+                    const size_t slot = front_q ? (size_t)k : (size_t)lv.out_capacity - 1u - k;
                     lv.out_q0[slot] = make_double2(r_refr.o.x, r_refr.o.y);
                     lv.out_q1[slot] = make_double2(r_refr.o.z, r_refr.d.x);
                     lv.out_q2[slot] = make_double2(r_refr.d.y, r_refr.d.z);
@@ -321,159 +379,51 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
     }
 }
 
-// ---- kernel 2: World::is_shadowed, uniform half -----------------------------------------------------------------
-// One thread per (hit, light) of the batch, all levels in one launch, light-major: consecutive threads take consecutive
-// hits towards the SAME light.  Builds the shadow ray (src/world.rs:33-40), tests the always-tested primitives and the
-// root box of the BVH: every lane runs the same straight-line code.  A ray that is decided stores its byte; a ray that has
-// to walk the BVH is appended to the shadow walker queue (one atomic per warp).
-// ANYHIT: every shape casts shadows, so "nearest crossing < distance" <=> "any crossing in [0, distance)".  Otherwise the
-// nearest crossing decides (src/world.rs:43-47) and the walk is a closest-hit query below `distance`.
+// ---- kernel 2: World::is_shadowed for every (hit, light) of the batch, all levels in one launch ----------------
+// blockIdx.y = light, threads stride over the hits: consecutive threads take consecutive hits towards the SAME light, so
+// a warp's rays start next to each other and head the same way.  The hits are enumerated bin by bin (hits on BVH items
+// of every level first, then hits on always-tested primitives: HitList), so a warp's shadow rays either all start
+// inside the BVH's root box — and walk — or mostly pass it by.
+// A light behind the surface (light . normal < 0, the same expression Shape::lighting evaluates, src/shape.rs:449) gets
+// ambient light only whatever is_shadowed says: such a query is answered without tracing anything.
 template <int FEAT, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) shadow_setup(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
-    const bool brute_all = (f.flags & 1u) != 0;
-    uint32_t first[MAX_LEVELS + 1];
-    const uint32_t n_hits = hit_prefix(hl, first);
-    const uint32_t L = (uint32_t)sc.n_lights;
-    const uint32_t total = n_hits * L;  // < 2^32: checked by the host (hit capacity * lights)
+__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) trace_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
+    const bool brute = (f.flags & 1u) != 0;
+    __shared__ HitRanges hr;  // (one copy per block: per-thread copies of the two small tables sat in local memory)
+    __shared__ uint32_t s_hits;
+    if (threadIdx.x == 0) s_hits = hit_ranges(hl, hr);
+    __syncthreads();
+    const uint32_t n_hits = s_hits;
+    const uint32_t li = blockIdx.y;
     const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t n_round = (total + 31u) & ~31u;
-    const unsigned lane = threadIdx.x & 31u;
     Tally tally = {0u, 0u, 0u, 0u};
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-        bool walk = false, brute = false;
+    uint32_t skipped = 0;
+    const Light& light = sc.lights[li];
+    const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_hits; j += stride) {
+        const size_t at = hit_at(hr, j);
+        const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at];
+        const V3 over_point = mk(a.x, a.y, b.x), normal = mk(b.y, c.x, c.y);
+        const V3 to_light = lpos - over_point;
+        const double distance = magnitude(to_light);
         Ray sray;
-        double distance = 0.0, t0 = 0.0;
-        int prim0 = -1;
-        uint32_t flag_at = 0;
-        if (i < total) {
-            const uint32_t li = i / n_hits;
-            const uint32_t j = i - li * n_hits;  // packed hit index over all levels
-            int k = 0;
-            while (k + 1 < hl.n_levels && j >= first[k + 1]) ++k;
-            const size_t at = (size_t)hl.seg_off[k] + (j - first[k]);
-            flag_at = li * hl.total_cap + (uint32_t)at;
-            const double2 a = hl.a[at];
-            const double oz = hl.b[at].x;
-            const V3 over_point = mk(a.x, a.y, oz);
-            const Light& light = sc.lights[li];
-            const V3 to_light = mk(light.origin[0], light.origin[1], light.origin[2]) - over_point;
-            distance = magnitude(to_light);
-            sray.o = over_point;
-            sray.d = normalize(to_light);
-            brute = brute_all || near_cone_slope<FEAT>(sc, sray);
-            bool shadowed = false;
+        sray.o = over_point;
+        sray.d = normalize(to_light);
+        bool shadowed = true;
+        if (dot(sray.d, normal) >= 0.0) {
             if (ANYHIT) {
-                AnyVisitor<FEAT> v(sc, sray, distance, tally, lv.overflow);
-                if (visit_unbounded(sc, v)) shadowed = v.found;
-                else if (sc.n_bvh_items > 0) {
-                    Walk w;
-                    walk = brute || walk_setup(sc, sray, 0, w);
-                }
-            } else {
-                ClosestVisitor<FEAT> v(sc, sray, distance, tally, lv.overflow);
-                visit_unbounded(sc, v);
-                t0 = v.best.t;
-                prim0 = v.best.prim;
-                if (sc.n_bvh_items > 0) {
-                    Walk w;
-                    walk = brute || walk_setup(sc, sray, 0, w);
-                }
-                if (!walk) shadowed = prim0 >= 0 && (__ldg(&sc.prims[prim0].kind_flags) & 0x100) != 0;
+                shadowed = any_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
+            } else {  // some shape does not cast shadows: the nearest crossing decides (src/world.rs:43-47)
+                const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
+                shadowed = sh.prim >= 0 && (__ldg(&sc.prims[sh.prim].kind_flags) & 0x100) != 0;
             }
-            if (!walk) lv.shadow[flag_at] = shadowed ? 1 : 0;
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, walk);
-        if (m) {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(lv.sw_count, (unsigned long long)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (walk) {
-                const uint64_t slot = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
-                if (slot < lv.sw_capacity) {
-                    lv.sw0[slot] = make_double2(sray.o.x, sray.o.y);
-                    lv.sw1[slot] = make_double2(sray.o.z, sray.d.x);
-                    lv.sw2[slot] = make_double2(sray.d.y, sray.d.z);
-                    lv.sw3[slot] = make_double2(distance, __longlong_as_double((long long)((uint64_t)flag_at | (brute ? 1ull << 63 : 0ull))));
-                    if (!ANYHIT) lv.sw4[slot] = make_double2(t0, __longlong_as_double((long long)prim0));
-                } else *lv.overflow = 2;
-            }
-        }
+        } else skipped++;
+        lv.shadow[(size_t)li * hl.total_cap + at] = shadowed ? 1 : 0;
     }
-    if (FEAT & FEAT_TALLY) flush_tally(tally, lv.stats, lane);
-}
-
-// ---- kernel 3: World::is_shadowed, the BVH walks ------------------------------------------------------------------
-// Persistent warps over the shadow walker queue.  Every lane owns one query at a time (a resumable WalkCursor); the warp
-// alternates a node phase (each lane descends to its next leaf) and a leaf phase (the exact f64 item tests), and before
-// each round the lanes whose query has ended take the next rays of the queue.  The queue is claimed in chunks (one
-// atomic per RTC_WALK_CHUNK rays and warp), so a refill is a few loads and the fp32 walk setup — the uniform, expensive
-// part of a shadow ray (normalisation, always-tested primitives) was done at full width by shadow_setup.
-#ifndef RTC_WALK_CHUNK
-#define RTC_WALK_CHUNK 128
-#endif
-#ifndef RTC_WALK_REFILL_MIN  // refill once this many lanes are idle (or all of them)
-#define RTC_WALK_REFILL_MIN 4
-#endif
-template <int FEAT, bool ANYHIT>
-__global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_WALK_MIN_BLOCKS_CSG : RTC_WALK_MIN_BLOCKS) walk_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv) {
-    constexpr bool TALLY = (FEAT & FEAT_TALLY) != 0;
-    constexpr unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
-    const unsigned long long pushed = *lv.sw_count;
-    const uint32_t n_total = (uint32_t)(pushed < lv.sw_capacity ? pushed : lv.sw_capacity);
-    uint32_t next = 0, end = 0;  // this warp's chunk of the queue (warp-uniform)
-    bool exhausted = n_total == 0;
-    bool busy = false;
-    Ray ray;
-    ray.o = mk(0.0, 0.0, 0.0);
-    ray.d = mk(0.0, 0.0, 1.0);
-    uint32_t flag_at = 0;
-    Tally tally = {0u, 0u, 0u, 0u};
-    WalkCursor c;
-    c.link = WALK_DONE;
-    typename ShadowVisitor<FEAT, ANYHIT>::type v(sc, ray, 0.0, tally, lv.overflow);
-    for (;;) {
-        const unsigned idle = __ballot_sync(FULL, !busy);
-        if (idle != 0u && !exhausted && (idle == FULL || __popc(idle) >= RTC_WALK_REFILL_MIN)) {
-            if (next == end) {
-                uint32_t base = 0;
-                if (lane == 0) base = (uint32_t)atomicAdd(lv.sw_head, (unsigned long long)RTC_WALK_CHUNK);
-                base = __shfl_sync(FULL, base, 0);
-                if (base >= n_total) exhausted = true;
-                else { next = base; end = min(base + (uint32_t)RTC_WALK_CHUNK, n_total); }
-            }
-            if (!exhausted) {
-                const uint32_t avail = end - next;
-                const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
-                if (!busy && rank < avail) {
-                    const uint32_t i = next + rank;
-                    const double2 s0 = lv.sw0[i], s1 = lv.sw1[i], s2 = lv.sw2[i], s3 = lv.sw3[i];
-                    ray.o = mk(s0.x, s0.y, s1.x);
-                    ray.d = mk(s1.y, s2.x, s2.y);
-                    const uint64_t bits = (uint64_t)__double_as_longlong(s3.y);
-                    flag_at = (uint32_t)(bits & 0xffffffffu);
-                    if (ANYHIT) ShadowVisitor<FEAT, ANYHIT>::restart(v, s3.x, 0.0, -1);
-                    else {
-                        const double2 s4 = lv.sw4[i];
-                        ShadowVisitor<FEAT, ANYHIT>::restart(v, s3.x, s4.x, (int)__double_as_longlong(s4.y));
-                    }
-                    busy = walk_begin(sc, ray, 0, (bits >> 63) != 0, v.tmax(), c);
-                    if (!busy) lv.shadow[flag_at] = ShadowVisitor<FEAT, ANYHIT>::shadowed(sc, v) ? 1 : 0;
-                }
-                next += min(avail, (uint32_t)__popc(idle));
-            }
-        }
-        if (__ballot_sync(FULL, busy) == 0u) {
-            if (exhausted) break;
-            continue;
-        }
-        if (busy) walk_descend<TALLY>(sc, c, tally, nullptr, 0);
-        if (busy && (c.link == WALK_DONE || walk_leaf(sc, c, v))) {
-            lv.shadow[flag_at] = ShadowVisitor<FEAT, ANYHIT>::shadowed(sc, v) ? 1 : 0;
-            busy = false;
-        }
-    }
-    if (TALLY) flush_tally(tally, lv.stats, lane);
+    if (FEAT & FEAT_TALLY) flush_tally(tally, lv.stats, lane);
+    for (int off = 16; off; off >>= 1) skipped += __shfl_down_sync(0xffffffffu, skipped, off);
+    if (lane == 0 && skipped) atomicAdd(lv.stats + 8, (unsigned long long)skipped);
 }
 
 // ---- kernel 4: World::shade_hit for the hits of one level ---------------------------------------------------------
@@ -492,13 +442,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS 
         for (int i = threadIdx.x; i < 512; i += blockDim.x) s_perm[i] = c_perm[i];
         __syncthreads();
     }
-    const unsigned long long counted = hl.counts[lv.level];
-    const uint32_t seg = hl.seg_off[lv.level], seg_cap = hl.seg_cap[lv.level];
-    const uint32_t n_hits = (uint32_t)(counted < seg_cap ? counted : seg_cap);
+    uint32_t n_front, n_back;
+    level_bins(hl, lv.level, n_front, n_back);
+    const uint32_t n_hits = n_front + n_back;
     const int L = sc.n_lights;
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t h = blockIdx.x * blockDim.x + threadIdx.x; h < n_hits; h += stride) {
-        const size_t at = (size_t)seg + h;
+        const size_t at = level_hit_at(hl, lv.level, n_front, h);
         const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at], d = hl.d[at], e = hl.e[at], fr = hl.f[at];
         const uint64_t link = (uint64_t)__double_as_longlong(fr.x);
         const uint32_t bits = (uint32_t)(uint64_t)__double_as_longlong(fr.y);
@@ -536,7 +486,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, PLAIN ? RTC_SHADE_PLAIN_MIN_BLOCKS 
             const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
             const Rgb intensity = rgb(light.intensity[0], light.intensity[1], light.intensity[2]);
             const V3 lightv = normalize(lpos - over_point);
-            const bool shadowed = lv.shadow[(uint32_t)li * hl.total_cap + (uint32_t)at] != 0;
+            const bool shadowed = lv.shadow[(size_t)li * hl.total_cap + at] != 0;
             const Rgb effective = color * intensity;
             Rgb surface = effective * mat.ambient;
             const double light_dot_normal = dot(lightv, normal);
@@ -599,37 +549,21 @@ void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene
 }
 
 template <int TALLY>
-static void launch_shadow_setup_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+static void launch_shadow_tally(int feat, dim3 grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
     if (sc.all_cast_shadow) {
-        if (full) shadow_setup<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else shadow_setup<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     } else {
-        if (full) shadow_setup<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
-        else shadow_setup<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else trace_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     }
 }
-void launch_shadow_setup(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
+void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     if (sc.n_lights == 0) return;
-    if (feat & FEAT_TALLY) launch_shadow_setup_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv, hl);
-    else launch_shadow_setup_tally<0>(feat, grid, st, sc, f, lv, hl);
-}
-
-template <int TALLY>
-static void launch_walk_shadow_tally(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
-    if (sc.all_cast_shadow) {
-        if (full) walk_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-        else walk_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    } else {
-        if (full) walk_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-        else walk_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv);
-    }
-}
-void launch_walk_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv) {
-    if (sc.n_lights == 0 || sc.n_bvh_items == 0) return;
-    if (feat & FEAT_TALLY) launch_walk_shadow_tally<FEAT_TALLY>(feat, grid, st, sc, f, lv);
-    else launch_walk_shadow_tally<0>(feat, grid, st, sc, f, lv);
+    const dim3 g((unsigned)std::max(grid / sc.n_lights, 1), (unsigned)sc.n_lights);  // blockIdx.y = light
+    if (feat & FEAT_TALLY) launch_shadow_tally<FEAT_TALLY>(feat, g, st, sc, f, lv, hl);
+    else launch_shadow_tally<0>(feat, g, st, sc, f, lv, hl);
 }
 
 void launch_light(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hl) {

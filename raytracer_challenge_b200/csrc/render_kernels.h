@@ -22,12 +22,6 @@
 #ifndef RTC_SHADOW_MIN_BLOCKS_CSG
 #define RTC_SHADOW_MIN_BLOCKS_CSG 8
 #endif
-#ifndef RTC_WALK_MIN_BLOCKS  // persistent walk kernels: cursor + visitor + the f64 leaf tests
-#define RTC_WALK_MIN_BLOCKS 6
-#endif
-#ifndef RTC_WALK_MIN_BLOCKS_CSG
-#define RTC_WALK_MIN_BLOCKS_CSG 4
-#endif
 #ifndef RTC_SHADE_MIN_BLOCKS
 #define RTC_SHADE_MIN_BLOCKS 5
 #endif
@@ -49,11 +43,14 @@ struct FrameParams {
     int32_t spp_x, spp_y, spp;
     int32_t fuel;
     uint32_t flags;
-    int32_t pad;
+    int32_t two_bins;  // compact rays / hits that leave BVH items apart from those that leave always-tested primitives (render_kernels.cu)
 };
 
 // Hit list of one batch: structure-of-arrays of 16-byte chunks (a warp's accesses are whole 512-byte lines), one
-// segment per bounce level at a static offset.  Written by trace_spawn, read by shadow_setup (a, b) and light:
+// segment per bounce level at a static offset, each holding two bins that grow towards each other: hits on BVH items
+// from the segment's first slot upwards (counts), hits on always-tested primitives from its last slot downwards
+// (counts_back).  A segment is sized for "every ray of the level hits", so the bins cannot meet.
+// Written by trace_spawn, read by trace_shadow (a, b, c) and light:
 //     a = (over_point.x, over_point.y)   b = (over_point.z, normal.x)   c = (normal.y, normal.z)
 //     d = (eye.x, eye.y)                 e = (eye.z, reflectance)       f = (primitive | parent << 32, HIT_* bits)
 // parent: level 0 -> the sample of the batch; level k > 0 -> index of the parent's record in the whole list (its level's
@@ -67,7 +64,8 @@ constexpr uint32_t HIT_SPAWNED_REFLECTED = 2u, HIT_SPAWNED_REFRACTED = 4u;  // t
 struct HitList {
     double2 *a, *b, *c, *d, *e, *f;
     double* child_rgb;
-    const unsigned long long* counts;  // hits per level (device counters)
+    const unsigned long long* counts;       // hits per level, front bin (device counters)
+    const unsigned long long* counts_back;  // ... back bin
     uint32_t seg_off[MAX_LEVELS];      // first record of each level's segment
     uint32_t seg_cap[MAX_LEVELS];
     int32_t n_levels;
@@ -79,38 +77,31 @@ struct HitList {
 // One bounce level of one batch.
 //   ray queue (64 B per ray):  q0 = (origin.x, origin.y)  q1 = (origin.z, dir.x)  q2 = (dir.y, dir.z)
 //                              q3 = (parent record | fuel << 32 | child kind << 40, unused)
-//   shadow walkers (64 / 80 B): the shadow rays that have to walk the BVH (shadow_setup -> walk_shadow)
-//                              s0 = (origin.x, origin.y)  s1 = (origin.z, dir.x)  s2 = (dir.y, dir.z)
-//                              s3 = (distance to the light, flag index | brute-force bit 63)
-//                              s4 = (nearest crossing among the always-tested primitives: t, primitive) — only read by
-//                                   scenes with shapes that cast no shadow
+//   two bins like the hit list: children of hits on BVH items in slots 0, 1, ... (count), children of hits on
+//   always-tested primitives in slots capacity-1, capacity-2, ... (count_back)
 struct LevelParams {
     const double2 *in_q0, *in_q1, *in_q2, *in_q3;
     double2 *out_q0, *out_q1, *out_q2, *out_q3;
-    const unsigned long long* in_count;
-    unsigned long long* out_count;
+    const unsigned long long *in_count, *in_count_back;
+    unsigned long long *out_count, *out_count_back;
     uint64_t in_capacity, out_capacity;
     uint64_t first_sample;  // primary level: first sample ordinal of this batch
     uint64_t n_primary;     // primary level: samples in this batch
     int32_t level;
     int32_t pad;
-    unsigned long long* hit_count;  // this level's counter (= hits.counts + level)
+    unsigned long long *hit_count, *hit_count_back;  // this level's counters (= hits.counts + level, hits.counts_back + level)
     uint8_t* shadow;            // [light][hits.total_cap]: 1 = occluded
     double* accum;              // 3 doubles per sample of the batch: the colour of its primary ray
-    unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms, [7] most node visits of one closest-hit query
+    unsigned long long* stats;  // [0] active primary rays, [1] reflected pushed, [2] refracted pushed, [3..6] Tally: nodes, tris, prims, xforms,
+                                // [7] most node visits of one closest-hit query, [8] shadow queries answered without tracing (light behind the surface)
     int* overflow;
-    double2 *sw0, *sw1, *sw2, *sw3, *sw4;  // shadow walker queue
-    unsigned long long* sw_count;          // walkers pushed by shadow_setup
-    unsigned long long* sw_head;           // walkers claimed by walk_shadow
-    uint64_t sw_capacity;
 };
 
 void upload_perm(const uint8_t* perm512);
-// Per batch: trace_spawn once per level (a chain); then over every hit of the batch shadow_setup (uniform: one thread per
-// (hit, light)) and walk_shadow (persistent: the shadow rays that walk the BVH); then light per level, deepest first.
+// Per batch: trace_spawn once per level (a chain); then over every hit of the batch trace_shadow (one thread per
+// (hit, light)); then light per level, deepest first.
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
-void launch_shadow_setup(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
-void launch_walk_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv);
+void launch_shadow(int feat, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hits);
 void launch_light(int grid, cudaStream_t st, const Scene& sc, const LevelParams& lv, const HitList& hits);
 // Device-side LBVH build (bvh_build.cu): everything lives in the scene arena.
 struct LbvhArgs {

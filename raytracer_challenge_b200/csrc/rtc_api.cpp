@@ -46,7 +46,10 @@ const uint8_t kPerm[256] = {
 
 constexpr int MAX_PIPES = 8;
 constexpr int MAX_DEVICES = 64;
-constexpr int COUNTERS_PER_BATCH = 64;  // [0..15] queue counts per level, [16..31] hit counts per level, [32..39] stats, [40] shadow walkers pushed, [41] claimed
+// Device counters of one batch (unsigned long long each):
+constexpr int CNT_QUEUE = 0, CNT_HITS = 16, CNT_QUEUE_BACK = 32, CNT_HITS_BACK = 48;  // per level: queue / hit-list fill, front and back bins
+constexpr int CNT_STATS = 64;                                                           // LevelParams::stats
+constexpr int COUNTERS_PER_BATCH = 80;
 
 // Scratch of one pipeline (= one CUDA stream working through batches): ray queues (ping-pong), hit list, shadow
 // bytes, sample accumulators.
@@ -57,10 +60,9 @@ struct Pipe {
     double2* q[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
     double2* hit[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     double* child_rgb = nullptr;  // colours the children of a hit returned (HitList::child_rgb)
-    double2* sw[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // shadow walker queue (LevelParams::sw0..sw4)
     uint8_t* shadow = nullptr;
     double* accum = nullptr;
-    uint64_t q_capacity = 0, hit_capacity = 0, child_doubles = 0, sw_capacity = 0, shadow_bytes = 0, accum_samples = 0;
+    uint64_t q_capacity = 0, hit_capacity = 0, child_doubles = 0, shadow_bytes = 0, accum_samples = 0;
 };
 
 // Per-device render context: streams, events and scratch memory.  It outlives scenes, so that the drop-in call
@@ -93,11 +95,10 @@ void free_pipe(Pipe& p) {
     for (int a = 0; a < 2; ++a)
         for (int b = 0; b < 4; ++b) { cudaFree(p.q[a][b]); p.q[a][b] = nullptr; }
     for (auto& h : p.hit) { cudaFree(h); h = nullptr; }
-    for (auto& w : p.sw) { cudaFree(w); w = nullptr; }
     cudaFree(p.child_rgb); p.child_rgb = nullptr;
     cudaFree(p.shadow); p.shadow = nullptr;
     cudaFree(p.accum); p.accum = nullptr;
-    p.q_capacity = p.hit_capacity = p.child_doubles = p.sw_capacity = p.shadow_bytes = p.accum_samples = 0;
+    p.q_capacity = p.hit_capacity = p.child_doubles = p.shadow_bytes = p.accum_samples = 0;
 }
 
 int env_int(const char* name, int fallback, int lo, int hi);
@@ -531,7 +532,7 @@ int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out) {
     return rtc_scene_create_multi(desc, &device, 1, out);
 }
 
-static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t child_doubles, uint64_t sw_capacity, uint64_t shadow_bytes, uint64_t accum_samples) {
+static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint64_t child_doubles, uint64_t shadow_bytes, uint64_t accum_samples) {
     if (q_capacity > p.q_capacity) {
         for (int a = 0; a < 2; ++a)
             for (int c = 0; c < 4; ++c) {
@@ -552,12 +553,6 @@ static int ensure_pipe(Pipe& p, uint64_t q_capacity, uint64_t hit_capacity, uint
         cudaFree(p.child_rgb); p.child_rgb = nullptr; p.child_doubles = 0;
         CU(cudaMalloc((void**)&p.child_rgb, child_doubles * sizeof(double)));
         p.child_doubles = child_doubles;
-    }
-    if (sw_capacity > p.sw_capacity) {
-        for (auto& w : p.sw) { cudaFree(w); w = nullptr; }
-        p.sw_capacity = 0;
-        for (auto& w : p.sw) CU(cudaMalloc((void**)&w, sw_capacity * sizeof(double2)));
-        p.sw_capacity = sw_capacity;
     }
     if (shadow_bytes > p.shadow_bytes) {
         cudaFree(p.shadow); p.shadow = nullptr; p.shadow_bytes = 0;
@@ -616,6 +611,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     f.spp_x = o.spp_x; f.spp_y = o.spp_y; f.spp = o.spp_x * o.spp_y;
     f.fuel = o.fuel;
     f.flags = o.flags;
+    f.two_bins = (s->feat & rtcdev::FEAT_CSG) != 0;
 
     const uint64_t per_tile = (uint64_t)o.tile_w * o.tile_h;
     const uint64_t all_slots = (uint64_t)f.tiles_x * f.tiles_y * per_tile;  // padded pixel slots of the whole window
@@ -658,7 +654,6 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     if (hit_cap * (uint64_t)std::max(L, 1) >= 0xf0000000ull) return fail("rtc_render: batch too large");
     hits.total_cap = (uint32_t)hit_cap;
     hits.fan = fan;
-    const uint64_t sw_cap = hit_cap * (uint64_t)std::max(L, 1);  // worst case: every shadow ray walks the BVH
     // Batch schedule: (first pixel slot, slots).  Device-resident frames use equal batches.  When each finished batch is
     // copied to the host, the copy of the LAST batch cannot overlap any kernel, so the tail of the schedule is tapered
     // (..., B, B/2, B/4, B/4): the exposed copy shrinks from 1/6 to 1/24 of the frame (teapot 4K: 0.6 -> 0.15 ms).
@@ -685,7 +680,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
     const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
     for (int p = 0; p < n_pipes; ++p)
-        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)fan * 3, s->dev.n_bvh_items > 0 ? sw_cap : 1, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
+        if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)fan * 3, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
     if (n_out > ctx.out_pixels) {
         cudaFree(ctx.out); ctx.out = nullptr; ctx.out_pixels = 0;
         CU(cudaMalloc((void**)&ctx.out, std::max<uint64_t>(n_out, 1) * 3 * sizeof(double)));
@@ -711,7 +706,6 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     CU(cudaEventRecord(ctx.ev[0], st0));
     for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
-    const int grid_walk = ctx.sm_count * env_int("RTC_WALK_BLOCKS_PER_SM", 8, 1, 32);  // persistent: about what is resident
     const int feat = s->feat | (profile ? rtcdev::FEAT_TALLY : 0);  // the work tallies are counted under RTC_FLAG_PROFILE only
     uint64_t launches = 0;
     const bool timeline = std::getenv("RTC_TIMELINE") != nullptr;  // debugging aid: when each batch's kernels / copy finished
@@ -738,28 +732,28 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         CU(cudaMemsetAsync(p.accum, 0, npix * f.spp * 3 * sizeof(double), st));  // (padding slots of partial tiles are never written)
         hits.child_rgb = p.child_rgb;
         hits.a = p.hit[0]; hits.b = p.hit[1]; hits.c = p.hit[2]; hits.d = p.hit[3]; hits.e = p.hit[4]; hits.f = p.hit[5];
-        hits.counts = cnt + 16;
+        hits.counts = cnt + CNT_HITS;
+        hits.counts_back = cnt + CNT_HITS_BACK;
         auto level_params = [&](int level) {
             rtcdev::LevelParams lv{};
             const int in = level & 1, outq = in ^ 1;
             lv.in_q0 = p.q[in][0]; lv.in_q1 = p.q[in][1]; lv.in_q2 = p.q[in][2]; lv.in_q3 = p.q[in][3];
             lv.out_q0 = p.q[outq][0]; lv.out_q1 = p.q[outq][1]; lv.out_q2 = p.q[outq][2]; lv.out_q3 = p.q[outq][3];
-            lv.in_count = cnt + level;
-            lv.out_count = cnt + level + 1;
+            lv.in_count = cnt + CNT_QUEUE + level;
+            lv.in_count_back = cnt + CNT_QUEUE_BACK + level;
+            lv.out_count = cnt + CNT_QUEUE + level + 1;
+            lv.out_count_back = cnt + CNT_QUEUE_BACK + level + 1;
             lv.in_capacity = p.q_capacity;
             lv.out_capacity = p.q_capacity;
             lv.first_sample = first * f.spp;
             lv.n_primary = npix * f.spp;
             lv.level = level;
-            lv.hit_count = cnt + 16 + level;
+            lv.hit_count = cnt + CNT_HITS + level;
+            lv.hit_count_back = cnt + CNT_HITS_BACK + level;
             lv.shadow = p.shadow;
             lv.accum = p.accum;
-            lv.stats = cnt + 32;
+            lv.stats = cnt + CNT_STATS;
             lv.overflow = ctx.overflow;
-            lv.sw0 = p.sw[0]; lv.sw1 = p.sw[1]; lv.sw2 = p.sw[2]; lv.sw3 = p.sw[3]; lv.sw4 = p.sw[4];
-            lv.sw_count = cnt + 40;
-            lv.sw_head = cnt + 41;
-            lv.sw_capacity = p.sw_capacity;
             return lv;
         };
         const int grid0 = (int)std::min<uint64_t>((uint64_t)grid_full, (npix * f.spp + RTC_BLOCK - 1) / RTC_BLOCK);
@@ -767,13 +761,12 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         for (int level = 0; level <= o.fuel; ++level)  // the chain: level k+1 depends on level k only
             rtcdev::launch_trace(feat, level == 0, level == 0 ? grid0 : grid_full, st, s->dev, f, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(0); }
-        rtcdev::launch_shadow_setup(feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
-        rtcdev::launch_walk_shadow(feat, grid_walk, st, s->dev, f, level_params(0));        // ... and the ones that walk the BVH
+        rtcdev::launch_shadow(feat, grid_full, st, s->dev, f, level_params(0), hits);  // every (hit, light) of the batch
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(1); }
         for (int level = o.fuel; level >= 0; --level)  // deepest first: a hit is lit when its children's colours are final
             rtcdev::launch_light(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
-        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0) + (L > 0 && s->dev.n_bvh_items > 0 ? 1 : 0);
+        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0);
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
         launches++;
         if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, st)); tl_events.push_back(e); }
@@ -856,19 +849,21 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         // R_ref: the reference re-traces every secondary sub-tree once per light, so a ray at
         // bounce level k exists L^k times there, and each of its hits issues L shadow queries.
         double mult = 1.0;
-        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0, hits_all = 0, tally[4] = {0, 0, 0, 0}, longest = 0;
+        uint64_t primary = 0, shadow = 0, refl = 0, refr = 0, hits_all = 0, tally[4] = {0, 0, 0, 0}, longest = 0, skipped = 0;
         double ref = 0.0;
         for (uint64_t b = 0; b < n_batches; ++b) {
             const unsigned long long* c = ctx.counters_host + b * COUNTERS_PER_BATCH;
-            primary += c[32];
-            if (s->feat & rtcdev::FEAT_TRANSPARENT) { refl += c[33]; refr += c[34]; }
-            else for (int level = 1; level <= o.fuel; ++level) refl += std::min<uint64_t>(c[level], q_cap);  // every child is a reflection
-            for (int k = 0; k < 4; ++k) tally[k] += c[35 + k];
-            longest = std::max<uint64_t>(longest, c[39]);
+            auto level_rays = [&](int level) { return std::min<uint64_t>(c[CNT_QUEUE + level] + c[CNT_QUEUE_BACK + level], q_cap); };
+            primary += c[CNT_STATS];
+            if (s->feat & rtcdev::FEAT_TRANSPARENT) { refl += c[CNT_STATS + 1]; refr += c[CNT_STATS + 2]; }
+            else for (int level = 1; level <= o.fuel; ++level) refl += level_rays(level);  // every child is a reflection
+            for (int k = 0; k < 4; ++k) tally[k] += c[CNT_STATS + 3 + k];
+            longest = std::max<uint64_t>(longest, c[CNT_STATS + 7]);
+            skipped += c[CNT_STATS + 8];
             mult = 1.0;
             for (int level = 0; level <= o.fuel; ++level) {
-                const uint64_t n_in = level == 0 ? c[32] : std::min<uint64_t>(c[level], q_cap);
-                const uint64_t hits = c[16 + level];
+                const uint64_t n_in = level == 0 ? c[CNT_STATS] : level_rays(level);
+                const uint64_t hits = c[CNT_HITS + level] + c[CNT_HITS_BACK + level];
                 shadow += hits * (uint64_t)L;
                 hits_all += hits;
                 ref += mult * ((double)n_in + (double)hits * L);
@@ -891,6 +886,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         stats->primitive_tests = tally[2];
         stats->ray_transforms = tally[3];
         stats->max_node_visits = longest;
+        stats->shadow_queries_culled = skipped;
         for (size_t k = 1; k < n_prof; ++k) {
             float t = 0.f;
             if (prof_class[k] < 0 || cudaEventElapsedTime(&t, ctx.prof_events[k - 1], ctx.prof_events[k]) != cudaSuccess) continue;

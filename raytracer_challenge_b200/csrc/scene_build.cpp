@@ -635,6 +635,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                 } else if (prim_box[(size_t)ch].bounded) {
                     item_boxes.push_back(prim_box[(size_t)ch]);
                     item_ids.push_back(ch);
+                    out.prims[(size_t)ch].kind_flags |= rtcdev::PRIM_IN_BVH;
                 } else {
                     out.unbounded.push_back(ch);
                 }
@@ -656,6 +657,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                 if (sub.bounded && !sub.empty()) {
                     item_boxes.push_back(sub);
                     item_ids.push_back(~my_root);
+                    for (int q = pb; q < pe; ++q) out.prims[(size_t)q].kind_flags |= rtcdev::PRIM_IN_BVH;
                 } else if (pe > pb) {
                     out.unbounded.push_back(~my_root);
                 }

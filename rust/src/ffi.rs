@@ -146,6 +146,7 @@ pub struct rtc_stats {
     pub ms_shadow: f64,
     pub ms_shade: f64,
     pub max_node_visits: u64,
+    pub shadow_queries_culled: u64,
 }
 
 #[repr(C)]

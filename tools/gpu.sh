@@ -41,14 +41,15 @@ PY
         python bench.py --steps 2 --warmup 1 --no-cpu "$@" > gpurun_out/ncu_launches_$TAG.log 2>&1
     echo "launches $TAG rc=$?"; wc -l gpurun_out/launches_$TAG.csv ;;
   ncu)
-    TAG=$1; CASE=$2; SKIP=$3; COUNT=$4; RX=${5:-trace_|shade}
+    TAG=$1; CASE=$2; SKIP=$3; COUNT=$4; RX=${5:-trace_|shadow|light}
     python tools/perf_probe.py --frames 2 $CASE > gpurun_out/plain_$TAG.log 2>&1 &&
     ncu --set full --clock-control none --import-source on -k regex:"$RX" -s $SKIP -c $COUNT -o gpurun_out/prof_$TAG \
         python tools/perf_probe.py --frames 2 $CASE > gpurun_out/ncu_full_$TAG.log 2>&1
     echo "ncu $TAG rc=$?"; cut -c1-300 gpurun_out/plain_$TAG.log
     python tools/ncu_summary.py gpurun_out/prof_$TAG.ncu-rep gpurun_out/ncu_summary_$TAG.csv
     ncu -i gpurun_out/prof_$TAG.ncu-rep --page source --csv 2>/dev/null | gzip > gpurun_out/ncu_source_$TAG.csv.gz
-    if [ $(stat -c %s gpurun_out/prof_$TAG.ncu-rep) -gt 24000000 ]; then rm gpurun_out/prof_$TAG.ncu-rep; fi
+    ncu -i gpurun_out/prof_$TAG.ncu-rep --page source --print-source cuda --csv 2>/dev/null | gzip > gpurun_out/ncu_cuda_$TAG.csv.gz
+    if [ $(stat -c %s gpurun_out/prof_$TAG.ncu-rep) -gt 40000000 ]; then rm gpurun_out/prof_$TAG.ncu-rep; fi
     ls -la gpurun_out/ | grep $TAG ;;
   multi)
     TAG=$1; N=$2; shift 2
