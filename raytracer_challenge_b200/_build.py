@@ -22,6 +22,17 @@ DEVICE_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-Xcompiler", "
 HOST_FLAGS = ["-std=c++17", "-O2", "-Xcompiler", "-fPIC,-Wall", "-Wno-deprecated-gpu-targets"] + ARCH
 
 
+def read_units():
+    """(file, kind) pairs of csrc/UNITS — the one list of translation units, shared with rust/build.rs."""
+    units = []
+    with open(os.path.join(CSRC, "UNITS")) as f:
+        for line in f:
+            line = line.split("#")[0].split()
+            if len(line) == 2:
+                units.append((line[0], line[1]))
+    return units
+
+
 def _newer(target, sources):
     if not os.path.exists(target):
         return True
@@ -42,9 +53,9 @@ def build_rtc(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".hpp", ".cuh"))]
     headers.append(os.path.join(ROOT, "include", "rtc.h"))
-    units = [("render_kernels.cu", DEVICE_FLAGS + (["-Xptxas", "-v"] if verbose else [])), ("bvh_build.cu", ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH),
-             ("rtc_api.cpp", HOST_FLAGS), ("scene_build.cpp", HOST_FLAGS),
-             ("microbench.cu", ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH)]
+    cuda_flags = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Wno-deprecated-gpu-targets"] + ARCH
+    flags_of = {"device": DEVICE_FLAGS + (["-Xptxas", "-v"] if verbose else []), "cuda": cuda_flags, "host": HOST_FLAGS}
+    units = [(name, flags_of[kind]) for name, kind in read_units()]
     objs = []
     log = ""
     for name, flags in units:

@@ -5,7 +5,10 @@
 //
 //   morton_keys     item -> 30-bit Morton code of its box centre inside the root box; key = code << 32 | item index
 //                   (unique keys: no duplicate handling in the hierarchy)
-//   sort_keys       one block, bitonic sort of <= 8 192 keys in shared memory
+//   sort_keys       up to 8 192 keys: one block, bitonic sort in shared memory;
+//   radix_*         more: a stable least-significant-digit radix sort over the 30-bit codes, 4 bits per pass: per pass a
+//                   per-tile digit histogram (ballot + popc per digit), an exclusive scan over (digit, tile) and a stable
+//                   scatter — "stable" makes the result equal to sorting the unique keys code << 32 | item
 //   build_hierarchy Karras 2012: internal node i covers a range of sorted keys found by binary searches on the common
 //                   prefix length; children / parents / ranges written in one pass
 //   fit_boxes       bottom-up: each leaf walks towards the root, the second arrival at a node (atomic counter) unites
@@ -67,6 +70,92 @@ __global__ void __launch_bounds__(1024) sort_keys(LbvhArgs a, int np2) {
         }
     __syncthreads();
     for (int i = threadIdx.x; i < a.n; i += blockDim.x) a.keys[i] = sk[i];
+}
+
+// ---- multi-block radix sort (n > LBVH_ONE_BLOCK_ITEMS) --------------------------------------------------------
+// Keys are sorted by their 30-bit Morton code with a STABLE sort; the items start in index order, so ties end up in
+// index order = the order of the unique 64-bit keys.  One tile = 256 consecutive keys = one block; a pass handles one
+// 4-bit digit:
+//   radix_count    hist[digit * tiles + tile] = keys of the tile with that digit
+//   radix_scan     exclusive scan of hist in (digit, tile) order: where each tile's keys of each digit start
+//   radix_scatter  every key moves to offset[digit][tile] + (its rank among the tile's keys of that digit, in tile order)
+constexpr int RADIX_TILE = 256, RADIX_BITS = 4, RADIX_BINS = 1 << RADIX_BITS;
+
+// per-thread digit -> (rank of this key among the tile's keys with the same digit that precede it, tile count per digit)
+__device__ __forceinline__ void radix_rank(uint32_t digit, bool valid, uint32_t* s_warp /*[8][16]*/, uint32_t& rank, uint32_t& before_me_warps) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t my_rank = 0;
+#pragma unroll
+    for (int b = 0; b < RADIX_BINS; ++b) {
+        const unsigned m = __ballot_sync(0xffffffffu, valid && digit == (uint32_t)b);
+        if (lane == 0) s_warp[warp * RADIX_BINS + b] = __popc(m);
+        if (valid && digit == (uint32_t)b) my_rank = __popc(m & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    uint32_t before = 0;
+    for (unsigned w = 0; w < warp; ++w) before += s_warp[w * RADIX_BINS + (valid ? digit : 0)];
+    rank = my_rank;
+    before_me_warps = before;
+}
+
+__global__ void __launch_bounds__(RADIX_TILE) radix_count(const unsigned long long* __restrict__ keys, int n, int shift, int tiles, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t s_warp[(RADIX_TILE / 32) * RADIX_BINS];
+    const int i = blockIdx.x * RADIX_TILE + threadIdx.x;
+    const bool valid = i < n;
+    const uint32_t digit = valid ? (uint32_t)(keys[i] >> shift) & (RADIX_BINS - 1) : 0u;
+    uint32_t rank, before;
+    radix_rank(digit, valid, s_warp, rank, before);
+    if (threadIdx.x < RADIX_BINS) {
+        uint32_t total = 0;
+        for (int w = 0; w < RADIX_TILE / 32; ++w) total += s_warp[w * RADIX_BINS + threadIdx.x];
+        hist[threadIdx.x * tiles + blockIdx.x] = total;
+    }
+}
+
+// One block: exclusive scan of `count` values in place, 1 024 per step.
+__global__ void __launch_bounds__(1024) radix_scan(uint32_t* __restrict__ v, int count) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_base;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    for (int tile = 0; tile < count; tile += 1024) {
+        const int i = tile + (int)threadIdx.x;
+        const uint32_t x = i < count ? v[i] : 0u;
+        uint32_t incl = x;
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, incl, off);
+            if ((int)lane >= off) incl += u;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = s_warp[lane];
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, w, off);
+                if ((int)lane >= off) w += u;
+            }
+            s_warp[lane] = w;  // inclusive over warps
+        }
+        __syncthreads();
+        const uint32_t base = s_base + (warp ? s_warp[warp - 1] : 0u);
+        if (i < count) v[i] = base + incl - x;
+        __syncthreads();
+        if (threadIdx.x == 0) s_base += s_warp[31];
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(RADIX_TILE) radix_scatter(const unsigned long long* __restrict__ in, unsigned long long* __restrict__ out, int n, int shift, int tiles,
+                                                            const uint32_t* __restrict__ offset) {
+    __shared__ uint32_t s_warp[(RADIX_TILE / 32) * RADIX_BINS];
+    const int i = blockIdx.x * RADIX_TILE + threadIdx.x;
+    const bool valid = i < n;
+    const unsigned long long key = valid ? in[i] : 0ull;
+    const uint32_t digit = valid ? (uint32_t)(key >> shift) & (RADIX_BINS - 1) : 0u;
+    uint32_t rank, before;
+    radix_rank(digit, valid, s_warp, rank, before);
+    if (valid) out[offset[digit * tiles + blockIdx.x] + before + rank] = key;
 }
 
 // length of the common prefix of keys i and j; -1 outside the array (Karras 2012, section 3)
@@ -251,18 +340,31 @@ __global__ void permute_items(LbvhArgs a) {
 // bound of the collapsed tree's), [2] node count.  Returns a CUDA error code.
 int build_lbvh(const LbvhArgs& a, cudaStream_t st) {
     if (a.n < 8 || a.n > LBVH_MAX_ITEMS) return (int)cudaErrorInvalidValue;
-    int np2 = 1;
-    while (np2 < a.n) np2 <<= 1;
-    const size_t smem = (size_t)np2 * sizeof(unsigned long long);
-    // (per device and cheap: set on every build rather than tracking which devices have seen it)
-    if (smem > 48u * 1024u &&
-        cudaFuncSetAttribute(sort_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, LBVH_MAX_ITEMS * (int)sizeof(unsigned long long)) != cudaSuccess)
-        return (int)cudaGetLastError();
     cudaMemsetAsync(a.counter, 0, sizeof(int) * (size_t)a.n, st);
     cudaMemsetAsync(a.result, 0, sizeof(int) * 4, st);
     const int block = 128, grid = (a.n + block - 1) / block;
     morton_keys<<<grid, block, 0, st>>>(a);
-    sort_keys<<<1, 1024, smem, st>>>(a, np2);
+    if (a.n <= LBVH_ONE_BLOCK_ITEMS) {
+        int np2 = 1;
+        while (np2 < a.n) np2 <<= 1;
+        const size_t smem = (size_t)np2 * sizeof(unsigned long long);
+        // (per device and cheap: set on every build rather than tracking which devices have seen it)
+        if (smem > 48u * 1024u &&
+            cudaFuncSetAttribute(sort_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, LBVH_ONE_BLOCK_ITEMS * (int)sizeof(unsigned long long)) != cudaSuccess)
+            return (int)cudaGetLastError();
+        sort_keys<<<1, 1024, smem, st>>>(a, np2);
+    } else {
+        // 30-bit codes sit in bits 32..61 of the keys: 8 passes of 4 bits, ping-pong between keys and keys_alt (even count: ends in keys)
+        const int tiles = (a.n + RADIX_TILE - 1) / RADIX_TILE;
+        unsigned long long *src = a.keys, *dst = a.keys_alt;
+        for (int shift = 32; shift < 62; shift += RADIX_BITS) {
+            radix_count<<<tiles, RADIX_TILE, 0, st>>>(src, a.n, shift, tiles, a.radix_hist);
+            radix_scan<<<1, 1024, 0, st>>>(a.radix_hist, RADIX_BINS * tiles);
+            radix_scatter<<<tiles, RADIX_TILE, 0, st>>>(src, dst, a.n, shift, tiles, a.radix_hist);
+            unsigned long long* t = src; src = dst; dst = t;
+        }
+        static_assert(((62 - 32 + RADIX_BITS - 1) / RADIX_BITS) % 2 == 0, "an even number of passes leaves the sorted keys in a.keys");
+    }
     build_hierarchy<<<grid, block, 0, st>>>(a);
     fit_boxes<<<grid, block, 0, st>>>(a);
     number_nodes<<<1, 1024, 0, st>>>(a);

@@ -6,13 +6,15 @@
 namespace rtcdev {
 
 constexpr int MAX_LIGHTS = 16;
+constexpr int MAX_GATES = 64;           // group boxes that must be evaluated exactly per ray (one bit each in Prim::gate_mask / gate_mask_hi)
 constexpr int MAX_PATTERN_FRAMES = 8;   // nesting of Blend/Gradient/RingGradient/ColorJitter along one path
 constexpr int MAX_CSG_LIST = 48;        // crossings held while evaluating one top-level CSG item
 constexpr int MAX_CSG_MARKS = 8;        // CSG nesting depth
 constexpr int MAX_CROSSINGS = 64;       // crossings (t <= t_hit) replayed for n1/n2 (src/intersection.rs:70-103)
 constexpr int MAX_CONTAINERS = 24;      // simultaneously open shapes during that replay
-constexpr int BVH_STACK = 48;
-constexpr int LBVH_MAX_ITEMS = 8192;    // device-side build (bvh_build.cu): one-block shared-memory sort
+constexpr int BVH_STACK = 64;           // a radix tree over unique 62-bit keys (30-bit Morton code, 32-bit item) is at most 62 deep
+constexpr int LBVH_ONE_BLOCK_ITEMS = 8192;  // device-side build (bvh_build.cu): up to here one block sorts the keys in shared memory
+constexpr int LBVH_MAX_ITEMS = 1 << 22;     // ... beyond, a multi-block radix sort (4 M items: scratch ~100 B per item)
 constexpr int LBVH_MIN_ITEMS = 64;      // below this the host build costs microseconds
 
 // Kernel feature bits (compile-time variants of the wavefront kernel)
@@ -41,8 +43,9 @@ struct Prim {
     int32_t xform;
     int32_t matinv;
     int32_t geom;        // triangles: slot in tri_pe / tri_n; cylinder / cone: slot in ranges
-    uint32_t gate_mask;  // non-trivial ancestor group boxes that must pass (src/shape.rs:251)
-    int32_t pad0, pad1;
+    int32_t pad1;
+    uint32_t gate_mask;     // non-trivial ancestor group boxes that must pass (src/shape.rs:251): gates 0..31 ... (8-byte aligned pair)
+    uint32_t gate_mask_hi;  // ... and gates 32..63
 };  // 32 B
 
 struct Material {

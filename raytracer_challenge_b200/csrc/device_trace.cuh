@@ -32,7 +32,7 @@ __device__ __forceinline__ Prim load_prim(const Scene& sc, int id) {
     const int4 a = __ldg(q), b = __ldg(q + 1);
     Prim p;
     p.kind_flags = a.x; p.material = a.y; p.xform = a.z; p.matinv = a.w;
-    p.geom = b.x; p.gate_mask = (uint32_t)b.y; p.pad0 = 0; p.pad1 = 0;
+    p.geom = b.x; p.pad1 = 0; p.gate_mask = (uint32_t)b.z; p.gate_mask_hi = (uint32_t)b.w;
     return p;
 }
 __device__ __forceinline__ LeafItem load_leaf(const Scene& sc, int slot) {
@@ -49,13 +49,14 @@ __device__ __forceinline__ bool allows_intersection(int kind, bool left_hit, boo
 }
 
 template <int FEAT>
-__device__ __forceinline__ uint32_t gates_passed(const Scene& sc, const Ray& ray) {
-    uint32_t m = 0;
+__device__ __forceinline__ uint64_t gates_passed(const Scene& sc, const Ray& ray) {
+    uint64_t m = 0;
     if (FEAT & FEAT_GATES)
         for (int g = 0; g < sc.n_gates; ++g)
-            if (box_gate(sc.gates[g], ray)) m |= 1u << g;
+            if (box_gate(sc.gates[g], ray)) m |= 1ull << g;
     return m;
 }
+__device__ __forceinline__ uint64_t prim_gates(const Prim& p) { return (uint64_t)p.gate_mask_hi << 32 | p.gate_mask; }
 
 // Finite cones are BVH items under finite boxes; the one crossing such a box may not hold belongs to the cone's
 // single-root branch, taken iff |a| < EPSILON with a = dx^2 - dy^2 + dz^2 of the OBJECT-space direction
@@ -85,7 +86,7 @@ template <int FEAT>
 struct Query {
     const Scene& sc;
     const Ray& ray;
-    uint32_t passed;
+    uint64_t passed;
     ObjRay cache;
     Tally& tally;
     Tally scratch;  // FEAT_TALLY off: the increments land here, are never read, and the compiler drops them
@@ -96,7 +97,7 @@ struct Query {
         cache.xform = -1;
     }
     // copy of a query for an out-of-line evaluation: the gates are already known
-    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg, uint32_t passed_gates)
+    __device__ __forceinline__ Query(const Scene& s, const Ray& r, Tally& tl, int* ovf, bool skip_neg, uint64_t passed_gates)
         : sc(s), ray(r), passed(passed_gates), tally(tl), scratch{0u, 0u, 0u, 0u}, overflow(ovf), skip_negative(skip_neg) {
         cache.xform = -1;
     }
@@ -109,13 +110,14 @@ struct Query {
     __device__ __forceinline__ Tally& counters() { return kTally ? tally : scratch; }
     __device__ __forceinline__ bool gate_ok(int prim_id) const {
         if (!(FEAT & FEAT_GATES)) return true;
-        return (__ldg(&sc.prims[prim_id].gate_mask) & ~passed) == 0u;
+        const uint2 m = __ldg(reinterpret_cast<const uint2*>(&sc.prims[prim_id].gate_mask));
+        return (((uint64_t)m.y << 32 | m.x) & ~passed) == 0ull;
     }
     // crossings of primitive `id` (by index: unbounded list, CSG programs, brute force)
     __device__ __forceinline__ void roots_of_prim(int id, Roots& r) {
         r.n = 0;
         const Prim p = load_prim(sc, id);
-        if ((FEAT & FEAT_GATES) && (p.gate_mask & ~passed) != 0u) return;
+        if ((FEAT & FEAT_GATES) && (prim_gates(p) & ~passed) != 0ull) return;
         prim_roots<0x02>(sc, p, ray, cache, counters(), skip_negative, r);  // planes are the usual always-tested primitive
     }
     // crossing of a plane of the always-tested list held in the kernel parameters (ungated by construction)
@@ -173,7 +175,7 @@ __device__ __forceinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cro
 // device_math.cuh: a pointer into the caller's state handed to a real call would pin that state in local memory).
 struct CsgCall {
     Ray ray;
-    uint32_t passed;
+    uint64_t passed;
     int skip_negative;
     Tally tally;
     int n;  // surviving crossings in `list`, sorted by t; -1 = overflow

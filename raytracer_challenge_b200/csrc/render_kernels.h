@@ -115,6 +115,8 @@ struct LbvhArgs {
     double* leaf_tri;           // out: leaf order
     BvhNode* bvh;               // out: n - 1 slots
     unsigned long long* keys;   // n
+    unsigned long long* keys_alt;  // n > LBVH_ONE_BLOCK_ITEMS: the radix sort's second buffer
+    uint32_t* radix_hist;          // ... and its (digit, tile) histogram: 16 * ceil(n / 256)
     int2* child;                // n - 1
     int* parent;                // 2 n
     int2* range;                // n - 1

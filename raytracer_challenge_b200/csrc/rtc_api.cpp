@@ -305,7 +305,7 @@ struct PackedScene {
         o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots, o_guards;
     // device-side BVH build only (HostScene::device_build): staging + scratch sections
     size_t upload_bytes = 0, total_bytes = 0;  // host -> device copy / arena size
-    size_t o_item_ids = 0, o_box32 = 0, o_keys = 0, o_child = 0, o_parent = 0, o_range = 0, o_nbox = 0, o_counter = 0, o_dense = 0, o_result = 0;
+    size_t o_item_ids = 0, o_box32 = 0, o_keys = 0, o_keys_alt = 0, o_radix_hist = 0, o_child = 0, o_parent = 0, o_range = 0, o_nbox = 0, o_counter = 0, o_dense = 0, o_result = 0;
 };
 static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     auto place = [&](const void* src, size_t bytes) -> size_t {
@@ -343,6 +343,10 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
         p.o_leaf_items = reserve(n * sizeof(rtcdev::LeafItem));
         p.o_leaf_tri = reserve(n * 80);
         p.o_keys = reserve(n * 8);
+        if (n > (size_t)rtcdev::LBVH_ONE_BLOCK_ITEMS) {
+            p.o_keys_alt = reserve(n * 8);
+            p.o_radix_hist = reserve(16 * ((n + 255) / 256) * 4);
+        }
         p.o_child = reserve(n * 8);
         p.o_parent = reserve(2 * n * 4);
         p.o_range = reserve(n * 8);
@@ -424,6 +428,8 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
         a.leaf_tri = (double*)(base + p.o_leaf_tri);
         a.bvh = (rtcdev::BvhNode*)(base + p.o_bvh);
         a.keys = (unsigned long long*)(base + p.o_keys);
+        a.keys_alt = (unsigned long long*)(base + p.o_keys_alt);
+        a.radix_hist = (uint32_t*)(base + p.o_radix_hist);
         a.child = (int2*)(base + p.o_child);
         a.parent = (int*)(base + p.o_parent);
         a.range = (int2*)(base + p.o_range);
@@ -462,7 +468,7 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     std::memset(d.fast_planes, 0, sizeof d.fast_planes);
     if (!h.unbounded.empty() && h.unbounded.size() <= (size_t)rtcdev::MAX_FAST_PLANES && !std::getenv("RTC_NO_FAST_PLANES")) {
         bool ok = true;
-        for (int32_t id : h.unbounded) ok = ok && id >= 0 && (h.prims[id].kind_flags & 0xff) == RTC_PLANE && h.prims[id].gate_mask == 0u;
+        for (int32_t id : h.unbounded) ok = ok && id >= 0 && (h.prims[id].kind_flags & 0xff) == RTC_PLANE && h.prims[id].gate_mask == 0u && h.prims[id].gate_mask_hi == 0u;
         if (ok) {
             for (int32_t id : h.unbounded) {
                 rtcdev::FastPlane& fp = d.fast_planes[d.n_fast_planes++];

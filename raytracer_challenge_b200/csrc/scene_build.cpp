@@ -567,6 +567,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
     // csg_root: index into out.csg_roots of the enclosing top-level CSG item, or -1.
     walk = [&](int ni, uint32_t mask, int csg_root, int csg_depth, int& pb, int& pe) -> Box {
         Box sub;
+        (void)mask;
         pb = next_prim;
         pe = next_prim;
         if (!err.empty()) return sub;
@@ -579,30 +580,21 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         if (is_csg && nd.n_children != 2) { err = "CSG group needs exactly two children (src/shape.rs:80-83)"; return sub; }
         if (ni == 0 && is_csg) { err = "the root node must be an aggregation"; return sub; }
 
-        // gate of this group (the virtual root has none: src/world.rs:21-23)
-        int gate_slot = -1;
+        // Gate of this group (the virtual root has none: src/world.rs:21-23).  Whether the box must be evaluated per ray
+        // is only known once the subtree's bounds are: the slot is assigned AFTER the walk (below), so boxes that turn
+        // out to be conservative, and boxes that can never fail, cost no slot.
+        bool gate_candidate = false;
         if (ni != 0) {
             int constraining = 0;
-            bool finite6 = true;
             for (int k = 0; k < 3; ++k) {
                 const double lo = nd.bbox_min[k], hi = nd.bbox_max[k];
                 if (lo != lo || hi != hi) { err = "group box holds NaN"; return sub; }
                 const bool free_axis = (lo == -INF && hi == INF) || (lo == INF && hi == -INF);
                 if (!free_axis) constraining++;
-                if (!std::isfinite(lo) || !std::isfinite(hi)) finite6 = false;
             }
-            if (constraining <= 1) {
-                out.n_gates_always_pass++;  // the slab test cannot fail ("group boxes")
-            } else {
-                gate_slot = (int)out.gates.size();  // provisional: dropped again below if provably conservative
-                rtcdev::Gate g{};
-                for (int k = 0; k < 3; ++k) { g.lo[k] = nd.bbox_min[k]; g.hi[k] = nd.bbox_max[k]; }
-                out.gates.push_back(g);
-                (void)finite6;
-            }
+            if (constraining <= 1) out.n_gates_always_pass++;  // the slab test cannot fail ("group boxes")
+            else gate_candidate = true;
         }
-        const uint32_t child_mask = gate_slot >= 0 && gate_slot < 32 ? (mask | (1u << gate_slot)) : mask;
-        if (gate_slot >= 32) { err = "more than 32 group boxes need exact evaluation"; return sub; }
 
         int my_root = csg_root;
         int my_depth = csg_depth;
@@ -628,7 +620,6 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                 visited_prim[(size_t)ch] = 1;
                 next_prim++;
                 ce = next_prim;
-                out.prims[(size_t)ch].gate_mask = child_mask;
                 sub.add(prim_box[(size_t)ch]);
                 if (my_root >= 0) {
                     out.csg_ops.push_back({rtcdev::OP_PRIM, ch, 0, 0});
@@ -640,7 +631,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                     out.unbounded.push_back(ch);
                 }
             } else {
-                Box b = walk(~ch, child_mask, my_root, my_depth, cb, ce);
+                Box b = walk(~ch, 0u, my_root, my_depth, cb, ce);
                 if (!err.empty()) return sub;
                 sub.add(b);
             }
@@ -663,8 +654,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                 }
             }
         }
-        // a finite box that encloses everything below it can only reject rays that miss all of it: skip it
-        if (gate_slot >= 0) {
+        // a finite box that encloses everything below it can only reject rays that miss all of it: no gate needed
+        if (gate_candidate) {
             bool conservative = sub.bounded && sub.exact;  // (a finite cone's single-root crossing may lie outside its box)
             for (int k = 0; k < 3 && conservative; ++k) {
                 const double lo = nd.bbox_min[k], hi = nd.bbox_max[k];
@@ -673,16 +664,18 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
                 const double tol = 4e-9 * std::max({1.0, std::fabs(sub.lo[k]), std::fabs(sub.hi[k])});
                 if (lo > sub.lo[k] + tol || hi < sub.hi[k] - tol) conservative = false;
             }
-            if (conservative && gate_slot == (int)out.gates.size() - 1) {
-                // no deeper gate took a later slot: release this one
-                out.gates.pop_back();
-                for (int p = pb; p < pe; ++p) out.prims[(size_t)p].gate_mask &= ~(1u << gate_slot);
-                out.n_gates_conservative++;
-            } else if (conservative) {
-                for (int p = pb; p < pe; ++p) out.prims[(size_t)p].gate_mask &= ~(1u << gate_slot);
-                // slot stays allocated but unused by any primitive; harmless
+            if (conservative || pe == pb) {
                 out.n_gates_conservative++;
             } else {
+                const int slot = (int)out.gates.size();
+                if (slot >= rtcdev::MAX_GATES) { err = "more than " + std::to_string(rtcdev::MAX_GATES) + " group boxes need exact evaluation"; return sub; }
+                rtcdev::Gate g{};
+                for (int k = 0; k < 3; ++k) { g.lo[k] = nd.bbox_min[k]; g.hi[k] = nd.bbox_max[k]; }
+                out.gates.push_back(g);
+                for (int q = pb; q < pe; ++q) {
+                    if (slot < 32) out.prims[(size_t)q].gate_mask |= 1u << slot;
+                    else out.prims[(size_t)q].gate_mask_hi |= 1u << (slot - 32);
+                }
                 out.n_gates_exact++;
             }
         }

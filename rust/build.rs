@@ -21,13 +21,24 @@ fn main() {
     let out = PathBuf::from(env::var("OUT_DIR").unwrap());
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "nvcc".into());
     let arch = ["-gencode", "arch=compute_100a,code=sm_100a"];
-    // -fmad=false: no multiply-add contraction, f64 results stay bit-identical to this crate's scalar code
-    let units: [(&str, &[&str]); 4] = [
-        ("render_kernels.cu", &["-O3", "-lineinfo", "-fmad=false"]),
-        ("microbench.cu", &["-O3", "-lineinfo"]),
-        ("rtc_api.cpp", &["-O2"]),
-        ("scene_build.cpp", &["-O2"]),
-    ];
+    // The translation units and their flag classes come from csrc/UNITS, the list the Python build reads too.
+    //   device: -fmad=false (no multiply-add contraction: f64 results stay bit-identical to this crate's scalar code)
+    let listing = std::fs::read_to_string(csrc.join("UNITS")).expect("cannot read csrc/UNITS");
+    println!("cargo:rerun-if-changed={}", csrc.join("UNITS").display());
+    let mut units: Vec<(String, Vec<&str>)> = Vec::new();
+    for line in listing.lines() {
+        let line = line.split('#').next().unwrap();
+        let mut it = line.split_whitespace();
+        if let (Some(name), Some(kind)) = (it.next(), it.next()) {
+            let flags: Vec<&str> = match kind {
+                "device" => vec!["-O3", "-lineinfo", "-fmad=false"],
+                "cuda" => vec!["-O3", "-lineinfo"],
+                "host" => vec!["-O2"],
+                other => panic!("csrc/UNITS: unknown kind {}", other),
+            };
+            units.push((name.to_string(), flags));
+        }
+    }
     let mut objs = Vec::new();
     for (name, flags) in units.iter() {
         let obj = out.join(format!("{}.o", name));
@@ -35,13 +46,13 @@ fn main() {
             .args(["-std=c++17", "-Xcompiler", "-fPIC", "-x", "cu", "-c"])
             .args(arch)
             .args(flags.iter())
-            .arg(csrc.join(name))
+            .arg(csrc.join(name.as_str()))
             .arg("-o")
             .arg(&obj)
             .status()
             .expect("failed to run nvcc");
         assert!(status.success(), "nvcc failed on {}", name);
-        println!("cargo:rerun-if-changed={}", csrc.join(name).display());
+        println!("cargo:rerun-if-changed={}", csrc.join(name.as_str()).display());
         objs.push(obj);
     }
     let so = out.join("librtc.so");

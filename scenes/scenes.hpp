@@ -880,12 +880,83 @@ Scene<A> no_shadow_flat(size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- authored: more than 32 group boxes that must be evaluated exactly ------------------------------------------------
+// 40 groups, each holding one finite cone: a cone's single-root crossing may lie outside its box (src/shape.rs:811-818), so
+// none of these group boxes is provably conservative and each one stays an exact per-ray gate (gate slots).
+template <class A>
+Scene<A> many_gates(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.8, 0.8, 0.75)), {{'s', 0.0}, {'r', 0.2}}))));
+    for (int i = 0; i < 40; i++) {
+        const int gx = i % 8, gz = i / 8;
+        std::vector<E> inner;
+        inner.push_back(E::cone(shape_args<A>(M::translation(0.0, 1.0, 0.0) * M::scaling(0.4, 1.0, 0.4),
+                                              material_with<A>(P::plain(C::make(0.2 + 0.1 * gx, 0.9 - 0.15 * gz, 0.3 + 0.05 * i / 4)), {{'r', (i % 5 == 0) ? 0.3 : 0.0}})),
+                                -1.0, 0.0, (i & 1) != 0));
+        std::vector<E> outer;  // nested: the inner group's box is a gate too
+        outer.push_back(E::composite(M::rotation_y(0.2 * i), std::nullopt, G::Aggregation, std::move(inner)));
+        if (i % 4 == 0) outer.push_back(E::sphere(shape_args<A>(M::translation(0.0, 1.3, 0.0) * M::scaling(0.2, 0.2, 0.2), material_with<A>(P::plain(C::make(0.9, 0.9, 0.2)), {}))));
+        el.push_back(E::composite(M::translation(-5.25 + 1.5 * gx, 0.0, 1.5 * gz), std::nullopt, G::Aggregation, std::move(outer)));
+    }
+    s.world.lights.push_back({C::make(0.9, 0.9, 0.9), V::point(-6.0, 9.0, -8.0)});
+    s.camera = A::Camera::make(hsize, vsize, 0.9,
+                               A::Camera::transform(V::point(0.0, 6.0, -9.0), V::point(0.0, 0.5, 3.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
+// --- authored: a mesh beyond the one-block device sort (obj.rs has no size limit) -------------------
+// teapot_high.obj with every triangle split into 16 (two rounds of edge midpoints; normals of the midpoints = normalised
+// sums): 101 120 smooth triangles in the chapter-15 scene.  Exercises the multi-block radix sort of bvh_build.cu.
+template <class A>
+typename A::ObjData tessellate(const typename A::ObjData& in, int rounds) {
+    using V = typename A::Vector;
+    typename A::ObjData d = in;
+    for (int r = 0; r < rounds; r++) {
+        std::vector<typename A::ObjData::Tri> next;
+        next.reserve(d.triangles.size() * 4);
+        for (const auto& t : d.triangles) {
+            size_t mp[3], mn[3] = {0, 0, 0};
+            for (int e = 0; e < 3; e++) {
+                const V& a = d.vertices[t.p[e] - 1];
+                const V& b = d.vertices[t.p[(e + 1) % 3] - 1];
+                d.vertices.push_back(V::point(0.5 * (a.x + b.x), 0.5 * (a.y + b.y), 0.5 * (a.z + b.z)));
+                mp[e] = d.vertices.size();
+                if (t.has_n) {
+                    const V& na = d.normals[t.n[e] - 1];
+                    const V& nb = d.normals[t.n[(e + 1) % 3] - 1];
+                    d.normals.push_back(V::vector(na.x + nb.x, na.y + nb.y, na.z + nb.z).normalize());
+                    mn[e] = d.normals.size();
+                }
+            }
+            auto tri = [&](size_t p0, size_t p1, size_t p2, size_t n0, size_t n1, size_t n2) {
+                typename A::ObjData::Tri q = t;
+                q.p[0] = p0; q.p[1] = p1; q.p[2] = p2;
+                q.n[0] = n0; q.n[1] = n1; q.n[2] = n2;
+                next.push_back(q);
+            };
+            tri(t.p[0], mp[0], mp[2], t.n[0], mn[0], mn[2]);
+            tri(mp[0], t.p[1], mp[1], mn[0], t.n[1], mn[1]);
+            tri(mp[2], mp[1], t.p[2], mn[2], mn[1], t.n[2]);
+            tri(mp[0], mp[1], mp[2], mn[0], mn[1], mn[2]);
+        }
+        d.triangles.swap(next);
+    }
+    return d;
+}
+template <class A>
+Scene<A> teapot_tess(size_t hsize, size_t vsize) {
+    return teapot_from<A>(tessellate<A>(load_mesh_fixture<A>(data_dir() + "/teapot_high.mesh"), 2), hsize, vsize);
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
                                                "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope",
-                                               "axis_aligned", "no_shadow_flat"};
+                                               "axis_aligned", "no_shadow_flat", "many_gates"};
     return n;
 }
 
@@ -908,6 +979,8 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "cone_slope") return cone_slope<A>(hsize, vsize);
     if (name == "axis_aligned") return axis_aligned<A>(hsize, vsize);
     if (name == "no_shadow_flat") return no_shadow_flat<A>(hsize, vsize);
+    if (name == "many_gates") return many_gates<A>(hsize, vsize);
+    if (name == "teapot_tess") return teapot_tess<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");
 }

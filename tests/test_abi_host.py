@@ -115,6 +115,8 @@ def test_host_scene_build(built, name):
         assert b["features"] & 1
     if name == "chapter14_title":  # 36 finite open cones: BVH items behind per-ray guards, only the backdrop plane is tested for every ray
         assert b["unbounded"] == 1 and b["bvh_items"] == 72 and b["cone_guards"] == 36 and (b["features"] & 4)
+    if name == "many_gates":  # every box above a finite cone is an exact gate; the 10 outer boxes that also hold a sphere still are
+        assert b["gates_exact"] > 32 and b["cone_guards"] >= 1
     if name == "cone_slope":  # boxes above a finite cone stay exact gates: its single-root crossing may lie outside them
         assert b["cone_guards"] == 1 and b["gates_exact"] == 2 and b["gates_conservative"] == 0
 
@@ -224,3 +226,81 @@ def test_shards_partition_the_window(built, w, h, tile, n):
         seen[real] += 1
     assert (seen == 1).all()
     assert R.shard_pixels(w, h, n, n, tile).size == 0  # shard index out of range -> empty
+
+
+# ---- the Rust mirror of the header (rust/src/ffi.rs, unbuilt here: no toolchain) must not drift from include/rtc.h ------
+C_TO_RUST = {"int32_t": "i32", "uint32_t": "u32", "uint64_t": "u64", "int64_t": "i64", "double": "f64", "int": "c_int", "uint8_t": "u8"}
+
+
+def _c_structs():
+    """struct name -> [(field, rust-type spelling of its C type)] parsed from include/rtc.h."""
+    text = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    out = {}
+    for body, name in re.findall(r"typedef struct \w+ \{(.*?)\} (\w+);", text, flags=re.S):
+        fields = []
+        for decl in body.split(";"):
+            decl = " ".join(decl.split())
+            if not decl:
+                continue
+            m = re.match(r"(const )?(\w+)\s*(\*?)\s*(.*)", decl)
+            const, ctype, ptr, names = m.groups()
+            for n in names.split(","):
+                n = n.strip()
+                star = ptr or ("*" if n.startswith("*") else "")
+                n = n.lstrip("* ")
+                arr = re.match(r"(\w+)\[(\d+)\]", n)
+                base = C_TO_RUST.get(ctype, ctype)
+                if star:
+                    ty = ("*const " if const else "*mut ") + base
+                elif arr:
+                    n, ty = arr.group(1), f"[{base}; {arr.group(2)}]"
+                else:
+                    ty = base
+                fields.append((n, ty))
+        out[name] = fields
+    return out
+
+
+def _rust_structs():
+    text = re.sub(r"//[^\n]*", "", open(os.path.join(ROOT, "rust", "src", "ffi.rs")).read())
+    out = {}
+    for attrs, name, body in re.findall(r"((?:#\[[^\]]*\]\s*)+)pub struct (\w+) \{(.*?)\n\}", text, flags=re.S):
+        assert "repr(C)" in attrs, f"{name} is not #[repr(C)]"
+        out[name] = [(f.strip(), " ".join(t.split())) for f, t in re.findall(r"pub (\w+)\s*:\s*([^,]+),", body)]
+    return out
+
+
+def test_rust_ffi_structs_mirror_the_header():
+    c, r = _c_structs(), _rust_structs()
+    for name in ["rtc_prim", "rtc_node", "rtc_material", "rtc_pattern", "rtc_light", "rtc_scene_desc", "rtc_camera", "rtc_opts", "rtc_stats"]:
+        assert name in r, f"rust/src/ffi.rs lacks {name}"
+        assert r[name] == c[name], (name, [x for x in zip(r[name], c[name]) if x[0] != x[1]], len(r[name]), len(c[name]))
+
+
+def test_rust_ffi_functions_and_constants_mirror_the_header():
+    header = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
+    rust = open(os.path.join(ROOT, "rust", "src", "ffi.rs")).read()
+    declared = set(declared_functions())
+    bound = set(re.findall(r"pub fn (rtc_\w+)\s*\(", rust))
+    assert bound <= declared, bound - declared
+    # what Image::par_render needs (rust/src/gpu.rs) must be bound
+    for must in ["rtc_device_count", "rtc_scene_create_multi", "rtc_scene_destroy", "rtc_render_multi", "rtc_last_error", "rtc_alloc_host", "rtc_free_host"]:
+        assert must in bound, must
+    # argument counts agree
+    for fn in bound:
+        c_args = re.search(r"\b" + fn + r"\s*\(([^)]*)\)", header).group(1)
+        r_args = re.search(r"pub fn " + fn + r"\s*\(([^)]*)\)", rust).group(1)
+        n_c = 0 if c_args.strip() in ("", "void") else c_args.count(",") + 1
+        n_r = 0 if not r_args.strip() else r_args.count(",") + 1
+        assert n_c == n_r, (fn, c_args, r_args)
+    for const in ["RTC_ABI_VERSION", "RTC_BUILD_FAST"]:
+        cv = int(re.search(r"#define " + const + r" (\d+)", header).group(1))
+        rv = int(re.search(r"pub const " + const + r": \w+ = (\d+);", rust).group(1))
+        assert cv == rv, const
+    # and build.rs compiles exactly the units the Python build compiles (csrc/UNITS is the one list)
+    assert "UNITS" in open(os.path.join(ROOT, "rust", "build.rs")).read()
+    from raytracer_challenge_b200 import _build
+    names = [n for n, _ in _build.read_units()]
+    assert "bvh_build.cu" in names and "render_kernels.cu" in names
+    for n in names:
+        assert os.path.exists(os.path.join(ROOT, "raytracer_challenge_b200", "csrc", n)), n

@@ -28,6 +28,7 @@ CASES = [
     ("axis_aligned", 48, 1),
     ("axis_aligned", 1, 1),
     ("axis_aligned", 65, 37),
+    ("many_gates", 96, 54),             # 80 group boxes over finite cones: 64-bit gate masks, slots assigned after the subtree walk
     ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
 
@@ -317,3 +318,31 @@ def test_device_built_bvh_renders_the_same_frame(built, name, w, h, monkeypatch)
     if host_stats["bvh_items"] >= 64:  # smaller scenes keep the host build
         assert dev_stats["bvh_depth"] >= 3 and 0 < dev_stats["bvh_nodes"] < dev_stats["bvh_items"]
         assert dev_stats["device_bytes"] > host_stats["device_bytes"]  # the arena also holds the builder's scratch: the device path ran
+
+
+# ---- capacity: scenes beyond the sizes the example binaries need ---------------------------------------------------------
+def test_hundred_thousand_triangle_mesh_on_the_device_built_bvh(built, monkeypatch):
+    """src/obj.rs has no size limit.  teapot_high tessellated to 101 120 smooth triangles: the device-side build sorts its
+    Morton keys with the multi-block radix sort (bvh_build.cu) instead of the one-block sort; windows on the mesh equal
+    the oracle, the host-built SAH tree and the brute-force scan."""
+    w, h = 3840, 2160
+    windows = [(1900, 1300, 12, 6), (1700, 1400, 12, 6)]
+    with R.Session("teapot_tess", w, h, device=0) as s:
+        host_stats = dict(s.build_stats)
+        sah = [s.render(R.Opts(window=win))[0] for win in windows]
+    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
+    with R.Session("teapot_tess", w, h, device=0) as s:
+        dev_stats = dict(s.build_stats)
+        for win, want in zip(windows, sah):
+            img, st = s.render(R.Opts(window=win))
+            brute, _ = s.render(R.Opts(window=win, flags=1))
+            ref, counts, _ = oracle_render("teapot_tess", w, h, window=win)
+            rep = compare_images(img, ref)
+            assert rep["ok"] and rep["max_abs_f64"] < 1e-9, (win, rep)
+            assert np.array_equal(img, want) and np.array_equal(img, brute), win
+            assert st.rays_ref == int(counts.sum())
+        whole, st = s.render(R.Opts())
+        assert np.isfinite(whole).all() and st.rays_primary == w * h
+    assert host_stats["bvh_items"] == 101120 and dev_stats["bvh_items"] == 101120
+    assert 0 < dev_stats["bvh_nodes"] < 101120 and 3 <= dev_stats["bvh_depth"] <= 62
+    assert dev_stats["device_bytes"] > host_stats["device_bytes"]  # the arena also holds the builder's scratch: the device path ran
