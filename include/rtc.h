@@ -212,6 +212,25 @@ int rtc_render_multi(rtc_scene* const* scenes, int n, const rtc_camera* camera, 
 int rtc_render_device(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double** out_dev_rgb,
                       uint64_t* out_pixels, rtc_stats* stats);
 
+/* No counterpart in the reference: added for callers that cannot allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * rtc_render for a small window with NO allocation: no cudaMalloc / cudaFree / cudaHostAlloc, no stream or event is
+ * created; every byte of per-render scratch lives in one static device array of RTC_NOALLOC_SCRATCH_BYTES that each GPU
+ * holds from the moment it loads the library until the process exits.  Same kernels, same pixels as rtc_render.
+ *   - `scene` is an existing handle (rtc_scene_create allocates; this call does not); out_rgb receives win_w * win_h (or
+ *     hsize * vsize) f64 rgb triples, row-major, and may be HOST or DEVICE memory of the caller.
+ *   - opts: fuel, spp, window and RTC_FLAG_BRUTE_FORCE are honoured; sharding and the other flags are rejected.
+ *   - A window whose queues do not fit the array is rejected with an error that names the bytes needed and the limit.
+ *     Rule of thumb for fuel 5: ~19 000 samples (pixels x samples per pixel) when no material both reflects and refracts,
+ *     ~1 100 samples when one does (the binary path tree is sized for its worst case).
+ *   - Every call on a device shares the array, which keeps the previous call's contents; the call clears what must start at
+ *     zero.  Calls that overlap on one GPU would race: the library serialises the calls of one process (per-device
+ *     mutex, and the call blocks until the pixels have landed).  Each process has its own copy of the array.
+ *   - Work runs on the legacy default stream and the call ends with a stream synchronisation.
+ * 0 = ok; otherwise rtc_last_error(). */
+#define RTC_NOALLOC_SCRATCH_BYTES (16u << 20)
+int rtc_render_noalloc(rtc_scene* scene, const rtc_camera* camera, const rtc_opts* opts, double* out_rgb, rtc_stats* stats);
+
 /* Output slots of shard (shard_index, shard_count) of a w x h window.  The window is cut into tile_w x tile_h
  * tiles (default 8x4, numbered row-major); shard i owns tiles i, i+shard_count, ...; its output lists the owned
  * tiles in ascending order, each tile row-major and FULL size: slots that fall outside the window (partial edge

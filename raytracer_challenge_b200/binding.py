@@ -99,6 +99,7 @@ def load_rtc():
         lib.rtc_scene_destroy.argtypes = [C.c_void_p]
         lib.rtc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.rtc_render_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.rtc_render_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.rtc_alloc_host.restype = C.c_void_p
         lib.rtc_alloc_host.argtypes = [C.c_uint64]
         lib.rtc_free_host.argtypes = [C.c_void_p]

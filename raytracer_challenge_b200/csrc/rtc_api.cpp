@@ -16,6 +16,7 @@
 
 #include "../../include/rtc.h"
 #include "render_kernels.h"
+#include "rtc_internal.hpp"
 #include "scene_build.hpp"
 
 namespace {
@@ -144,15 +145,9 @@ int env_int(const char* name, int fallback, int lo, int hi) {
 
 }  // namespace
 
-struct rtc_scene {
-    int device = 0;
-    int feat = 0;
-    std::shared_ptr<rtchost::HostScene> host;  // shared by the handles of one rtc_scene_create_multi call
-    rtcdev::Scene dev{};
-    void* arena = nullptr;  // one device allocation holding every scene array
-    size_t arena_bytes = 0;
-    int bvh_depth = -1, bvh_nodes = -1;  // device-side build: what the device reported (host build: see HostScene)
-};
+namespace rtcapi {
+int fail(const std::string& msg) { return ::fail(msg); }
+}  // namespace rtcapi
 
 extern "C" {
 

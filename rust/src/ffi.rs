@@ -161,6 +161,7 @@ extern "C" {
     pub fn rtc_scene_destroy(scene: *mut rtc_scene);
     pub fn rtc_render(scene: *mut rtc_scene, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;
     pub fn rtc_render_multi(scenes: *const *mut rtc_scene, n: c_int, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;
+    pub fn rtc_render_noalloc(scene: *mut rtc_scene, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;
     pub fn rtc_alloc_host(bytes: u64) -> *mut std::ffi::c_void;
     pub fn rtc_free_host(p: *mut std::ffi::c_void);
     pub fn rtc_last_error() -> *const c_char;
