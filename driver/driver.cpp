@@ -32,6 +32,7 @@ struct HostApi {
 };
 
 struct Session {
+    std::unique_ptr<scenes::Scene<HostApi>> built;  // the World and the Camera, as a bin's construct_world() leaves them
     std::unique_ptr<rtc::FlatScene> flat;
     rtc_camera camera{};
     rtc_scene* scene = nullptr;
@@ -52,8 +53,9 @@ extern "C" {
 int drv_open(const char* name, const char* data_dir, int hsize, int vsize, int device, void** out, int64_t* stats16, char* err, int errlen) {
     try {
         if (data_dir && *data_dir) scenes::data_dir() = data_dir;
-        auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
         auto s = std::make_unique<Session>();
+        s->built = std::make_unique<scenes::Scene<HostApi>>(scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize));
+        const auto& sc = *s->built;
         s->flat = std::make_unique<rtc::FlatScene>(sc.world);
         s->camera = sc.camera.to_c();
         const rtc_scene_desc d = s->flat->desc();
@@ -118,6 +120,52 @@ int drv_e2e_step(void* h, int device, const rtc_opts* opts, double* out_rgb, rtc
         std::fprintf(stderr, "e2e step: create %.3f ms, render %.3f ms (kernels %.3f), destroy %.3f ms\n", ms(t0, t1), ms(t1, t2), stats ? stats->ms_kernels : 0.0, ms(t2, t3));
     }
     return rc;
+}
+
+// One end-to-end step of the REAL drop-in call: Image::par_render(camera, world) of the host builder API on the World
+// drv_open built (mesh parsing excluded, like the bins' "Rendering image" timer): flatten the World, create the scene on
+// `n_devices` GPUs starting at `first_device`, render, bring the frame to the host, destroy the scene, return the Image.
+// probe3 (optional) receives the centre pixel, so that the caller can see the pixels arrived; phase_ms (optional, 2
+// doubles): time spent flattening the World / in the rest of the call.
+int drv_par_render_step(void* h, int first_device, int n_devices, const rtc_opts* opts, double* probe3, rtc_stats* stats, double* phase_ms, char* err, int errlen) {
+    Session* s = (Session*)h;
+    try {
+        if (!s || !s->built) { set_err(err, errlen, "drv_par_render_step: no scene"); return 1; }
+        rtc::RenderOptions ro;
+        if (opts) { ro.opts.fuel = opts->fuel; ro.opts.spp_x = opts->spp_x; ro.opts.spp_y = opts->spp_y; ro.opts.flags = opts->flags & RTC_FLAG_BRUTE_FORCE; }
+        for (int i = 0; i < n_devices; ++i) ro.devices.push_back(first_device + i);
+        const auto t0 = std::chrono::steady_clock::now();
+        rtc::Image img = rtc::Image::par_render(s->built->camera, s->built->world, ro);
+        const auto t1 = std::chrono::steady_clock::now();
+        if (probe3) {
+            const rtc::Color c = img.read(img.hsize / 2, img.vsize / 2);
+            probe3[0] = c.r; probe3[1] = c.g; probe3[2] = c.b;
+        }
+        if (stats) *stats = img.stats;
+        if (phase_ms) { phase_ms[0] = img.flatten_ms; phase_ms[1] = std::chrono::duration<double, std::milli>(t1 - t0).count() - img.flatten_ms; }
+        return 0;
+    } catch (const std::exception& e) {
+        set_err(err, errlen, e.what());
+        return 1;
+    }
+}
+
+// Host-only timing aid: milliseconds per FlatScene(world) (best of `reps`), and per host half of rtc_scene_create.
+double drv_flatten_ms(void* h, int reps, double* validate_ms) {
+    Session* s = (Session*)h;
+    double best = 1e30, best_v = 1e30;
+    for (int r = 0; r < reps; ++r) {
+        const auto t0 = std::chrono::steady_clock::now();
+        rtc::FlatScene flat(s->built->world);
+        const auto t1 = std::chrono::steady_clock::now();
+        const rtc_scene_desc d = flat.desc(RTC_BUILD_FAST);
+        rtc_scene_validate(&d, nullptr);
+        const auto t2 = std::chrono::steady_clock::now();
+        best = std::min(best, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        best_v = std::min(best_v, std::chrono::duration<double, std::milli>(t2 - t1).count());
+    }
+    if (validate_ms) *validate_ms = best_v;
+    return best;
 }
 
 // The single-process multi-GPU form (rtc_render_multi) through the host API: Image::par_render over the first

@@ -260,9 +260,13 @@ int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16);
  * create-render-destroy per frame (what Image::par_render does) does not reallocate it.  This frees it. */
 void rtc_release_device_memory(int device);
 
-/* Page-locked host memory for out_rgb (optional: any host buffer works, pinned ones copy at full PCIe rate). */
+/* Page-locked host memory for out_rgb (optional: any host buffer works, pinned ones copy at full PCIe rate).  Pooled:
+ * rtc_free_host parks the buffer inside the library and the next rtc_alloc_host of a similar size reuses it, so that one
+ * frame-sized buffer per Image::par_render call (src/image.rs:65-81) costs nothing after the first call (page-locking
+ * 199 MB takes tens of milliseconds).  rtc_release_host_memory hands the parked buffers back to the driver. */
 void* rtc_alloc_host(uint64_t bytes);
 void rtc_free_host(void* p);
+void rtc_release_host_memory(void);
 /* Page-locks / unlocks memory the caller already owns (e.g. a shared-memory frame several processes render into). */
 int rtc_host_register(void* p, uint64_t bytes);
 int rtc_host_unregister(void* p);

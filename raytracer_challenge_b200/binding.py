@@ -154,6 +154,7 @@ def load_driver():
         lib.drv_par_render_ppm.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_char_p, C.c_int]
         lib.drv_par_render_multi.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
         lib.drv_e2e_step.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        lib.drv_par_render_step.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
         lib.drv_scene.restype = C.c_void_p
         lib.drv_scene.argtypes = [C.c_void_p]
         lib.drv_camera.restype = C.c_void_p

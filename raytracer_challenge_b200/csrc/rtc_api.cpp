@@ -163,16 +163,58 @@ int rtc_device_count(void) {
     return n;
 }
 
+// Page-locked host buffers are pooled: cudaHostAlloc / cudaFreeHost of a 199 MB frame cost tens of milliseconds each, and
+// Image::par_render (src/image.rs:65-81) needs one frame-sized buffer per call.  rtc_free_host parks a buffer, the next
+// rtc_alloc_host of a similar size takes it back; rtc_release_host_memory returns the parked ones to the driver.
+namespace {
+struct HostBlock { void* p; uint64_t bytes; };
+std::mutex g_host_mu;
+std::vector<HostBlock> g_host_live, g_host_free;
+constexpr uint64_t HOST_POOL_MAX_BYTES = 4ull << 30;  // parked bytes beyond this are freed at once
+}  // namespace
+
 void* rtc_alloc_host(uint64_t bytes) {
+    if (!bytes) bytes = 1;
+    {
+        std::lock_guard<std::mutex> lock(g_host_mu);
+        size_t best = g_host_free.size();
+        for (size_t i = 0; i < g_host_free.size(); ++i)  // smallest parked block that fits without wasting more than half of itself
+            if (g_host_free[i].bytes >= bytes && g_host_free[i].bytes <= 2 * bytes + 4096 && (best == g_host_free.size() || g_host_free[i].bytes < g_host_free[best].bytes)) best = i;
+        if (best != g_host_free.size()) {
+            const HostBlock b = g_host_free[best];
+            g_host_free.erase(g_host_free.begin() + (long)best);
+            g_host_live.push_back(b);
+            return b.p;
+        }
+    }
     void* p = nullptr;
-    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
         g_error = "rtc_alloc_host: cudaHostAlloc failed";
         return nullptr;
     }
+    std::lock_guard<std::mutex> lock(g_host_mu);
+    g_host_live.push_back({p, bytes});
     return p;
 }
 void rtc_free_host(void* p) {
-    if (p) cudaFreeHost(p);
+    if (!p) return;
+    std::lock_guard<std::mutex> lock(g_host_mu);
+    for (size_t i = 0; i < g_host_live.size(); ++i)
+        if (g_host_live[i].p == p) {
+            const HostBlock b = g_host_live[i];
+            g_host_live.erase(g_host_live.begin() + (long)i);
+            uint64_t parked = b.bytes;
+            for (const HostBlock& f : g_host_free) parked += f.bytes;
+            if (parked <= HOST_POOL_MAX_BYTES) g_host_free.push_back(b);
+            else cudaFreeHost(b.p);
+            return;
+        }
+    cudaFreeHost(p);  // (not one of ours: e.g. allocated before a rtc_release_host_memory raced; let the driver decide)
+}
+void rtc_release_host_memory(void) {
+    std::lock_guard<std::mutex> lock(g_host_mu);
+    for (const HostBlock& f : g_host_free) cudaFreeHost(f.p);
+    g_host_free.clear();
 }
 int rtc_host_register(void* p, uint64_t bytes) {
     if (!p || !bytes) return fail("rtc_host_register: null argument");

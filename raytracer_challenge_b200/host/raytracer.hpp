@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <array>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <fstream>
@@ -556,6 +557,12 @@ class FlatScene {
         const double inf = std::numeric_limits<double>::infinity();
         for (int k = 0; k < 3; ++k) { root.bbox_min[k] = -inf; root.bbox_max[k] = inf; }
         nodes.push_back(root);
+        // one pass to size the arrays (growing a 600-byte-per-primitive vector by doubling copies it several times over)
+        size_t n_prims = 0, n_groups = 0;
+        count(world.elements, n_prims, n_groups);
+        prims.reserve(n_prims);
+        nodes.reserve(n_groups + 1);
+        children.reserve(n_prims + n_groups);
         emit_children(0, world.elements);
     }
 
@@ -581,6 +588,15 @@ class FlatScene {
 
   private:
     std::vector<std::pair<const Pattern::Node*, int32_t>> pattern_cache_;   // identical subtrees are shared
+    const Pattern::Node* last_pattern_ = nullptr;  // the previous primitive's material: the triangles of a mesh all carry the same one
+    int32_t last_material_ = -1;
+
+    static void count(const std::vector<Element>& elems, size_t& n_prims, size_t& n_groups) {
+        for (const Element& e : elems) {
+            if (e.is_group()) { n_groups++; count(std::get<Group>(e.node).children, n_prims, n_groups); }
+            else n_prims++;
+        }
+    }
 
     static void copy16(double (&dst)[16], const Matrix& m) { for (int i = 0; i < 16; ++i) dst[i] = m.m[(size_t)i]; }
     static void copy3(double (&dst)[3], const Vector& v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
@@ -603,6 +619,17 @@ class FlatScene {
         return idx;
     }
     int32_t emit_material(const Material& m) {
+        if (last_material_ >= 0 && m.pattern.root().get() == last_pattern_) {  // same pattern object as the previous primitive: compare the scalars only
+            const rtc_material& o = materials[(size_t)last_material_];
+            if (o.ambient == m.ambient && o.diffuse == m.diffuse && o.specular == m.specular && o.shininess == m.shininess &&
+                o.reflective == m.reflective && o.transparency == m.transparency && o.refractive_index == m.refractive_index)
+                return last_material_;
+        }
+        last_pattern_ = m.pattern.root().get();
+        last_material_ = emit_material_slow(m);
+        return last_material_;
+    }
+    int32_t emit_material_slow(const Material& m) {
         const int32_t pat = emit_pattern(m.pattern.root());
         for (size_t i = 0; i < materials.size(); ++i) {
             const rtc_material& o = materials[i];
@@ -619,9 +646,11 @@ class FlatScene {
         return (int32_t)materials.size() - 1;
     }
     int32_t emit_prim(const Shape& s) {
-        rtc_prim p{};
+        const int32_t material = emit_material(s.material);
+        prims.emplace_back();  // filled in place: one pass over its 600 bytes
+        rtc_prim& p = prims.back();
         p.kind = s.kind;
-        p.material = emit_material(s.material);
+        p.material = material;
         p.casts_shadow = s.casts_shadow ? 1 : 0;
         p.closed = s.closed ? 1 : 0;
         copy16(p.transform_inv, s.transform_inv);
@@ -631,7 +660,6 @@ class FlatScene {
         p.max = s.max;
         copy3(p.p1, s.p1); copy3(p.e1, s.e1); copy3(p.e2, s.e2);
         copy3(p.n1, s.n1); copy3(p.n2, s.n2); copy3(p.n3, s.n3);
-        prims.push_back(p);
         return (int32_t)prims.size() - 1;
     }
     void emit_children(int32_t node_index, const std::vector<Element>& elems) {
@@ -660,6 +688,73 @@ class FlatScene {
 };
 
 // ---- Image (src/image.rs) -----------------------------------------------------------------
+// The pixel store of an Image: what `pixels: Vec<Color>` is in the reference (src/image.rs:11-15, a private field).  A
+// Color is three f64 (src/color.rs:7-11) — exactly the (r, g, b) triples rtc_render writes — so the frame a render call
+// lands in page-locked host memory IS the pixel array: Pixels adopts that buffer instead of copying 199 MB out of it,
+// and hands it back to the library's pool (rtc_free_host) when the Image dies.  Otherwise it behaves like the vector it
+// replaces (size, [], data, iteration, resize; copies are deep, into ordinary memory).
+static_assert(sizeof(Color) == 3 * sizeof(double) && alignof(Color) == alignof(double), "Color must be layout-identical to an f64 rgb triple");
+class Pixels {
+  public:
+    Pixels() = default;
+    ~Pixels() { release(); }
+    Pixels(const Pixels& o) : own_(o.begin(), o.end()) { p_ = own_.data(); n_ = own_.size(); }
+    Pixels& operator=(const Pixels& o) {
+        if (this != &o) { release(); own_.assign(o.begin(), o.end()); p_ = own_.data(); n_ = own_.size(); }
+        return *this;
+    }
+    Pixels(Pixels&& o) noexcept { steal(o); }
+    Pixels& operator=(Pixels&& o) noexcept {
+        if (this != &o) { release(); steal(o); }
+        return *this;
+    }
+    // takes ownership of a buffer obtained from rtc_alloc_host that holds n (r, g, b) triples
+    static Pixels adopt_pinned(double* rgb, size_t n) {
+        Pixels px;
+        px.pinned_ = rgb;
+        px.p_ = reinterpret_cast<Color*>(rgb);
+        px.n_ = n;
+        return px;
+    }
+    size_t size() const { return n_; }
+    bool empty() const { return n_ == 0; }
+    Color* data() { return p_; }
+    const Color* data() const { return p_; }
+    Color& operator[](size_t i) { return p_[i]; }
+    const Color& operator[](size_t i) const { return p_[i]; }
+    Color* begin() { return p_; }
+    Color* end() { return p_ + n_; }
+    const Color* begin() const { return p_; }
+    const Color* end() const { return p_ + n_; }
+    void resize(size_t n) {
+        if (pinned_) { std::vector<Color> v(p_, p_ + std::min(n, n_)); release(); own_.swap(v); }
+        own_.resize(n);
+        p_ = own_.data();
+        n_ = n;
+    }
+
+  private:
+    void release() {
+        if (pinned_) rtc_free_host(pinned_);
+        pinned_ = nullptr;
+        p_ = nullptr;
+        n_ = 0;
+    }
+    void steal(Pixels& o) {
+        own_ = std::move(o.own_);
+        pinned_ = o.pinned_;
+        n_ = o.n_;
+        p_ = pinned_ ? reinterpret_cast<Color*>(pinned_) : own_.data();
+        o.pinned_ = nullptr;
+        o.p_ = nullptr;
+        o.n_ = 0;
+    }
+    Color* p_ = nullptr;
+    size_t n_ = 0;
+    std::vector<Color> own_;
+    double* pinned_ = nullptr;
+};
+
 struct RenderOptions {
     std::vector<int> devices;  // CUDA device ordinals to shard the frame over; empty = every visible device
     rtc_opts opts{};           // fuel / supersampling / window (sharding is chosen by par_render itself)
@@ -669,14 +764,17 @@ struct RenderOptions {
 class Image {
   public:
     size_t hsize = 0, vsize = 0;
-    std::vector<Color> pixels;
+    Pixels pixels;
     rtc_stats stats{};
+    double flatten_ms = 0.0;  // (diagnostic) time par_render spent turning the World into the flat arrays of the C ABI
 
     // Image::par_render(camera, world) (src/image.rs:65-81): flatten -> upload to every device -> CUDA wavefront on
     // each device's share of the rows -> rows land in one host image.  Infallible in the reference; here every
     // failure (no device, CUDA error, overflow) throws.
     static Image par_render(const Camera& camera, const World& world, const RenderOptions& ro = RenderOptions{}) {
+        const auto t_flat = std::chrono::steady_clock::now();
         FlatScene flat(world);
+        const double flatten_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_flat).count();
         const rtc_scene_desc d = flat.desc(RTC_BUILD_FAST);  // one frame, then the scene is released: BVH built on the device
         std::vector<int> devices = ro.devices;
         if (devices.empty()) {
@@ -695,7 +793,8 @@ class Image {
         img.hsize = windowed ? (size_t)ro.opts.win_w : camera.hsize;
         img.vsize = windowed ? (size_t)ro.opts.win_h : camera.vsize;
         const size_t n = img.hsize * img.vsize;
-        // page-locked staging buffer: the device -> host copies run at full PCIe rate and overlap the kernels
+        // page-locked frame (from the library's pool): the device -> host copies run at full PCIe rate, overlap the kernels, and
+        // the buffer then becomes the Image's pixel array as it is
         double* buf = (double*)rtc_alloc_host((uint64_t)n * 3 * sizeof(double));
         if (!buf) { release(); throw std::runtime_error(std::string("rtc_alloc_host: ") + rtc_last_error()); }
         rtc_opts o = ro.opts;
@@ -705,9 +804,8 @@ class Image {
         const std::string err = rc ? rtc_last_error() : "";
         release();
         if (rc != 0) { rtc_free_host(buf); throw std::runtime_error("rtc_render: " + err); }
-        img.pixels.resize(n);
-        for (size_t i = 0; i < n; ++i) img.pixels[i] = Color{buf[3 * i], buf[3 * i + 1], buf[3 * i + 2]};
-        rtc_free_host(buf);
+        img.pixels = Pixels::adopt_pinned(buf, n);
+        img.flatten_ms = flatten_ms;
         return img;
     }
     Color read(size_t x, size_t y) const { return pixels[y * hsize + x]; }

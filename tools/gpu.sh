@@ -47,9 +47,11 @@ PY
         python tools/perf_probe.py --frames 2 $CASE > gpurun_out/ncu_full_$TAG.log 2>&1
     echo "ncu $TAG rc=$?"; cut -c1-300 gpurun_out/plain_$TAG.log
     python tools/ncu_summary.py gpurun_out/prof_$TAG.ncu-rep gpurun_out/ncu_summary_$TAG.csv
+    python tools/ncu_traffic.py extract gpurun_out/prof_$TAG.ncu-rep gpurun_out/traffic_$TAG.json "ncu --set full -k regex:$RX -s $SKIP -c $COUNT of tools/perf_probe.py --frames 2 $CASE ($TAG)" > /dev/null
     ncu -i gpurun_out/prof_$TAG.ncu-rep --page source --csv 2>/dev/null | gzip > gpurun_out/ncu_source_$TAG.csv.gz
     ncu -i gpurun_out/prof_$TAG.ncu-rep --page source --print-source cuda --csv 2>/dev/null | gzip > gpurun_out/ncu_cuda_$TAG.csv.gz
-    if [ $(stat -c %s gpurun_out/prof_$TAG.ncu-rep) -gt 40000000 ]; then rm gpurun_out/prof_$TAG.ncu-rep; fi
+    # gpurun brings back at most 64 MiB: the .ncu-rep (30+ MB) only travels when asked for (KEEP_REP=1, one capture per call)
+    if [ "${KEEP_REP:-0}" != "1" ]; then rm -f gpurun_out/prof_$TAG.ncu-rep; fi
     ls -la gpurun_out/ | grep $TAG ;;
   multi)
     TAG=$1; N=$2; shift 2
