@@ -89,6 +89,17 @@ struct DeviceCtx {
     std::vector<cudaEvent_t> batch_events; // "batch b is resolved": what its copy waits for
     void* spare_arena = nullptr;           // scene arena of the last destroyed scene, reused by the next create
     size_t spare_arena_bytes = 0;
+    cudaEvent_t fork = nullptr;            // "the counters are cleared": what the other pipelines wait for
+    // Frames that repeat — same scene layout, camera, options, output buffer, scratch — replay a captured CUDA graph: one
+    // launch instead of ~60 kernel launches, 30 event operations and 10 copies enqueued one by one (the enqueueing alone
+    // kept the last pipeline idle for the first ~150 us of a frame; at 8 GPUs a rank's share of the frame takes 1 ms).
+    struct CachedGraph {
+        std::vector<unsigned char> key;
+        cudaGraphExec_t exec = nullptr;
+        uint64_t last_used = 0;
+    };
+    CachedGraph graphs[4];
+    uint64_t graph_clock = 0;
 };
 DeviceCtx g_ctx[MAX_DEVICES];
 
@@ -127,6 +138,7 @@ int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the d
     for (auto& e : c.ev) CU(cudaEventCreate(&e));
     for (auto& cs : c.copy_stream) CU(cudaStreamCreateWithPriority(&cs, cudaStreamNonBlocking, prio_greatest));
     CU(cudaEventCreateWithFlags(&c.copy_done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming));
     CU(cudaMalloc((void**)&c.overflow, sizeof(int)));
     uint8_t perm[512];
     for (int i = 0; i < 512; ++i) perm[i] = kPerm[i & 255];
@@ -326,6 +338,11 @@ void rtc_release_device_memory(int device) {
     cudaSetDevice(device);
     cudaDeviceSynchronize();
     for (Pipe& p : c.pipe) free_pipe(p);
+    for (auto& g : c.graphs) {
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+        g.exec = nullptr;
+        g.key.clear();
+    }
     cudaFree(c.out); c.out = nullptr; c.out_pixels = 0;
     cudaFree(c.counters); c.counters = nullptr;
     cudaFreeHost(c.counters_host); c.counters_host = nullptr;
@@ -744,13 +761,16 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     for (Pipe& p : ctx.pipe) p.stream = staggered ? p.stream_staggered : p.stream_flat;
     cudaStream_t st0 = ctx.pipe[0].stream;
     const size_t counter_bytes = n_batches * COUNTERS_PER_BATCH * sizeof(unsigned long long);
-    CU(cudaMemsetAsync(ctx.counters, 0, counter_bytes, st0));
-    CU(cudaMemsetAsync(ctx.overflow, 0, sizeof(int), st0));
-    CU(cudaEventRecord(ctx.ev[0], st0));
-    for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.ev[0], 0));
     const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
     const int feat = s->feat | (profile ? rtcdev::FEAT_TALLY : 0);  // the work tallies are counted under RTC_FLAG_PROFILE only
-    uint64_t launches = 0;
+    uint64_t n_live = 0;
+    for (const auto& b : schedule) n_live += b.second != 0;
+    const uint64_t launches = n_live * (2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0) + 1);
+    while (host_out && copy_on_own_stream && ctx.batch_events.size() < n_batches) {  // (created here: nothing is allocated while a graph is being captured)
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx.batch_events.push_back(e);
+    }
     const bool timeline = std::getenv("RTC_TIMELINE") != nullptr;  // debugging aid: when each batch's kernels / copy finished
     std::vector<cudaEvent_t> tl_events;
     size_t n_prof = 0;  // profile mode: event k is recorded after launch k-1 (classes cycle trace, shadow, shade)
@@ -765,6 +785,14 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         return 0;
     };
     std::vector<int> prof_class;  // class of the interval that ENDS at event k (0 trace, 1 shadow, 2 shade, -1 other)
+    int* h_overflow = (int*)(ctx.counters_host + n_batches * COUNTERS_PER_BATCH);
+    // Everything one frame puts on the device's streams, from clearing the counters to reading them back: issued directly,
+    // or once under stream capture and replayed as a graph afterwards.
+    auto enqueue = [&]() -> int {
+    CU(cudaMemsetAsync(ctx.counters, 0, counter_bytes, st0));
+    CU(cudaMemsetAsync(ctx.overflow, 0, sizeof(int), st0));
+    CU(cudaEventRecord(ctx.fork, st0));
+    for (int p = 1; p < n_pipes; ++p) CU(cudaStreamWaitEvent(ctx.pipe[p].stream, ctx.fork, 0));
     for (uint64_t b = 0; b < n_batches; ++b) {
         Pipe& p = ctx.pipe[b % (uint64_t)n_pipes];
         cudaStream_t st = p.stream;
@@ -809,18 +837,11 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         for (int level = o.fuel; level >= 0; --level)  // deepest first: a hit is lit when its children's colours are final
             rtcdev::launch_light(level == 0 ? grid0 : grid_full, st, s->dev, level_params(level), hits);
         if (profile) { if (int rc = prof_mark(st)) return rc; prof_class.push_back(2); }
-        launches += 2 * (uint64_t)(o.fuel + 1) + (L > 0 ? 1 : 0);
         rtcdev::launch_resolve(st, f, p.accum, first, npix, ctx.out, row_major ? 1 : 0);
-        launches++;
         if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, st)); tl_events.push_back(e); }
         if (host_out) {  // this batch's pixels are final: copy them out while the other pipelines keep tracing
             cudaStream_t cst = st;
             if (copy_on_own_stream) {
-                while (ctx.batch_events.size() <= b) {
-                    cudaEvent_t e;
-                    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                    ctx.batch_events.push_back(e);
-                }
                 CU(cudaEventRecord(ctx.batch_events[b], st));
                 cst = ctx.copy_stream[b % (uint64_t)n_pipes];
                 CU(cudaStreamWaitEvent(cst, ctx.batch_events[b], 0));
@@ -869,10 +890,61 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         CU(cudaEventRecord(ctx.pipe[p].done, ctx.pipe[p].stream));
         CU(cudaStreamWaitEvent(st0, ctx.pipe[p].done, 0));
     }
-    CU(cudaEventRecord(ctx.ev[1], st0));
-    int* h_overflow = (int*)(ctx.counters_host + n_batches * COUNTERS_PER_BATCH);
     CU(cudaMemcpyAsync(ctx.counters_host, ctx.counters, counter_bytes, cudaMemcpyDeviceToHost, st0));
     CU(cudaMemcpyAsync(h_overflow, ctx.overflow, sizeof(int), cudaMemcpyDeviceToHost, st0));
+    return 0;
+    };  // enqueue
+
+    // ---- replay a captured graph when the frame repeats ----
+    bool use_graph = !profile && !timeline && env_int("RTC_GRAPHS", 1, 0, 1) != 0;
+    if (use_graph && host_out) {  // (copies into pageable memory cannot be captured)
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, host_out) != cudaSuccess || attr.type != cudaMemoryTypeHost) { use_graph = false; cudaGetLastError(); }
+    }
+    if (use_graph) {
+        std::vector<unsigned char> key;
+        auto put = [&key](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+        put(&s->dev, sizeof s->dev); put(&f, sizeof f); put(&o, sizeof o); put(&host_out, sizeof host_out); put(&feat, sizeof feat);
+        put(&n_pipes, sizeof n_pipes); put(&staggered, sizeof staggered); put(&copy_on_own_stream, sizeof copy_on_own_stream); put(&grid_full, sizeof grid_full);
+        put(&ctx.out, sizeof ctx.out); put(&ctx.counters, sizeof ctx.counters); put(&ctx.counters_host, sizeof ctx.counters_host);
+        put(schedule.data(), schedule.size() * sizeof schedule[0]);
+        for (int p = 0; p < n_pipes; ++p) {
+            const Pipe& pp = ctx.pipe[p];
+            put(pp.q, sizeof pp.q); put(pp.hit, sizeof pp.hit); put(&pp.child_rgb, sizeof pp.child_rgb); put(&pp.shadow, sizeof pp.shadow); put(&pp.accum, sizeof pp.accum);
+            put(&pp.q_capacity, sizeof pp.q_capacity);
+        }
+        DeviceCtx::CachedGraph* slot = nullptr;
+        for (auto& g : ctx.graphs)
+            if (g.exec && g.key == key) slot = &g;
+        if (!slot) {
+            slot = &ctx.graphs[0];
+            for (auto& g : ctx.graphs)
+                if (!g.exec || g.last_used < slot->last_used) { slot = &g; if (!g.exec) break; }
+            if (slot->exec) { cudaGraphExecDestroy(slot->exec); slot->exec = nullptr; }
+            slot->key.clear();
+            cudaGraph_t graph = nullptr;
+            CU(cudaStreamBeginCapture(st0, cudaStreamCaptureModeThreadLocal));
+            const int rc = enqueue();
+            const cudaError_t ce = cudaStreamEndCapture(st0, &graph);
+            if (rc != 0 || ce != cudaSuccess || !graph) {
+                if (graph) cudaGraphDestroy(graph);
+                cudaGetLastError();
+                return rc != 0 ? rc : fail(std::string("rtc_render: cudaStreamEndCapture: ") + cudaGetErrorString(ce));
+            }
+            const cudaError_t ie = cudaGraphInstantiate(&slot->exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (ie != cudaSuccess) { slot->exec = nullptr; return fail(std::string("rtc_render: cudaGraphInstantiate: ") + cudaGetErrorString(ie)); }
+            slot->key = std::move(key);
+        }
+        slot->last_used = ++ctx.graph_clock;
+        CU(cudaEventRecord(ctx.ev[0], st0));
+        CU(cudaGraphLaunch(slot->exec, st0));
+        CU(cudaEventRecord(ctx.ev[1], st0));
+    } else {
+        CU(cudaEventRecord(ctx.ev[0], st0));
+        if (int rc = enqueue()) return rc;
+        CU(cudaEventRecord(ctx.ev[1], st0));
+    }
     CU(cudaStreamSynchronize(st0));
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, ctx.ev[0], ctx.ev[1]));
