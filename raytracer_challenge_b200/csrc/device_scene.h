@@ -21,6 +21,8 @@ constexpr int LBVH_MIN_ITEMS = 64;      // below this the host build costs micro
 constexpr int FEAT_TRANSPARENT = 1;  // some material has transparency != 0: n1/n2 replay needed
 constexpr int FEAT_CSG = 2;          // CSG items present
 constexpr int FEAT_GATES = 4;        // per-ray exact pre-tests: group boxes that must be evaluated exactly, cone guards
+constexpr int FEAT_ONEPASS = 16;     // transparent scene with a small BVH: the closest-hit walk also gathers the crossings the n1/n2 replay needs
+constexpr int ONEPASS_MAX_ITEMS = 512;  // (with more BVH items the walk over t < 0 that this needs for EVERY ray costs more than a second walk for the transparent hits)
 constexpr int FEAT_TALLY = 8;        // RTC_FLAG_PROFILE: count the work done (node visits, primitive tests, ...); off, the counters and
                                      // their registers do not exist in the kernel
 

@@ -482,6 +482,98 @@ __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, doub
     return v.best;
 }
 
+// ---- closest hit AND the crossings before it, in one walk (FEAT_ONEPASS) ------------------------------------------
+// Intersection::prepare_state derives n1 / n2 from EVERY crossing of the ray's line up to the hit, those behind the origin
+// included (src/intersection.rs:70-103).  The two-pass form walks once for the closest hit (t >= 0 only) and, for hits on
+// transparent shapes, a second time for that list.  Here one walk without a lower bound on t does both: every crossing
+// not beyond the nearest hit found so far is kept in `out`, and whenever the list fills up the entries the hit has since
+// overtaken are dropped.  The hit cannot move further away, so a crossing at t <= t_hit is never discarded or culled.
+template <int FEAT>
+struct ClosestCollectVisitor {
+    static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
+    Query<FEAT> q;
+    Hit best;
+    Cross* out;
+    int n;
+    bool full;
+    __device__ __forceinline__ ClosestCollectVisitor(const Scene& sc, const Ray& ray, Cross* list, Tally& tl, int* ovf) : q(sc, ray, tl, ovf, false), out(list), n(0), full(false) {
+        best.t = 0.0; best.prim = -1; best.u = 0.0; best.v = 0.0;
+    }
+    __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : CUDART_INF; }
+    __device__ __forceinline__ void take(double t, int prim, double u, double v) {
+        if (best.prim < 0 || t <= best.t) {
+            if (n == MAX_CROSSINGS && best.prim >= 0) {  // drop what the hit has overtaken
+                int k = 0;
+                for (int i = 0; i < n; ++i)
+                    if (out[i].t <= best.t) out[k++] = out[i];
+                n = k;
+            }
+            if (n == MAX_CROSSINGS) full = true;
+            else { out[n].t = t; out[n].prim = prim; n++; }
+        }
+        if (t >= 0.0 && (best.prim < 0 || t < best.t || (t == best.t && prim < best.prim))) {
+            best.t = t; best.prim = prim; best.u = u; best.v = v;
+        }
+    }
+    __device__ __forceinline__ bool take_roots(const Roots& r, int id) {
+        for (int k = 0; k < r.n; ++k) take(r.t[k], id, r.u, r.v);
+        return full;
+    }
+    __device__ __forceinline__ bool csg(int root) {
+        CsgCall c;
+        csg_call<FEAT>(q, root, c);
+        if (c.n < 0) return true;
+        bool first = true;
+        for (int k = 0; k < c.n; ++k) {
+            double u = 0.0, v = 0.0;
+            if (first && c.list[k].t >= 0.0) {  // the list is sorted: the first non-negative entry is the only one that can be this item's hit
+                first = false;
+                const Prim p = load_prim(q.sc, c.list[k].prim);
+                if ((p.kind_flags & 0xff) >= 5) {  // triangle: recover (u, v)
+                    Roots r;
+                    prim_roots<0>(q.sc, p, q.ray, q.cache, q.counters(), false, r);
+                    u = r.u; v = r.v;
+                }
+            }
+            take(c.list[k].t, c.list[k].prim, u, v);
+        }
+        return full;
+    }
+    __device__ __forceinline__ bool item(int id) {
+        if ((FEAT & FEAT_CSG) && id < 0) return csg(~id);
+        Roots r;
+        q.roots_of_prim(id, r);
+        return take_roots(r, id);
+    }
+    __device__ __forceinline__ bool plane(const FastPlane& p) {
+        double oy, dy;
+        q.counters().prims++;
+        if (!plane_fraction(p.row[0], p.row[1], p.row[2], p.row[3], q.ray, false, oy, dy)) return false;
+        const bool behind = (oy > 0.0 && dy > 0.0) || (oy < 0.0 && dy < 0.0);  // t < 0: always wanted
+        if (!behind && plane_certainly_above(oy, dy, tmax())) return false;
+        take(-oy / dy, p.prim, 0.0, 0.0);
+        return full;
+    }
+    __device__ __forceinline__ bool leaf(int slot) {
+        const LeafItem li = load_leaf(q.sc, slot);
+        if ((FEAT & FEAT_CSG) && li.id < 0) return csg(~li.id);
+        Roots r;
+        q.roots_of_leaf(li, slot, r);
+        return take_roots(r, li.id);
+    }
+};
+
+// Returns the closest hit; xs[0..n_xs) holds (a superset of) the crossings with t <= hit.t, unsorted.
+template <int FEAT>
+__device__ __forceinline__ Hit closest_hit_collect(const Scene& sc, const Ray& ray, bool brute, Cross* xs, int& n_xs, Tally& tally, int* overflow) {
+    brute = brute || near_cone_slope<FEAT>(sc, ray);
+    ClosestCollectVisitor<FEAT> v(sc, ray, xs, tally, overflow);
+    if (!visit_unbounded(sc, v)) walk_bvh(sc, ray, 1, brute, v, tally);
+    if (v.full) *overflow = 1;
+    n_xs = v.n;
+    return v.best;
+}
+
 // ---- shadow query: World::is_shadowed (src/world.rs:26-48) -------------------------------------------
 template <int FEAT>
 struct AnyVisitor {
@@ -617,23 +709,17 @@ struct CollectVisitor {
     }
 };
 
-struct IndexCall {
-    Ray ray;
+// The container walk of Intersection::prepare_state (src/intersection.rs:70-103) over xs[0..n): sorts the crossings the way
+// the reference's stable sort leaves them (by t, ties in depth-first primitive order) and replays the list.
+struct IndexResult {
     double n1, n2;
-    Tally tally;
 };
-template <int FEAT>
-__device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit_t, int hit_prim, bool brute, int* overflow, IndexCall* call) {
-    const Ray ray = call->ray;
-    brute = brute || near_cone_slope<FEAT>(sc, ray);
-    Tally tally = {0u, 0u, 0u, 0u};
-    double n1, n2;
-    Cross xs[MAX_CROSSINGS];
-    CollectVisitor<FEAT> v(sc, ray, hit_t, xs, tally, overflow);
-    visit_unbounded(sc, v);
-    walk_bvh(sc, ray, 1, brute, v, tally);
-    const int n = v.n;
-    for (int i = 1; i < n; ++i) {  // order of the reference's sorted list: by t, ties in depth-first primitive order
+__device__ __noinline__ void replay_containers(const Scene& sc, Cross* xs, int n, double hit_t, int hit_prim, int* overflow, IndexResult* res) {
+    int m = 0;
+    for (int i = 0; i < n; ++i)  // (a one-pass list may still hold crossings the hit has overtaken)
+        if (xs[i].t <= hit_t) xs[m++] = xs[i];
+    n = m;
+    for (int i = 1; i < n; ++i) {
         const Cross c = xs[i];
         int j = i - 1;
         while (j >= 0 && (xs[j].t > c.t || (xs[j].t == c.t && xs[j].prim > c.prim))) { xs[j + 1] = xs[j]; --j; }
@@ -641,8 +727,7 @@ __device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit
     }
     int open[MAX_CONTAINERS];
     int no = 0;
-    n1 = 1.0;
-    n2 = 1.0;
+    double n1 = 1.0, n2 = 1.0;
     for (int i = 0; i < n; ++i) {
         const bool is_hit = xs[i].t == hit_t && xs[i].prim == hit_prim;  // Intersection::eq, src/intersection.rs:135-139
         if (is_hit) n1 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
@@ -658,8 +743,28 @@ __device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit
         }
         if (is_hit) n2 = no ? sc.materials[sc.prims[open[no - 1]].material].refractive_index : 1.0;
     }
-    call->n1 = n1;
-    call->n2 = n2;
+    res->n1 = n1;
+    res->n2 = n2;
+}
+
+struct IndexCall {
+    Ray ray;
+    double n1, n2;
+    Tally tally;
+};
+template <int FEAT>
+__device__ __noinline__ void refractive_indices_body(const Scene& sc, double hit_t, int hit_prim, bool brute, int* overflow, IndexCall* call) {
+    const Ray ray = call->ray;
+    brute = brute || near_cone_slope<FEAT>(sc, ray);
+    Tally tally = {0u, 0u, 0u, 0u};
+    Cross xs[MAX_CROSSINGS];
+    CollectVisitor<FEAT> v(sc, ray, hit_t, xs, tally, overflow);
+    visit_unbounded(sc, v);
+    walk_bvh(sc, ray, 1, brute, v, tally);
+    IndexResult res;
+    replay_containers(sc, xs, v.n, hit_t, hit_prim, overflow, &res);
+    call->n1 = res.n1;
+    call->n2 = res.n2;
     call->tally = tally;
 }
 // Out of line, over copies of the ray and the tallies (see roots_generic in device_math.cuh).

@@ -232,6 +232,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
     // of children off the queue counters).
     constexpr bool TALLY = (FEAT & FEAT_TALLY) != 0;
     constexpr bool SPLIT = (FEAT & FEAT_TRANSPARENT) != 0;
+    constexpr bool ONEPASS = (FEAT & FEAT_ONEPASS) != 0;  // the closest-hit walk gathers the crossings of the n1 / n2 replay (device_trace.cuh)
+    Cross xs[ONEPASS ? MAX_CROSSINGS : 1];
+    int n_xs = 0;
     uint32_t c_active = 0, longest = 0, c_refl = 0, c_refr = 0;
     Tally tally = {0u, 0u, 0u, 0u};
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n_round; idx += stride) {
@@ -248,7 +251,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
         if (active) {
             if (PRIMARY) c_active++;
             const uint32_t nodes_before = tally.nodes;
-            hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
+            if (ONEPASS) hit = closest_hit_collect<FEAT>(sc, ray, brute, xs, n_xs, tally, lv.overflow);
+            else hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
             if (TALLY) longest = max(longest, tally.nodes - nodes_before);
             if (hit.prim >= 0) {
                 const Prim prim = load_prim(sc, hit.prim);
@@ -257,8 +261,14 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
                 const Material& mat = sc.materials[prim.material];
                 const double reflective = mat.reflective, transparency = mat.transparency;
                 double n1 = 1.0, n2 = 1.0;
-                if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0)
-                    refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, tally, lv.overflow);
+                if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) {
+                    if (ONEPASS) {
+                        IndexResult res;
+                        replay_containers(sc, xs, n_xs, hit.t, hit.prim, lv.overflow, &res);
+                        n1 = res.n1;
+                        n2 = res.n2;
+                    } else refractive_indices<FEAT>(sc, ray, hit.t, hit.prim, brute, n1, n2, tally, lv.overflow);
+                }
                 s = surface_at(sc, prim, ray, hit.t, hit.u, hit.v);
                 if ((FEAT & FEAT_TRANSPARENT) && transparency != 0.0) reflectance = schlick(s.eye, s.normal, n1, n2);
                 // With no light World::shade_hit adds nothing at all (src/world.rs:58): the children would be traced for nothing.
@@ -538,9 +548,14 @@ static void launch_trace_feat(bool primary, int grid, cudaStream_t st, const Sce
 }
 template <int TALLY>
 static void launch_trace_tally(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
-    if (feat & (FEAT_CSG | FEAT_GATES)) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES | TALLY>(primary, grid, st, sc, f, lv, hl);
-    else if (feat & FEAT_TRANSPARENT) launch_trace_feat<FEAT_TRANSPARENT | TALLY>(primary, grid, st, sc, f, lv, hl);
-    else launch_trace_feat<TALLY>(primary, grid, st, sc, f, lv, hl);
+    const bool onepass = (feat & FEAT_ONEPASS) != 0;
+    if (feat & (FEAT_CSG | FEAT_GATES)) {
+        if (onepass) launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES | FEAT_ONEPASS | TALLY>(primary, grid, st, sc, f, lv, hl);
+        else launch_trace_feat<FEAT_TRANSPARENT | FEAT_CSG | FEAT_GATES | TALLY>(primary, grid, st, sc, f, lv, hl);
+    } else if (feat & FEAT_TRANSPARENT) {
+        if (onepass) launch_trace_feat<FEAT_TRANSPARENT | FEAT_ONEPASS | TALLY>(primary, grid, st, sc, f, lv, hl);
+        else launch_trace_feat<FEAT_TRANSPARENT | TALLY>(primary, grid, st, sc, f, lv, hl);
+    } else launch_trace_feat<TALLY>(primary, grid, st, sc, f, lv, hl);
 }
 // feat: the scene's FEAT_* bits, plus FEAT_TALLY when the caller wants the work counted
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {

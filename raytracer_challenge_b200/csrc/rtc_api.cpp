@@ -532,6 +532,7 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
         }
     }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
+    if ((s->feat & rtcdev::FEAT_TRANSPARENT) && h.n_bvh_items <= rtcdev::ONEPASS_MAX_ITEMS && !std::getenv("RTC_TWO_PASS")) s->feat |= rtcdev::FEAT_ONEPASS;
     return 0;
 }
 
