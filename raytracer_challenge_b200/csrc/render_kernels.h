@@ -14,7 +14,7 @@
 #define RTC_SHADOW_MIN_BLOCKS 8
 #endif
 #ifndef RTC_TRACE_MIN_BLOCKS_TRANSPARENT  // the n1/n2 replay keeps more state alive: trade occupancy for no spills
-#define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 3
+#define RTC_TRACE_MIN_BLOCKS_TRANSPARENT 4  // (r02i sweep with the one-pass walk: 4 blocks = 128 registers beats 3 and 5 on the glass scenes)
 #endif
 #ifndef RTC_TRACE_MIN_BLOCKS_CSG  // CSG evaluation on top of that
 #define RTC_TRACE_MIN_BLOCKS_CSG 3
