@@ -210,6 +210,8 @@ def run_cuda_inner(args):
         _build.build_driver()
     torch.cuda.set_device(local)
     if world > 1:
+        # one process per GPU: the ranks build their scenes at the same time and share the host cores
+        R.set_tuning(build_threads=max((os.cpu_count() or world) // world, 1))
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))

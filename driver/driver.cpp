@@ -105,7 +105,7 @@ int drv_render_device(void* h, const rtc_opts* opts, double** dev, uint64_t* n, 
 // render into the caller's host buffer (rtc_render: kernels + device->host copy), release (rtc_scene_destroy).
 int drv_e2e_step(void* h, int device, const rtc_opts* opts, double* out_rgb, rtc_stats* stats, char* err, int errlen) {
     Session* s = (Session*)h;
-    const rtc_scene_desc d = s->flat->desc(std::getenv("RTC_E2E_HOST_BVH") ? 0u : RTC_BUILD_FAST);  // as Image::par_render does
+    const rtc_scene_desc d = s->flat->desc(RTC_BUILD_FAST);  // as Image::par_render does (rtc_tuning.bvh_builder = 2 forces the host build)
     rtc_scene* scene = nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     if (rtc_scene_create(&d, device, &scene) != 0) { set_err(err, errlen, rtc_last_error()); return 1; }

@@ -275,6 +275,30 @@ int rtc_host_unregister(void* p);
 enum rtc_microbench_kind { RTC_MB_FP64_FMA = 0, RTC_MB_FP64_MUL_ADD = 1, RTC_MB_FP32_FMA = 2, RTC_MB_FP32_MUL_ADD = 3, RTC_MB_L2_READ = 4 };
 int rtc_microbench(int what, double* result);
 
+/* Tuning knobs and test hooks of the library, process-wide, set explicitly (the library reads no environment variable for
+ * them; RTC_TRACE / RTC_TIMELINE print debugging timelines and change nothing else).  Every field: 0 = the library's
+ * default.  None of them changes a pixel — they move work between batches, streams, builders and kernel variants. */
+typedef struct rtc_tuning {
+    int32_t batches;          /* aim for this many batches per rtc_render call (default 4 device-resident, 10 when copying out) */
+    int32_t batch_samples;    /* ... or fix the samples per batch */
+    int32_t pipes;            /* batch pipelines (CUDA streams) in flight, 1..8 (default 4) */
+    int32_t blocks_per_sm;    /* grid size of the wavefront kernels = SMs x this (default 16) */
+    int32_t no_taper;         /* 1: equal batches even when each finished batch is copied to the host */
+    int32_t no_copy_stream;   /* 1: copy a finished batch out on its own pipeline's stream */
+    int32_t no_stream_priorities; /* 1: equal stream priorities for host-output renders */
+    int32_t no_graphs;        /* 1: enqueue every frame launch by launch instead of replaying a captured CUDA graph */
+    int32_t no_fast_planes;   /* 1: always-tested planes go through the general primitive list, not the kernel parameters */
+    int32_t no_plain_shade;   /* 1: scenes of plain-colour materials still use the pattern evaluator's kernel */
+    int32_t two_pass;         /* 1: transparent hits re-walk the scene for their n1 / n2 crossing list (no one-pass collection) */
+    int32_t lbvh_leaf;        /* device-built BVH: items per leaf, 1..4 (default 1) */
+    int32_t bvh_builder;      /* 0: as rtc_scene_desc.build_flags says; 1: device (LBVH) whenever possible; 2: host (binned SAH) always */
+    int32_t build_threads;    /* host BVH build: threads it may use (default: all cores; one process per GPU should pass cores / ranks) */
+    int32_t sah_leaf_weight_x100, sah_bins, sah_small_node; /* host SAH build: leaf cost x 100 (default 300), bins 2..16 (16), exact-sweep size 2..8 (8) */
+    int32_t reserved[15];
+} rtc_tuning;
+void rtc_set_tuning(const rtc_tuning* tuning); /* NULL: back to the defaults */
+void rtc_get_tuning(rtc_tuning* out);
+
 /* Thread-local message for the last non-zero status. */
 const char* rtc_last_error(void);
 

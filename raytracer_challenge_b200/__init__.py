@@ -19,6 +19,11 @@ from .binding import (  # noqa: F401
     free_pinned,
     microbench,
     par_render_multi,
+    set_tuning,
+    tuning,
+    Tuning,
+    BVH_DEVICE,
+    BVH_HOST,
     FLAG_BRUTE_FORCE,
     FLAG_PROFILE,
     FLAG_SCATTER_ROWS,

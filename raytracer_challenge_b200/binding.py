@@ -52,6 +52,50 @@ class Stats(C.Structure):  # rtc_stats
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
 
 
+class Tuning(C.Structure):  # rtc_tuning
+    _fields_ = [(n, C.c_int32) for n in ("batches", "batch_samples", "pipes", "blocks_per_sm", "no_taper", "no_copy_stream", "no_stream_priorities",
+                                           "no_graphs", "no_fast_planes", "no_plain_shade", "two_pass", "lbvh_leaf", "bvh_builder", "build_threads",
+                                           "sah_leaf_weight_x100", "sah_bins", "sah_small_node")] + [("reserved", C.c_int32 * 15)]
+
+
+BVH_DEVICE, BVH_HOST = 1, 2  # rtc_tuning.bvh_builder
+# Harness convenience (tools/, sweeps): these environment variables are translated into rtc_set_tuning when the library is
+# loaded.  The library itself reads none of them.
+_ENV_TUNING = {"RTC_BATCHES": "batches", "RTC_BATCH_SAMPLES": "batch_samples", "RTC_PIPES": "pipes", "RTC_BLOCKS_PER_SM": "blocks_per_sm",
+               "RTC_NO_TAPER": "no_taper", "RTC_NO_COPY_STREAM": "no_copy_stream", "RTC_NO_STREAM_PRIORITIES": "no_stream_priorities",
+               "RTC_NO_GRAPHS": "no_graphs", "RTC_NO_FAST_PLANES": "no_fast_planes", "RTC_NO_PLAIN_SHADE": "no_plain_shade", "RTC_TWO_PASS": "two_pass",
+               "RTC_LBVH_LEAF": "lbvh_leaf", "RTC_BVH_BUILDER": "bvh_builder", "RTC_BUILD_THREADS": "build_threads",
+               "RTC_LEAF_WEIGHT_X100": "sah_leaf_weight_x100", "RTC_BINS": "sah_bins", "RTC_SMALL_NODE": "sah_small_node"}
+
+
+def set_tuning(**fields):
+    """rtc_set_tuning: process-wide knobs (0 / omitted = library default).  set_tuning() with no argument resets them."""
+    lib = load_rtc()
+    t = Tuning()
+    for k, v in fields.items():
+        setattr(t, k, int(v))
+    lib.rtc_set_tuning(C.byref(t) if fields else None)
+
+
+class tuning:
+    """with tuning(pipes=3, batch_samples=1024): ...   — knobs set for the block, defaults restored afterwards."""
+
+    def __init__(self, **fields):
+        self.fields = fields
+
+    def __enter__(self):
+        self.saved = Tuning()
+        load_rtc().rtc_get_tuning(C.byref(self.saved))
+        t = Tuning.from_buffer_copy(self.saved)
+        for k, v in self.fields.items():
+            setattr(t, k, int(v))
+        load_rtc().rtc_set_tuning(C.byref(t))
+        return self
+
+    def __exit__(self, *a):
+        load_rtc().rtc_set_tuning(C.byref(self.saved))
+
+
 STAT_KEYS = ["prims", "bvh_nodes", "bvh_depth", "unbounded", "gates_exact", "gates_conservative", "gates_always_pass",
              "csg_roots", "xforms", "features", "bvh_items", "device_bytes", "cone_guards"]
 
@@ -106,7 +150,12 @@ def load_rtc():
         lib.rtc_host_register.argtypes = [C.c_void_p, C.c_uint64]
         lib.rtc_host_unregister.argtypes = [C.c_void_p]
         lib.rtc_microbench.argtypes = [C.c_int, C.c_void_p]
+        lib.rtc_set_tuning.argtypes = [C.c_void_p]
+        lib.rtc_get_tuning.argtypes = [C.c_void_p]
         _rtc = lib
+        env = {field: int(os.environ[name]) for name, field in _ENV_TUNING.items() if os.environ.get(name)}
+        if env:
+            set_tuning(**env)
     return _rtc
 
 

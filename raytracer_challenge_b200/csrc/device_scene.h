@@ -12,6 +12,7 @@ constexpr int MAX_CSG_LIST = 48;        // crossings held while evaluating one t
 constexpr int MAX_CSG_MARKS = 8;        // CSG nesting depth
 constexpr int MAX_CROSSINGS = 64;       // crossings (t <= t_hit) replayed for n1/n2 (src/intersection.rs:70-103)
 constexpr int MAX_CONTAINERS = 24;      // simultaneously open shapes during that replay
+constexpr int MAX_TOP_NODES = 127;      // nodes 0 .. n_top-1 are the top of the tree in breadth-first order (7 levels): staged in shared memory (8 KB)
 constexpr int BVH_STACK = 64;           // a radix tree over unique 62-bit keys (30-bit Morton code, 32-bit item) is at most 62 deep
 constexpr int LBVH_ONE_BLOCK_ITEMS = 8192;  // device-side build (bvh_build.cu): up to here one block sorts the keys in shared memory
 constexpr int LBVH_MAX_ITEMS = 1 << 22;     // ... beyond, a multi-block radix sort (4 M items: scratch ~100 B per item)
@@ -152,6 +153,8 @@ struct Scene {
     int32_t max_children;    // max over materials of (reflective != 0) + (transparency != 0)
     int32_t n_guards;
     double root_lo[3], root_hi[3];  // f64 bounds of all BVH items (already padded)
+    int32_t n_top;                  // nodes [0, n_top) of bvh[] are numbered breadth-first from the root (0: unknown order, nothing is staged)
+    int32_t pad_top;
     int32_t n_fast_planes;          // > 0: fast_planes[] IS the always-tested list (unbounded[] is not read)
     int32_t plain_only;             // every material's pattern is Plain: shading needs no pattern evaluator
     FastPlane fast_planes[MAX_FAST_PLANES];

@@ -328,21 +328,22 @@ __device__ __forceinline__ void walk_descend(const Scene& sc, WalkCursor& c, Wal
     const Walk w = c.w;
     while (link >= 0) {
         if (TALLY) tally.nodes++;
-        float4 q0, q1, q2, q3;
-        if (link < n_top) {
-            const float4* q = reinterpret_cast<const float4*>(top + link);
-            q0 = q[0]; q1 = q[1]; q2 = q[2]; q3 = q[3];
-        } else {
-            const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
-            q0 = __ldg(q); q1 = __ldg(q + 1); q2 = __ldg(q + 2); q3 = __ldg(q + 3);
-        }
+#ifdef RTC_STAGE_TOP
+        // one load path for both homes of a node (generic addressing reaches shared and global memory alike; two separate
+        // paths cost the walk 12 % in registers and code)
+        const float4* q = reinterpret_cast<const float4*>(link < n_top ? top + link : sc.bvh + link);
+        const float4 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+#else
+        const float4* q = reinterpret_cast<const float4*>(sc.bvh + link);
+        const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+#endif
         float n0, n1;
         const bool h0 = slab(w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, thi, n0);
         const bool h1 = slab(w, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, thi, n1);
         const int c0 = __float_as_int(q3.x), c1 = __float_as_int(q3.y);
         if (h0 && h1) {
             const bool first0 = n0 <= n1;
-            stack.at[sp++] = first0 ? c1 : c0;
+            stack.at[sp++] = first0 ? c1 : c0;  // (prefetching the deferred child's line here changed nothing: r02i)
             link = first0 ? c0 : c1;
         } else if (h0) {
             link = c0;
@@ -376,13 +377,48 @@ __device__ __forceinline__ bool walk_leaf(const Scene& sc, WalkCursor& c, WalkSt
     return false;
 }
 
+// The first nodes of the tree (breadth-first: every walk starts there), staged in shared memory by the kernel.
+struct TopNodes {
+    const BvhNode* nodes = nullptr;
+    int n = 0;
+};
+
+// Built, measured, and off by default (RTC_STAGE_TOP): the top levels of a tree every walk starts in are L1-resident
+// anyway, and the staged walk loses the read-only path for the rest of the tree — teapot 3840x2160 5.03 -> 5.34 ms with
+// generic loads, 5.54 ms with separate shared / global load paths (profiles/README.md, r02i).
+// Stages the first sc.n_top nodes into `dst` (shared memory, 128-byte aligned, room for MAX_TOP_NODES) with ONE bulk
+// asynchronous copy (cp.async.bulk, the TMA's 1-D form; UBLKCP in SASS) completed through an mbarrier: thread 0 arms the
+// barrier with the byte count and issues the copy, every thread then waits for the barrier's phase to flip.
+// Call from all threads of the block, once, before the first query.
+__device__ __forceinline__ TopNodes stage_top_nodes(const Scene& sc, BvhNode* dst, unsigned long long* bar) {
+    TopNodes top;
+    if (sc.n_top <= 0) return top;  // (uniform over the grid)
+    const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(bar), dst_s = (uint32_t)__cvta_generic_to_shared(dst);
+    const uint32_t bytes = (uint32_t)sc.n_top * (uint32_t)sizeof(BvhNode);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(sc.bvh), "r"(bytes), "r"(bar_s) : "memory");
+    }
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar_s) : "memory");
+    top.nodes = dst;
+    top.n = sc.n_top;
+    return top;
+}
+
 template <class V>
-__device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v, Tally& tally) {
+__device__ __forceinline__ void walk_bvh(const Scene& sc, const Ray& ray, int mode, bool brute, V& v, Tally& tally, TopNodes top = TopNodes{}) {
     WalkCursor c;
     WalkStack stack;
     if (!walk_begin(sc, ray, mode, brute, v.tmax(), c)) return;
     for (;;) {
-        walk_descend<V::kTally>(sc, c, stack, tally, nullptr, 0);
+        walk_descend<V::kTally>(sc, c, stack, tally, top.nodes, top.n);
         if (c.link == WALK_DONE) return;
         if (walk_leaf(sc, c, stack, v)) return;
     }
@@ -474,11 +510,11 @@ struct ClosestVisitor {
 };
 
 template <int FEAT>
-__device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, Tally& tally, int* overflow) {
+__device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, double limit, bool brute, Tally& tally, int* overflow, TopNodes top = TopNodes{}) {
     brute = brute || near_cone_slope<FEAT>(sc, ray);
     ClosestVisitor<FEAT> v(sc, ray, limit, tally, overflow);
     visit_unbounded(sc, v);
-    walk_bvh(sc, ray, 0, brute, v, tally);
+    walk_bvh(sc, ray, 0, brute, v, tally, top);
     return v.best;
 }
 
@@ -565,10 +601,10 @@ struct ClosestCollectVisitor {
 
 // Returns the closest hit; xs[0..n_xs) holds (a superset of) the crossings with t <= hit.t, unsorted.
 template <int FEAT>
-__device__ __forceinline__ Hit closest_hit_collect(const Scene& sc, const Ray& ray, bool brute, Cross* xs, int& n_xs, Tally& tally, int* overflow) {
+__device__ __forceinline__ Hit closest_hit_collect(const Scene& sc, const Ray& ray, bool brute, Cross* xs, int& n_xs, Tally& tally, int* overflow, TopNodes top = TopNodes{}) {
     brute = brute || near_cone_slope<FEAT>(sc, ray);
     ClosestCollectVisitor<FEAT> v(sc, ray, xs, tally, overflow);
-    if (!visit_unbounded(sc, v)) walk_bvh(sc, ray, 1, brute, v, tally);
+    if (!visit_unbounded(sc, v)) walk_bvh(sc, ray, 1, brute, v, tally, top);
     if (v.full) *overflow = 1;
     n_xs = v.n;
     return v.best;
@@ -633,11 +669,11 @@ struct AnyVisitor {
 // Only instantiated for scenes where every primitive casts shadows: then "nearest t < dist" <=> "any t in
 // [0, dist)" and the walk may stop at the first such crossing.  (Scenes with non-casting shapes use closest_hit.)
 template <int FEAT>
-__device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, Tally& tally, int* overflow) {
+__device__ __forceinline__ bool any_hit(const Scene& sc, const Ray& ray, double dist, bool brute, Tally& tally, int* overflow, TopNodes top = TopNodes{}) {
     brute = brute || near_cone_slope<FEAT>(sc, ray);
     AnyVisitor<FEAT> v(sc, ray, dist, tally, overflow);
     if (visit_unbounded(sc, v)) return v.found;
-    walk_bvh(sc, ray, 0, brute, v, tally);
+    walk_bvh(sc, ray, 0, brute, v, tally, top);
     return v.found;
 }
 

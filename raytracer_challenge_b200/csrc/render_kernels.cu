@@ -232,6 +232,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
     // of children off the queue counters).
     constexpr bool TALLY = (FEAT & FEAT_TALLY) != 0;
     constexpr bool SPLIT = (FEAT & FEAT_TRANSPARENT) != 0;
+#ifdef RTC_STAGE_TOP
+    __shared__ __align__(128) BvhNode s_top[MAX_TOP_NODES + 1];
+    __shared__ unsigned long long s_top_bar;
+    const TopNodes top = stage_top_nodes(sc, s_top, &s_top_bar);
+#else
+    const TopNodes top{};
+#endif
     constexpr bool ONEPASS = (FEAT & FEAT_ONEPASS) != 0;  // the closest-hit walk gathers the crossings of the n1 / n2 replay (device_trace.cuh)
     Cross xs[ONEPASS ? MAX_CROSSINGS : 1];
     int n_xs = 0;
@@ -251,8 +258,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
         if (active) {
             if (PRIMARY) c_active++;
             const uint32_t nodes_before = tally.nodes;
-            if (ONEPASS) hit = closest_hit_collect<FEAT>(sc, ray, brute, xs, n_xs, tally, lv.overflow);
-            else hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow);
+            if (ONEPASS) hit = closest_hit_collect<FEAT>(sc, ray, brute, xs, n_xs, tally, lv.overflow, top);
+            else hit = closest_hit<FEAT>(sc, ray, CUDART_INF, brute, tally, lv.overflow, top);
             if (TALLY) longest = max(longest, tally.nodes - nodes_before);
             if (hit.prim >= 0) {
                 const Prim prim = load_prim(sc, hit.prim);
@@ -399,6 +406,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_TRACE_MIN_B
 template <int FEAT, bool ANYHIT>
 __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_BLOCKS_CSG : RTC_SHADOW_MIN_BLOCKS) trace_shadow(const __grid_constant__ Scene sc, const __grid_constant__ FrameParams f, const __grid_constant__ LevelParams lv, const __grid_constant__ HitList hl) {
     const bool brute = (f.flags & 1u) != 0;
+#ifdef RTC_STAGE_TOP
+    __shared__ __align__(128) BvhNode s_top[MAX_TOP_NODES + 1];
+    __shared__ unsigned long long s_top_bar;
+    const TopNodes top = stage_top_nodes(sc, s_top, &s_top_bar);
+#else
+    const TopNodes top{};
+#endif
     __shared__ HitRanges hr;  // (one copy per block: per-thread copies of the two small tables sat in local memory)
     __shared__ uint32_t s_hits;
     if (threadIdx.x == 0) s_hits = hit_ranges(hl, hr);
@@ -422,9 +436,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_
         bool shadowed = true;
         if (dot(sray.d, normal) >= 0.0) {
             if (ANYHIT) {
-                shadowed = any_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
+                shadowed = any_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow, top);
             } else {  // some shape does not cast shadows: the nearest crossing decides (src/world.rs:43-47)
-                const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow);
+                const Hit sh = closest_hit<FEAT>(sc, sray, distance, brute, tally, lv.overflow, top);
                 shadowed = sh.prim >= 0 && (__ldg(&sc.prims[sh.prim].kind_flags) & 0x100) != 0;
             }
         } else skipped++;

@@ -113,7 +113,14 @@ void free_pipe(Pipe& p) {
     p.q_capacity = p.hit_capacity = p.child_doubles = p.shadow_bytes = p.accum_samples = 0;
 }
 
-int env_int(const char* name, int fallback, int lo, int hi);
+// rtc_tuning (include/rtc.h): process-wide, set through rtc_set_tuning only
+std::mutex g_tuning_mu;
+rtc_tuning g_tuning{};
+rtc_tuning tuning_snapshot() {
+    std::lock_guard<std::mutex> lock(g_tuning_mu);
+    return g_tuning;
+}
+int knob(int32_t value, int fallback, int lo, int hi) { return value > 0 ? std::min(std::max((int)value, lo), hi) : fallback; }
 
 int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the device
     if (c.ready) return 0;
@@ -148,13 +155,6 @@ int ctx_init(DeviceCtx& c, int device) {  // caller holds c.mu and has set the d
     return 0;
 }
 
-int env_int(const char* name, int fallback, int lo, int hi) {
-    const char* v = std::getenv(name);
-    if (!v || !*v) return fallback;
-    const long x = std::strtol(v, nullptr, 10);
-    return (int)std::min<long>(std::max<long>(x, lo), hi);
-}
-
 }  // namespace
 
 namespace rtcapi {
@@ -164,6 +164,14 @@ int fail(const std::string& msg) { return ::fail(msg); }
 extern "C" {
 
 const char* rtc_last_error(void) { return g_error.c_str(); }
+
+void rtc_set_tuning(const rtc_tuning* t) {
+    std::lock_guard<std::mutex> lock(g_tuning_mu);
+    g_tuning = t ? *t : rtc_tuning{};
+}
+void rtc_get_tuning(rtc_tuning* out) {
+    if (out) *out = tuning_snapshot();
+}
 
 int rtc_device_count(void) {
     int n = 0;
@@ -304,7 +312,8 @@ int64_t rtc_scene_stat(const rtc_scene* s, int key) {
 int rtc_scene_validate(const rtc_scene_desc* desc, int64_t* stats16) {
     if (!desc) return fail("rtc_scene_validate: null argument");
     rtchost::HostScene h;
-    const std::string err = rtchost::build_host_scene(*desc, h);
+    const rtc_tuning tune = tuning_snapshot();
+    const std::string err = rtchost::build_host_scene(*desc, h, &tune);
     if (!err.empty()) return fail("rtc_scene_validate: " + err);
     if (stats16)
         for (int k = 0; k < 16; ++k) stats16[k] = host_stat(h, k);
@@ -416,6 +425,7 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
 
 // Device half of rtc_scene_create: arena (reused from the device context when one is parked there), copy, pointers.
 static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
+    const rtc_tuning tune = tuning_snapshot();
     const int device = s->device;
     if (cudaSetDevice(device) != cudaSuccess) { err = "cudaSetDevice failed"; return 1; }
     DeviceCtx& c = g_ctx[device];
@@ -467,13 +477,15 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     d.n_bvh_items = h.n_bvh_items;
     d.n_csg_roots = (int32_t)h.csg_roots.size();
     d.bvh_root = h.bvh_root;
+    // host-built trees are numbered breadth-first at the top (Builder::compact): the kernels stage that prefix in shared memory
+    d.n_top = (!h.device_build && h.n_bvh_items > 0 && h.bvh_root >= 0) ? (int32_t)std::min<size_t>(h.bvh.size(), (size_t)rtcdev::MAX_TOP_NODES) : 0;
     d.all_cast_shadow = h.all_cast_shadow;
     d.max_children = h.max_children;
     for (int k = 0; k < 3; ++k) { d.root_lo[k] = h.root_lo[k]; d.root_hi[k] = h.root_hi[k]; }
     if (h.device_build) {  // build the BVH where the scene now lives (bvh_build.cu); the host only staged the item boxes
         rtcdev::LbvhArgs a{};
         a.n = h.n_bvh_items;
-        a.leaf_max = env_int("RTC_LBVH_LEAF", 1, 1, 4);  // (sweep: 1 is the robust choice, the f64 item tests cost more than a node visit)
+        a.leaf_max = knob(tune.lbvh_leaf, 1, 1, 4);  // (sweep: 1 is the robust choice, the f64 item tests cost more than a node visit)
         a.box = (const float4*)(base + p.o_box32);
         a.item_ids = (const int32_t*)(base + p.o_item_ids);
         a.prims = d.prims;
@@ -518,9 +530,9 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     d.n_fast_planes = 0;
     d.plain_only = 1;
     for (const rtcdev::Material& m : h.materials) d.plain_only = d.plain_only && (m.flags & 1) != 0;
-    if (std::getenv("RTC_NO_PLAIN_SHADE")) d.plain_only = 0;
+    if (tune.no_plain_shade) d.plain_only = 0;
     std::memset(d.fast_planes, 0, sizeof d.fast_planes);
-    if (!h.unbounded.empty() && h.unbounded.size() <= (size_t)rtcdev::MAX_FAST_PLANES && !std::getenv("RTC_NO_FAST_PLANES")) {
+    if (!h.unbounded.empty() && h.unbounded.size() <= (size_t)rtcdev::MAX_FAST_PLANES && !tune.no_fast_planes) {
         bool ok = true;
         for (int32_t id : h.unbounded) ok = ok && id >= 0 && (h.prims[id].kind_flags & 0xff) == RTC_PLANE && h.prims[id].gate_mask == 0u && h.prims[id].gate_mask_hi == 0u;
         if (ok) {
@@ -532,7 +544,7 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
         }
     }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
-    if ((s->feat & rtcdev::FEAT_TRANSPARENT) && h.n_bvh_items <= rtcdev::ONEPASS_MAX_ITEMS && !std::getenv("RTC_TWO_PASS")) s->feat |= rtcdev::FEAT_ONEPASS;
+    if ((s->feat & rtcdev::FEAT_TRANSPARENT) && h.n_bvh_items <= rtcdev::ONEPASS_MAX_ITEMS && !tune.two_pass) s->feat |= rtcdev::FEAT_ONEPASS;
     return 0;
 }
 
@@ -552,7 +564,8 @@ int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n
     }
     const auto t_build0 = std::chrono::steady_clock::now();
     auto host = std::make_shared<rtchost::HostScene>();
-    const std::string err = rtchost::build_host_scene(*desc, *host);
+    const rtc_tuning tune = tuning_snapshot();
+    const std::string err = rtchost::build_host_scene(*desc, *host, &tune);
     if (!err.empty()) return fail("rtc_scene_create: " + err);
     const auto t_build1 = std::chrono::steady_clock::now();
     PackedScene packed;
@@ -653,6 +666,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     for (int i = 12; i < 16; ++i)  // last row equals (0,0,0,1) only up to the rounding of the reference's inverse
         if (!(std::fabs(cam->transform_inv[i] - (i == 15 ? 1.0 : 0.0)) <= 1e-9)) return fail("rtc_render: camera transform is not affine");
 
+    const rtc_tuning tune = tuning_snapshot();
     CU(cudaSetDevice(s->device));
     DeviceCtx& ctx = g_ctx[s->device];
     std::lock_guard<std::mutex> lock(ctx.mu);
@@ -694,8 +708,8 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     // default: about RTC_BATCHES batches per call so the pipelines have something to overlap, within [256 Ki, 2 Mi]
     // samples (measured: more, smaller batches only add launches; fewer leave the deep levels' tails exposed).
     // 4 when the frame stays in HBM; 10 (tapered at the end) when each finished batch is copied out, so that the copies start earlier.
-    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)env_int("RTC_BATCHES", host_out ? 10 : 4, 1, 1024), 256u << 10), 2u << 20);
-    const uint64_t target_samples = (uint64_t)env_int("RTC_BATCH_SAMPLES", (int)auto_samples, 1024, 1 << 28);
+    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)knob(tune.batches, host_out ? 10 : 4, 1, 1024), 256u << 10), 2u << 20);
+    const uint64_t target_samples = (uint64_t)knob(tune.batch_samples, (int)auto_samples, 1024, 1 << 28);
     const uint64_t max_records = (uint64_t)24 << 20;  // records per queue
     uint64_t batch_samples = std::min(target_samples, std::max<uint64_t>(max_records / worst, 1));
     uint64_t batch_pixels = std::max<uint64_t>(batch_samples / f.spp / unit, 1) * unit;
@@ -720,7 +734,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     // (..., B, B/2, B/4, B/4): the exposed copy shrinks from 1/6 to 1/24 of the frame (teapot 4K: 0.6 -> 0.15 ms).
     std::vector<std::pair<uint64_t, uint64_t>> schedule;
     {
-        const bool taper = host_out != nullptr && env_int("RTC_TAPER", 1, 0, 1) != 0;
+        const bool taper = host_out != nullptr && !tune.no_taper;
         uint64_t at = 0;
         while (at < n_slots) {
             const uint64_t left = n_slots - at;
@@ -739,7 +753,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     }
     const uint64_t n_batches = schedule.size();
     const bool profile = (o.flags & RTC_FLAG_PROFILE) != 0;
-    const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)env_int("RTC_PIPES", 4, 1, MAX_PIPES), n_batches);
+    const int n_pipes = profile ? 1 : (int)std::min<uint64_t>((uint64_t)knob(tune.pipes, 4, 1, MAX_PIPES), n_batches);
     for (int p = 0; p < n_pipes; ++p)
         if (int rc = ensure_pipe(ctx.pipe[p], q_cap, hit_cap, hit_cap * (uint64_t)fan * 3, hit_cap * (uint64_t)std::max(L, 1), batch_samples)) return rc;
     if (n_out > ctx.out_pixels) {
@@ -757,12 +771,12 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         ctx.counter_batches = nb;
     }
 
-    const bool copy_on_own_stream = host_out != nullptr && env_int("RTC_COPY_STREAM", 1, 0, 1) != 0;
-    const bool staggered = host_out != nullptr && env_int("RTC_STREAM_PRIORITIES", 1, 0, 1) != 0;
+    const bool copy_on_own_stream = host_out != nullptr && !tune.no_copy_stream;
+    const bool staggered = host_out != nullptr && !tune.no_stream_priorities;
     for (Pipe& p : ctx.pipe) p.stream = staggered ? p.stream_staggered : p.stream_flat;
     cudaStream_t st0 = ctx.pipe[0].stream;
     const size_t counter_bytes = n_batches * COUNTERS_PER_BATCH * sizeof(unsigned long long);
-    const int grid_full = ctx.sm_count * env_int("RTC_BLOCKS_PER_SM", 16, 1, 32);
+    const int grid_full = ctx.sm_count * knob(tune.blocks_per_sm, 16, 1, 32);
     const int feat = s->feat | (profile ? rtcdev::FEAT_TALLY : 0);  // the work tallies are counted under RTC_FLAG_PROFILE only
     uint64_t n_live = 0;
     for (const auto& b : schedule) n_live += b.second != 0;
@@ -897,7 +911,7 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     };  // enqueue
 
     // ---- replay a captured graph when the frame repeats ----
-    bool use_graph = !profile && !timeline && env_int("RTC_GRAPHS", 1, 0, 1) != 0;
+    bool use_graph = !profile && !timeline && !tune.no_graphs;
     if (use_graph && host_out) {  // (copies into pageable memory cannot be captured)
         cudaPointerAttributes attr{};
         if (cudaPointerGetAttributes(&attr, host_out) != cudaSuccess || attr.type != cudaMemoryTypeHost) { use_graph = false; cudaGetLastError(); }

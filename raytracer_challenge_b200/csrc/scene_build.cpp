@@ -173,17 +173,16 @@ struct Builder {
     int fork_levels = 4;         // the top levels of the tree fork a thread per left subtree (RTC_BUILD_FORK_LEVELS, 0 = sequential)
     std::atomic<int> depth{0};
 
-    Builder(const std::vector<Box>& boxes, double pad) {
-        if (const char* w = std::getenv("RTC_LEAF_WEIGHT")) leaf_weight = (float)std::max(0.1, std::atof(w));
-        {   // one process per GPU (torchrun sets LOCAL_WORLD_SIZE): the ranks of a node build at the same time, share the cores
+    Builder(const std::vector<Box>& boxes, double pad, const rtc_tuning& tune) {
+        if (tune.sah_leaf_weight_x100 > 0) leaf_weight = std::max(0.1f, (float)tune.sah_leaf_weight_x100 / 100.0f);
+        {   // thread budget: all cores unless the caller says otherwise (one process per GPU: the ranks of a node build at the same time)
             int cores = (int)std::thread::hardware_concurrency();
-            if (const char* w = std::getenv("LOCAL_WORLD_SIZE")) cores /= std::max(1, std::atoi(w));
+            if (tune.build_threads > 0) cores = tune.build_threads;
             fork_levels = 0;
             while (fork_levels < 4 && (2 << fork_levels) <= cores) fork_levels++;
         }
-        if (const char* w = std::getenv("RTC_BINS")) max_bins = std::min(16, std::max(2, std::atoi(w)));
-        if (const char* w = std::getenv("RTC_SMALL_NODE")) small_node = std::min(8, std::max(2, std::atoi(w)));
-        if (const char* w = std::getenv("RTC_BUILD_FORK_LEVELS")) fork_levels = std::min(8, std::max(0, std::atoi(w)));
+        if (tune.sah_bins > 0) max_bins = std::min(16, std::max(2, (int)tune.sah_bins));
+        if (tune.sah_small_node > 0) small_node = std::min(8, std::max(2, (int)tune.sah_small_node));
         items.resize(boxes.size());
         for (size_t i = 0; i < boxes.size(); ++i) {
             alignas(16) float lo[4] = {0.f, 0.f, 0.f, 0.f}, hi[4] = {0.f, 0.f, 0.f, 0.f}, c[4];
@@ -378,29 +377,48 @@ struct Builder {
         return finish(begin, mid, end, level, lb, rb);
     }
     // depth-first renumbering of the sparse slots into a dense array; returns the new root link
+    // Renumbering of the sparse slots into a dense array: the top of the tree breadth-first (the first MAX_TOP_NODES
+    // indices are what the kernels stage in shared memory: every walk starts there), the subtrees below depth-first (a
+    // parent is followed by its left subtree).  Returns the new root link.
     int32_t compact(int32_t root) {
         if (root < 0) { nodes.clear(); return root; }
         std::vector<BvhNode> dense;
         dense.reserve(nodes.size());
-        std::vector<std::pair<int32_t, int32_t>> stack;  // (sparse slot, dense index)
+        std::vector<std::pair<int32_t, int32_t>> work;  // (sparse slot, dense index): a queue while the top is numbered, then a stack
+        size_t head = 0;
         dense.emplace_back();
-        stack.push_back({root, 0});
-        while (!stack.empty()) {
-            const auto [slot, at] = stack.back();
-            stack.pop_back();
+        work.push_back({root, 0});
+        auto emit = [&](int32_t slot, int32_t at, bool breadth_first) {
             BvhNode nd = nodes[(size_t)slot];
-            // children are numbered when their parent is written: left first, so the left subtree follows its parent
+            // children are numbered when their parent is written
             int32_t kids[2] = {nd.c0, nd.c1};
             int32_t dense_kids[2];
             for (int k = 0; k < 2; ++k) {
                 if (kids[k] >= 0) { dense_kids[k] = (int32_t)dense.size(); dense.emplace_back(); }
                 else dense_kids[k] = kids[k];
             }
-            if (kids[1] >= 0) stack.push_back({kids[1], dense_kids[1]});
-            if (kids[0] >= 0) stack.push_back({kids[0], dense_kids[0]});
+            if (breadth_first) {
+                if (kids[0] >= 0) work.push_back({kids[0], dense_kids[0]});
+                if (kids[1] >= 0) work.push_back({kids[1], dense_kids[1]});
+            } else {
+                if (kids[1] >= 0) work.push_back({kids[1], dense_kids[1]});
+                if (kids[0] >= 0) work.push_back({kids[0], dense_kids[0]});
+            }
             nd.c0 = dense_kids[0];
             nd.c1 = dense_kids[1];
             dense[(size_t)at] = nd;
+        };
+        while (head < work.size() && dense.size() < (size_t)rtcdev::MAX_TOP_NODES) {
+            const auto [slot, at] = work[head++];
+            emit(slot, at, true);
+        }
+        // what is still queued are the roots of the subtrees below the top: depth-first from here, leftmost first
+        std::vector<std::pair<int32_t, int32_t>> rest(work.begin() + (long)head, work.end());
+        work.assign(rest.rbegin(), rest.rend());
+        while (!work.empty()) {
+            const auto [slot, at] = work.back();
+            work.pop_back();
+            emit(slot, at, false);
         }
         nodes.swap(dense);
         return 0;
@@ -420,8 +438,10 @@ int32_t dedupe(std::map<std::string, int32_t>& index, std::vector<T>& store, con
 
 }  // namespace
 
-std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
+std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_tuning* tuning) {
     out = HostScene{};
+    rtc_tuning tune{};
+    if (tuning) tune = *tuning;
     if (d.abi_version != RTC_ABI_VERSION) return "abi_version mismatch";
     if (d.n_prims < 0 || d.n_nodes < 1 || d.n_children < 0 || d.n_materials < 0 || d.n_patterns < 0 || d.n_lights < 0)
         return "negative array length (or no root node)";
@@ -699,8 +719,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
         const double pad = 4e-6 * std::max(S, 1e-30);
         for (int k = 0; k < 3; ++k) { out.root_lo[k] = root.lo[k] - pad; out.root_hi[k] = root.hi[k] + pad; }
         const int n_items = (int)item_ids.size();
-        const bool fast = (d.build_flags & RTC_BUILD_FAST) != 0 || std::getenv("RTC_DEVICE_BVH") != nullptr;  // (the variable: tests and probes)
-        if (fast && n_items >= rtcdev::LBVH_MIN_ITEMS && n_items <= rtcdev::LBVH_MAX_ITEMS && !std::getenv("RTC_HOST_BVH")) {
+        const bool fast = ((d.build_flags & RTC_BUILD_FAST) != 0 || tune.bvh_builder == 1) && tune.bvh_builder != 2;
+        if (fast && n_items >= rtcdev::LBVH_MIN_ITEMS && n_items <= rtcdev::LBVH_MAX_ITEMS) {
             // The device builds the tree after the upload (bvh_build.cu): hand it the same padded fp32 item boxes the
             // host build would use, and the leaf records in item order.
             out.device_build = 1;
@@ -720,7 +740,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out) {
             if (trace) std::fprintf(stderr, "build_host_scene: prims %.3f ms, group tree %.3f ms, device-build staging %.3f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, now()));
             return "";
         }
-        Builder bld(item_boxes, pad);
+        Builder bld(item_boxes, pad, tune);
         out.bvh_root = bld.compact(bld.build(0, (int)item_ids.size(), 0, bld.range_bounds(0, (int)item_ids.size())));
         out.bvh = std::move(bld.nodes);
         out.bvh_depth = bld.depth;

@@ -45,6 +45,7 @@ struct HostScene {
 };
 
 // Returns "" on success, otherwise a description of why the scene was rejected.
-std::string build_host_scene(const rtc_scene_desc& desc, HostScene& out);
+// tuning: rtc_tuning (builder choice, thread budget, SAH parameters); null = defaults
+std::string build_host_scene(const rtc_scene_desc& desc, HostScene& out, const rtc_tuning* tuning = nullptr);
 
 }  // namespace rtchost

@@ -107,7 +107,14 @@ class SharedFrame:
         self.seq += 1
         self.flags[rank] = self.seq
         t0 = time.perf_counter()
+        spins = 0
+        # (plain aligned 8-byte loads / stores: relies on x86's total store order and on the rank's copies having completed
+        # — its render call has returned — before its flag is stored.  After a short spin the wait backs off so that it does
+        # not hold a core the other ranks' host work could use.)
         while int(self.flags[:world].min()) < self.seq:
+            spins += 1
+            if spins > 200:
+                time.sleep(20e-6)
             if time.perf_counter() - t0 > timeout_s:
                 raise TimeoutError("SharedFrame.frame_barrier: a rank did not arrive")
 

@@ -75,16 +75,18 @@ def test_no_cuda_device_is_an_error_not_a_fallback(built):
 
 
 @pytest.mark.parametrize("name,items,staged", [("teapot", 6320, True), ("benchmark", 1000, True), ("hexagon", 12, False)])
-def test_fast_build_stages_the_items_for_the_device_and_builds_no_host_tree(built, name, items, staged, monkeypatch):
-    """rtc_scene_desc.build_flags & RTC_BUILD_FAST (here through its test hook RTC_DEVICE_BVH): scenes with 64..8192 BVH
+def test_fast_build_stages_the_items_for_the_device_and_builds_no_host_tree(built, name, items, staged):
+    """rtc_scene_desc.build_flags & RTC_BUILD_FAST (here through rtc_tuning.bvh_builder = device): scenes with 64 or more BVH
     items leave the tree to the device (bvh_build.cu), so the host half reports no nodes; tiny scenes keep the host build."""
-    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
-    s = R.Session(name, 64, 36, device=-1)
-    b = s.build_stats
-    s.close()
+    with R.tuning(bvh_builder=R.BVH_DEVICE):
+        s = R.Session(name, 64, 36, device=-1)
+        b = s.build_stats
+        s.close()
     assert b["bvh_items"] == items
     assert (b["bvh_nodes"] == 0) == staged
-    monkeypatch.delenv("RTC_DEVICE_BVH")
+    t = R.Tuning()
+    R.load_rtc().rtc_get_tuning(C.byref(t))
+    assert t.bvh_builder == 0  # the block restored the defaults
     s = R.Session(name, 64, 36, device=-1)
     assert s.build_stats["bvh_nodes"] >= 1
     s.close()

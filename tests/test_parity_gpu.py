@@ -180,14 +180,16 @@ def test_profile_flag_and_work_tallies(built):
     assert (sa.rays, sa.rays_reflected, sa.rays_refracted, sa.surface_hits) == (sb.rays, sb.rays_reflected, sb.rays_refracted, sb.surface_hits)
 
 
-def test_repeated_renders_are_identical_and_batches_do_not_matter(built, monkeypatch):
+def test_repeated_renders_are_identical_and_batches_do_not_matter(built):
     with R.Session("teapot_low", 160, 90, device=0) as s:
         a, _ = s.render(R.Opts())
-        monkeypatch.setenv("RTC_BATCH_SAMPLES", "1024")
-        monkeypatch.setenv("RTC_PIPES", "3")
-        b, st = s.render(R.Opts())
-        assert st.kernel_launches > 19 * 4
-    assert np.array_equal(a, b)
+        with R.tuning(batch_samples=1024, pipes=3):
+            b, st = s.render(R.Opts())
+            assert st.kernel_launches > 19 * 4
+            with R.tuning(no_graphs=1):  # launch by launch instead of the captured graph
+                c, _ = s.render(R.Opts())
+        d, _ = s.render(R.Opts())
+    assert np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d)
 
 
 def test_ppm_through_the_host_api(built):
@@ -286,30 +288,28 @@ def test_full_size_teapot_properties(built):
 
 
 @pytest.mark.parametrize("name", ["teapot_low", "chapter11_title", "glass_air_bubble", "three_spheres"])
-def test_planes_in_kernel_parameters_equal_the_general_list(built, name, monkeypatch):
+def test_planes_in_kernel_parameters_equal_the_general_list(built, name):
     """Scenes whose always-tested list is ungated planes keep them in the kernel parameters (device_scene.h,
-    FastPlane); RTC_NO_FAST_PLANES forces the general unbounded[] -> prims[] -> xforms[] walk.  Same expressions, so the
+    FastPlane); rtc_tuning.no_fast_planes forces the general unbounded[] -> prims[] -> xforms[] walk.  Same expressions, so the
     frames must be bit-identical (up to the order of the atomic adds where one pixel has several nodes in a level)."""
     w, h = 96, 54
     with R.Session(name, w, h, device=0) as s:
         fast, st = s.render(R.Opts())
-    monkeypatch.setenv("RTC_NO_FAST_PLANES", "1")
-    with R.Session(name, w, h, device=0) as s:
+    with R.tuning(no_fast_planes=1), R.Session(name, w, h, device=0) as s:
         general, st2 = s.render(R.Opts())
     assert same_pixels(name, fast, general)
     assert (st.rays, st.surface_hits) == (st2.rays, st2.surface_hits)
 
 
 @pytest.mark.parametrize("name,w,h", [("teapot_low", 96, 54), ("benchmark", 96, 54), ("chapter14_title", 96, 54), ("teapot", 160, 90), ("fuzz:3", 96, 54)])
-def test_device_built_bvh_renders_the_same_frame(built, name, w, h, monkeypatch):
+def test_device_built_bvh_renders_the_same_frame(built, name, w, h):
     """RTC_BUILD_FAST (what Image::par_render passes: the scene lives for one frame) builds the BVH on the device
     (bvh_build.cu, LBVH) instead of the host's binned-SAH build.  A BVH only culls: the frame must equal the SAH
     build's and the brute-force scan's bit for bit."""
     with R.Session(name, w, h, device=0) as s:
         sah, st = s.render(R.Opts())
         host_stats = dict(s.build_stats)
-    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
-    with R.Session(name, w, h, device=0) as s:
+    with R.tuning(bvh_builder=R.BVH_DEVICE), R.Session(name, w, h, device=0) as s:
         lbvh, st2 = s.render(R.Opts())
         brute, _ = s.render(R.Opts(flags=1))
         dev_stats = dict(s.build_stats)
@@ -321,7 +321,7 @@ def test_device_built_bvh_renders_the_same_frame(built, name, w, h, monkeypatch)
 
 
 # ---- capacity: scenes beyond the sizes the example binaries need ---------------------------------------------------------
-def test_hundred_thousand_triangle_mesh_on_the_device_built_bvh(built, monkeypatch):
+def test_hundred_thousand_triangle_mesh_on_the_device_built_bvh(built):
     """src/obj.rs has no size limit.  teapot_high tessellated to 101 120 smooth triangles: the device-side build sorts its
     Morton keys with the multi-block radix sort (bvh_build.cu) instead of the one-block sort; windows on the mesh equal
     the oracle, the host-built SAH tree and the brute-force scan."""
@@ -330,8 +330,7 @@ def test_hundred_thousand_triangle_mesh_on_the_device_built_bvh(built, monkeypat
     with R.Session("teapot_tess", w, h, device=0) as s:
         host_stats = dict(s.build_stats)
         sah = [s.render(R.Opts(window=win))[0] for win in windows]
-    monkeypatch.setenv("RTC_DEVICE_BVH", "1")
-    with R.Session("teapot_tess", w, h, device=0) as s:
+    with R.tuning(bvh_builder=R.BVH_DEVICE), R.Session("teapot_tess", w, h, device=0) as s:
         dev_stats = dict(s.build_stats)
         for win, want in zip(windows, sah):
             img, st = s.render(R.Opts(window=win))
