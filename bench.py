@@ -331,6 +331,8 @@ def run_cuda_inner(args):
     # Image's pixels, rtc_scene_destroy).  With N > 1 ranks only rank 0 runs it, over devices 0..N-1, while the others wait.
     par = None
     barrier()
+    if world > 1:
+        frame.frame_barrier(rank, world)
     if rank == 0:
         probe = (C.c_double * 3)()
         phases = (C.c_double * 2)()
@@ -357,6 +359,10 @@ def run_cuda_inner(args):
                "h2d_bytes_per_step": int(sess.build_stats["device_bytes"]) * world, "d2h_bytes_per_step": d2h,
                "path": f"rtc::Image::par_render(camera, world) (host/raytracer.hpp, the C++ mirror of the Rust call): FlatScene(world) + rtc_scene_create_multi + rtc_render_multi over {world} GPU(s) from ONE process "
                        "into a pooled page-locked frame that becomes Image.pixels + rtc_scene_destroy, per step; the World itself (OBJ parse, builders) is built once, outside"}
+    if world > 1:
+        # the other ranks wait HERE, on the host-side counters of the shared frame: an NCCL barrier would park a spinning kernel on
+        # every GPU that rank 0 is rendering on
+        frame.frame_barrier(rank, world, timeout_s=600.0)
     barrier()
 
     line = None
