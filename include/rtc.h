@@ -192,7 +192,10 @@ int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n
 
 void rtc_scene_destroy(rtc_scene* scene);
 
-/* Blocking render into caller-allocated host memory: out_rgb holds one (r,g,b) f64 triple per
+/* One render at a time per device: the library keeps one render context per GPU (streams, scratch pools, cached CUDA graphs)
+ * behind a mutex, so concurrent calls on the same device serialise; calls on different devices run concurrently.
+ *
+ * Blocking render into caller-allocated host memory: out_rgb holds one (r,g,b) f64 triple per
  * output slot (see rtc_shard_pixels; shard_count == 1: the whole window row-major, `y*w + x`, like
  * Image.pixels, src/image.rs:114-116).
  * Replaces the body of Image::par_render (src/image.rs:65-81).  0 = ok. */

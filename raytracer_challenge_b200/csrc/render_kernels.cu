@@ -187,9 +187,8 @@ __device__ __forceinline__ uint32_t hit_ranges(const HitList& hl, HitRanges& hr)
     hr.first[hr.n] = total;
     return total;
 }
-__device__ __forceinline__ size_t hit_at(const HitRanges& hr, uint32_t j) {
-    const int half = hr.n >> 1;
-    int r = j >= hr.first[half] ? half : 0;  // front bins of all levels, then back bins
+// r: the range the caller's previous (smaller) index fell into — a thread's indices only grow, so the search resumes there
+__device__ __forceinline__ size_t hit_at(const HitRanges& hr, uint32_t j, int& r) {
     while (r + 1 < hr.n && j >= hr.first[r + 1]) ++r;
     const uint32_t k = j - hr.first[r];
     return r < (hr.n >> 1) ? (size_t)hr.base[r] + k : (size_t)hr.base[r] - k;
@@ -424,8 +423,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, (FEAT & FEAT_CSG) ? RTC_SHADOW_MIN_
     uint32_t skipped = 0;
     const Light& light = sc.lights[li];
     const V3 lpos = mk(light.origin[0], light.origin[1], light.origin[2]);
+    int range = 0;
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_hits; j += stride) {
-        const size_t at = hit_at(hr, j);
+        const size_t at = hit_at(hr, j, range);
         const double2 a = hl.a[at], b = hl.b[at], c = hl.c[at];
         const V3 over_point = mk(a.x, a.y, b.x), normal = mk(b.y, c.x, c.y);
         const V3 to_light = lpos - over_point;
