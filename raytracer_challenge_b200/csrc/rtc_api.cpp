@@ -306,6 +306,7 @@ int64_t rtc_scene_stat(const rtc_scene* s, int key) {
     if (!s || !s->host) return -1;
     if (s->bvh_depth >= 0 && key == RTC_STAT_BVH_DEPTH) return s->bvh_depth;  // device-side build: what the device reported
     if (s->bvh_nodes >= 0 && key == RTC_STAT_BVH_NODES) return s->bvh_nodes;
+    if (key == RTC_STAT_FEATURES) return s->feat;  // (an uploaded scene: incl. the kernel variant chosen, e.g. FEAT_ONEPASS)
     return host_stat(*s->host, key);
 }
 

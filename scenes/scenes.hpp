@@ -181,7 +181,15 @@ Scene<A> hexagon(size_t hsize, size_t vsize) {
 
 // --- C3b: src/bin/chapter14_benchmark.rs:15-109 (native 4096x2160) --------------------------
 template <class A>
-Scene<A> benchmark(size_t hsize, size_t vsize) {
+Scene<A> benchmark_with(size_t hsize, size_t vsize, bool glass);
+template <class A>
+Scene<A> benchmark(size_t hsize, size_t vsize) { return benchmark_with<A>(hsize, vsize, false); }
+// The same 1 000 spheres made of glass: a line through a row of the lattice crosses up to 2 x 5 x 2 x ... spheres — dozens to
+// hundreds of crossings per n1 / n2 replay, beyond the 64 the on-chip list holds (device_scene.h: BIG_CROSSINGS).
+template <class A>
+Scene<A> benchmark_glass(size_t hsize, size_t vsize) { return benchmark_with<A>(hsize, vsize, true); }
+template <class A>
+Scene<A> benchmark_with(size_t hsize, size_t vsize, bool glass) {
     using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
     using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
     Scene<A> s;
@@ -213,6 +221,7 @@ Scene<A> benchmark(size_t hsize, size_t vsize) {
     typename A::Material material;
     material.pattern = P::gradient(M::scaling(1.0, 2.9, 1.0) * M::rotation_z(PI / 2.0), P::plain(C::make(1.0, 0.0, 0.0)),
                                    P::plain(C::make(0.0, 0.0, 1.0)));
+    if (glass) { material.transparency = 0.8; material.refractive_index = 1.0; material.diffuse = 0.3; }  // index 1: rays go straight through the rows
     s.world.lights.push_back({C::white(), V::point(-5.0, 7.0, -1.0)});
     s.world.elements.push_back(E::plane(backdrop));
     s.world.elements.push_back(E::composite(M::id(), material, G::Aggregation, std::move(spheres)));
@@ -951,12 +960,35 @@ Scene<A> teapot_tess(size_t hsize, size_t vsize) {
     return teapot_from<A>(tessellate<A>(load_mesh_fixture<A>(data_dir() + "/teapot_high.mesh"), 2), hsize, vsize);
 }
 
+// --- authored: crossing lists beyond the usual on-chip sizes -------------------------------------------------------------
+// The camera sits inside 70 concentric glass shells: the line of every ray crosses all of them behind the camera, so the
+// n1 / n2 replay of a hit (src/intersection.rs:70-103) sees 70+ crossings and 70 open containers — beyond the 64 / 24 the
+// on-chip lists hold, inside what a slot of global scratch holds (device_scene.h: BIG_CROSSINGS, BIG_CONTAINERS).
+template <class A>
+Scene<A> glass_shells(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::translation(0.0, -8.0, 0.0),
+                                        material_with<A>(P::checkers(M::scaling(2.0, 2.0, 2.0), P::plain(C::make(0.9, 0.9, 0.9)), P::plain(C::make(0.2, 0.3, 0.2))), {{'s', 0.0}}))));
+    for (int k = 0; k < 70; k++) {
+        const double r = 1.0 + 0.05 * k;
+        el.push_back(E::sphere(shape_args<A>(M::scaling(r, r, r), material_with<A>(P::plain(C::make(0.2 + 0.15 * (k % 5), 0.9 - 0.1 * (k % 7), 0.5)),
+                                                                                      {{'a', 0.3}, {'d', 0.3}, {'s', 0.3}, {'h', 200.0}, {'r', (k % 9 == 0) ? 0.2 : 0.0}, {'t', 0.95}, {'i', 1.0 + 0.01 * (k % 13)}}))));
+    }
+    s.world.lights.push_back({C::make(0.9, 0.9, 0.9), V::point(10.0, 12.0, -10.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.2,
+                               A::Camera::transform(V::point(0.1, 0.05, -0.2), V::point(0.3, -0.6, 1.0), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
                                                "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope",
-                                               "axis_aligned", "no_shadow_flat", "many_gates"};
+                                               "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells"};
     return n;
 }
 
@@ -981,6 +1013,8 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "no_shadow_flat") return no_shadow_flat<A>(hsize, vsize);
     if (name == "many_gates") return many_gates<A>(hsize, vsize);
     if (name == "teapot_tess") return teapot_tess<A>(hsize, vsize);
+    if (name == "glass_shells") return glass_shells<A>(hsize, vsize);
+    if (name == "benchmark_glass") return benchmark_glass<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");
 }

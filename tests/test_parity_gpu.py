@@ -28,6 +28,7 @@ CASES = [
     ("axis_aligned", 48, 1),
     ("axis_aligned", 1, 1),
     ("axis_aligned", 65, 37),
+    ("benchmark_glass", 96, 54),        # the 1 000-sphere scene made of glass (two-pass form: > 512 BVH items): up to ~100 crossings on a line
     ("many_gates", 96, 54),             # 80 group boxes over finite cones: 64-bit gate masks, slots assigned after the subtree walk
     ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
@@ -345,3 +346,16 @@ def test_hundred_thousand_triangle_mesh_on_the_device_built_bvh(built):
     assert host_stats["bvh_items"] == 101120 and dev_stats["bvh_items"] == 101120
     assert 0 < dev_stats["bvh_nodes"] < 101120 and 3 <= dev_stats["bvh_depth"] <= 62
     assert dev_stats["device_bytes"] > host_stats["device_bytes"]  # the arena also holds the builder's scratch: the device path ran
+
+
+@pytest.mark.parametrize("two_pass", [0, 1])
+def test_replays_that_overflow_the_on_chip_lists_fail_loudly(built, two_pass):
+    """glass_shells: the camera sits inside 70 concentric glass shells, so every n1 / n2 replay sees 70+ crossings and up to 70
+    open containers — more than the on-chip lists hold (64 / 24, device_scene.h).  That is a capacity limit of this
+    implementation, not of the reference ("Capacity"): the call must FAIL with an error in both forms of the walk,
+    never return a wrong pixel.  (An in-kernel retry with lists in global scratch was built and measured: the mere presence
+    of the fallback code cost the transparent kernels 15-20 %, so it was not kept.)"""
+    with R.tuning(two_pass=two_pass), R.Session("glass_shells", 48, 27, device=0) as s:
+        assert bool(s.build_stats["features"] & 16) == (not two_pass)  # FEAT_ONEPASS
+        with pytest.raises(R.RtcError, match="overflow"):
+            s.render(R.Opts())
