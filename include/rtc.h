@@ -282,7 +282,7 @@ int rtc_microbench(int what, double* result);
  * them; RTC_TRACE / RTC_TIMELINE print debugging timelines and change nothing else).  Every field: 0 = the library's
  * default.  None of them changes a pixel — they move work between batches, streams, builders and kernel variants. */
 typedef struct rtc_tuning {
-    int32_t batches;          /* aim for this many batches per rtc_render call (default 4 device-resident, 10 when copying out) */
+    int32_t batches;          /* aim for this many batches per rtc_render call (default 4 device-resident, 14 when copying out) */
     int32_t batch_samples;    /* ... or fix the samples per batch */
     int32_t pipes;            /* batch pipelines (CUDA streams) in flight, 1..8 (default 4) */
     int32_t blocks_per_sm;    /* grid size of the wavefront kernels = SMs x this (default 16) */

@@ -708,8 +708,9 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     const uint64_t unit = row_major ? (uint64_t)f.tiles_x * per_tile : per_tile;  // batch granularity in pixel slots
     // default: about RTC_BATCHES batches per call so the pipelines have something to overlap, within [256 Ki, 2 Mi]
     // samples (measured: more, smaller batches only add launches; fewer leave the deep levels' tails exposed).
-    // 4 when the frame stays in HBM; 10 (tapered at the end) when each finished batch is copied out, so that the copies start earlier.
-    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)knob(tune.batches, host_out ? 10 : 4, 1, 1024), 256u << 10), 2u << 20);
+    // 4 when the frame stays in HBM; 14 (tapered at the end) when each finished batch is copied out, so that the copies start earlier
+    // (r02 sweep with graph replay, profiles/r02m_e2e_batch_sweep.txt: 14 x 4 pipelines 6.11 ms, 10 x 4 6.28 ms for the teapot frame).
+    const uint64_t auto_samples = std::min<uint64_t>(std::max<uint64_t>(n_slots * (uint64_t)f.spp / (uint64_t)knob(tune.batches, host_out ? 14 : 4, 1, 1024), 256u << 10), 2u << 20);
     const uint64_t target_samples = (uint64_t)knob(tune.batch_samples, (int)auto_samples, 1024, 1 << 28);
     const uint64_t max_records = (uint64_t)24 << 20;  // records per queue
     uint64_t batch_samples = std::min(target_samples, std::max<uint64_t>(max_records / worst, 1));

@@ -7,11 +7,12 @@ from raytracer_challenge_b200 import sharding
 W, H = 3840, 2160
 s = R.Session("teapot", W, H, device=0)
 frame, ptr = R.pinned_array((H, W, 3))
-for world in (1, 2, 4, 8):
+worlds = [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "1,2,4,8").split(",")]
+for world in worlds:
     opts = sharding.band_opts(W, 0, world)
-    for batches in (2, 3, 4, 6, 8, 10, 14):
-        for pipes in (3, 4):
-            os.environ["RTC_BATCHES"] = str(batches); os.environ["RTC_PIPES"] = str(pipes)
+    for batches in (4, 6, 8, 10, 14, 20, 28):
+        for pipes in (3, 4, 6, 8):
+            R.set_tuning(batches=batches, pipes=pipes)
             best = 1e9
             for rep in range(6):
                 t = time.perf_counter()
