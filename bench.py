@@ -372,10 +372,11 @@ def run_cuda_inner(args):
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text(),
-                       "sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
-                       "l2": "256 MiB device memset between timed frames (L2 flush); the per-level ray queues of a batch exceed L2 anyway",
-                       "scene": "device-resident arm: scene handle created once (host binned-SAH BVH), frames rendered from it; end-to-end arm: scene created and destroyed every step"},
+            # (the same three keys as the reference arm's line, so that the two arms' configs compare equal)
+            "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text()},
+            "run": {"sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
+                    "l2": "256 MiB device memset between timed frames (L2 flush); the per-level ray queues of a batch exceed L2 anyway",
+                    "scene": "device-resident arm: scene handle created once (host binned-SAH BVH), frames rendered from it; end-to-end arms: scene created and destroyed every step"},
             "frame_ms": ms_per_step, "wall_ms_per_step": wall_ms / args.steps,
             "rays_per_frame": rays_all / args.steps, "value_rays": "R_uniq: rays actually traced (secondary sub-trees deduplicated across lights)",
             "ref_equivalent_rays_per_frame": rays_ref_all / args.steps,
