@@ -123,6 +123,14 @@ class ClockSampler:
         return out
 
 
+L2_NOTE = "GPU arm: 256 MiB device memset between timed frames (L2 flush); the per-level ray queues of a batch exceed L2 anyway"
+
+
+def config_dict(config_id):
+    """`config` of BOTH arms' lines (identical, so the driver can see they ran the same thing)."""
+    return {"workload": CFG["workload"], "config_id": config_id, "cpu_sample": cpu_sample_text(), "l2": L2_NOTE}
+
+
 def cpu_sample_text():
     x0, y0, w, h = CFG["cpu_window"]
     spp = CFG["spp"][0] * CFG["spp"][1]
@@ -165,7 +173,7 @@ def run_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text()},
+        "config": config_dict(args.config),
         "cpu_baseline": cpu_baseline_entry(rays, secs, args.steps),
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -372,10 +380,8 @@ def run_cuda_inner(args):
         line = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            # (the same three keys as the reference arm's line, so that the two arms' configs compare equal)
-            "config": {"workload": CFG["workload"], "config_id": args.config, "cpu_sample": cpu_sample_text()},
+            "config": config_dict(args.config),
             "run": {"sharding": f"bands of {sharding.TILE_H} pixel rows round-robin over {world} rank(s), scene replicated, no collective on the data path",
-                    "l2": "256 MiB device memset between timed frames (L2 flush); the per-level ray queues of a batch exceed L2 anyway",
                     "scene": "device-resident arm: scene handle created once (host binned-SAH BVH), frames rendered from it; end-to-end arms: scene created and destroyed every step"},
             "frame_ms": ms_per_step, "wall_ms_per_step": wall_ms / args.steps,
             "rays_per_frame": rays_all / args.steps, "value_rays": "R_uniq: rays actually traced (secondary sub-trees deduplicated across lights)",
