@@ -149,6 +149,30 @@ pub struct rtc_stats {
     pub shadow_queries_culled: u64,
 }
 
+/// Tuning knobs and test hooks, process-wide (0 = library default); none changes a pixel.
+#[repr(C)]
+#[derive(Clone, Copy, Default)]
+pub struct rtc_tuning {
+    pub batches: i32,
+    pub batch_samples: i32,
+    pub pipes: i32,
+    pub blocks_per_sm: i32,
+    pub no_taper: i32,
+    pub no_copy_stream: i32,
+    pub no_stream_priorities: i32,
+    pub no_graphs: i32,
+    pub no_fast_planes: i32,
+    pub no_plain_shade: i32,
+    pub two_pass: i32,
+    pub lbvh_leaf: i32,
+    pub bvh_builder: i32,
+    pub build_threads: i32,
+    pub sah_leaf_weight_x100: i32,
+    pub sah_bins: i32,
+    pub sah_small_node: i32,
+    pub reserved: [i32; 15],
+}
+
 #[repr(C)]
 pub struct rtc_scene {
     _private: [u8; 0],
@@ -164,5 +188,8 @@ extern "C" {
     pub fn rtc_render_noalloc(scene: *mut rtc_scene, camera: *const rtc_camera, opts: *const rtc_opts, out_rgb: *mut f64, stats: *mut rtc_stats) -> c_int;
     pub fn rtc_alloc_host(bytes: u64) -> *mut std::ffi::c_void;
     pub fn rtc_free_host(p: *mut std::ffi::c_void);
+    pub fn rtc_release_host_memory();
+    pub fn rtc_set_tuning(tuning: *const rtc_tuning);
+    pub fn rtc_get_tuning(out: *mut rtc_tuning);
     pub fn rtc_last_error() -> *const c_char;
 }

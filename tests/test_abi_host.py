@@ -50,6 +50,7 @@ def test_struct_layouts_match_a_c_compiler(built, tmp_path):
     assert sizes[1] == C.sizeof(R.Stats)
     assert sizes[8] == R.Stats.ms_trace.offset
     assert sizes[2] == 4 + 4 + 16 * 8 + 3 * 8
+    assert C.sizeof(R.Tuning) == 32 * 4  # rtc_tuning: 17 knobs + 15 reserved int32
 
 
 def test_build_flags_live_in_the_former_padding_of_the_scene_descriptor(built, tmp_path, lib_types):
@@ -274,7 +275,7 @@ def _rust_structs():
 
 def test_rust_ffi_structs_mirror_the_header():
     c, r = _c_structs(), _rust_structs()
-    for name in ["rtc_prim", "rtc_node", "rtc_material", "rtc_pattern", "rtc_light", "rtc_scene_desc", "rtc_camera", "rtc_opts", "rtc_stats"]:
+    for name in ["rtc_prim", "rtc_node", "rtc_material", "rtc_pattern", "rtc_light", "rtc_scene_desc", "rtc_camera", "rtc_opts", "rtc_stats", "rtc_tuning"]:
         assert name in r, f"rust/src/ffi.rs lacks {name}"
         assert r[name] == c[name], (name, [x for x in zip(r[name], c[name]) if x[0] != x[1]], len(r[name]), len(c[name]))
 
