@@ -192,8 +192,8 @@ int64_t drv_par_render_ppm(const char* name, const char* data_dir, int hsize, in
         if (data_dir && *data_dir) scenes::data_dir() = data_dir;
         auto sc = scenes::build_scene<HostApi>(name, (size_t)hsize, (size_t)vsize);
         rtc::RenderOptions ro;
-        if (device >= 0) ro.devices = {device};  // device < 0: shard over every visible device
-        rtc::Image img = rtc::Image::par_render(sc.camera, sc.world, ro);
+        if (device >= 0) ro.devices = {device};  // device < 0: shard over every visible device (= Camera::render, north_star's spelling)
+        rtc::Image img = device >= 0 ? rtc::Image::par_render(sc.camera, sc.world, ro) : sc.camera.render(sc.world);
         const std::string ppm = img.ppm();
         if ((int64_t)ppm.size() <= out_cap) std::memcpy(out, ppm.data(), ppm.size());
         return (int64_t)ppm.size();

@@ -182,7 +182,7 @@ typedef struct rtc_scene rtc_scene;
 int rtc_device_count(void);
 
 /* Copies and uploads the scene to CUDA device `device`, building the BVH (on the host — binned SAH — or, with
- * desc->build_flags & RTC_BUILD_FAST and 64..8192 bounded items, on the device after the upload).  0 = ok. */
+ * desc->build_flags & RTC_BUILD_FAST and 64 .. 4 M bounded items, on the device after the upload).  0 = ok. */
 int rtc_scene_create(const rtc_scene_desc* desc, int device, rtc_scene** out);
 
 /* The same for `n` distinct devices at once: ONE host build (validation, flattening, BVH), one upload per device

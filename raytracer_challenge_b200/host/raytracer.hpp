@@ -485,7 +485,11 @@ struct World {
     }
 };
 
+class Image;
 struct Camera {
+    // north_star's spelling of the drop-in call, `Camera::render(&World) -> Image`: an alias of Image::par_render(camera, world),
+    // which is what the reference's bins call (src/image.rs:65; the reference has no Camera::render).  Defined below Image.
+    Image render(const World& world) const;
     size_t hsize = 0, vsize = 0;
     double field_of_view = 0.0;
     Matrix transform_inv = Matrix::id();
@@ -899,6 +903,8 @@ class Image {
         put_be32(out, c ^ 0xffffffffu);
     }
 };
+
+inline Image Camera::render(const World& world) const { return Image::par_render(*this, world); }
 
 // ---- ObjParser (src/obj.rs) ---------------------------------------------------------------
 // Line grammar of the reference (nom combinators, src/obj.rs:53-149), first match wins, trailing text ignored:

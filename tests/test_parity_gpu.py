@@ -204,6 +204,8 @@ def test_ppm_through_the_host_api(built):
     err = C.create_string_buffer(1024)
     n = lib.drv_par_render_ppm(b"default_world", R.DATA_DIR.encode(), w, h, 0, buf, cap, err, 1024)
     assert n > 0, err.value
+    buf2 = C.create_string_buffer(cap)  # device < 0: through Camera::render(&World), the alias north_star names, over every visible GPU
+    assert lib.drv_par_render_ppm(b"default_world", R.DATA_DIR.encode(), w, h, -1, buf2, cap, err, 1024) == n and buf2.raw[:n] == buf.raw[:n]
     text = buf.raw[:n].decode()
     lines = text.split("\n")
     assert lines[0] == "P3" and lines[1] == "11 11" and lines[2] == "255" and text.endswith("\n")
