@@ -23,7 +23,7 @@
 #define RTC_SHADOW_MIN_BLOCKS_CSG 4  // (r02n sweep: 128 registers instead of 64 — the CSG lists spill less: chapter14 shadows 4.17 -> 3.73 ms)
 #endif
 #ifndef RTC_SHADE_MIN_BLOCKS
-#define RTC_SHADE_MIN_BLOCKS 5
+#define RTC_SHADE_MIN_BLOCKS 8  // (r02s sweep: 64 registers; the lighting kernels stream records and want occupancy: csg_noise 6.40 -> 6.19 ms, hexagon 0.93 -> 0.89)
 #endif
 #ifndef RTC_SHADE_PLAIN_MIN_BLOCKS  // scenes without procedural patterns: no evaluator, no permutation table, small register budget
 #define RTC_SHADE_PLAIN_MIN_BLOCKS 8
