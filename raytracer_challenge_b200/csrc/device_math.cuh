@@ -325,7 +325,8 @@ __device__ __forceinline__ void plane_roots(const Scene& sc, int xform, const Ra
     plane_roots_row(a.x, a.y, b.x, b.y, world, skip_negative, out);
 }
 
-// HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6).
+// HOT selects which kinds are intersected inline at this call site (bit k = rtc_prim_kind k; triangles = bits 5|6);
+// bit 8: every primitive that reaches this call site is a triangle.
 template <int HOT>
 __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int xform, int geom, const double* __restrict__ tri_rec,
                                            const Ray& world, ObjRay& cache, Tally& tally, bool skip_negative, Roots& out) {
@@ -337,6 +338,13 @@ __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int 
         return;
     }
     const Ray& r = object_ray(sc, world, xform, cache, tally);
+    if (HOT & 0x100) {  // the caller knows the primitive is a triangle (FEAT_TRIS): no dispatch, no out-of-line fallback in this kernel
+        tally.tris++;
+        V3 p1, e1, e2;
+        load_tri(tri_rec, p1, e1, e2);
+        isect_triangle(r, p1, e1, e2, out);
+        return;
+    }
     if (kind >= 5) tally.tris++; else tally.prims++;
     if ((HOT & 0x60) && kind >= 5) {
         V3 p1, e1, e2;

@@ -130,7 +130,7 @@ struct Query {
     __device__ __forceinline__ void roots_of_leaf(const LeafItem& li, int slot, Roots& r) {
         r.n = 0;
         if (!gate_ok(li.id)) return;
-        prim_roots<0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, counters(), skip_negative, r);  // triangles, spheres
+        prim_roots<(FEAT & FEAT_TRIS) ? 0x160 : 0x61>(sc, li.kind_flags, li.xform, li.geom, sc.leaf_tri + 10 * (size_t)slot, ray, cache, counters(), skip_negative, r);  // triangles, spheres
     }
 };
 

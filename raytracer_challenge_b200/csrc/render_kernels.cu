@@ -569,7 +569,8 @@ static void launch_trace_tally(int feat, bool primary, int grid, cudaStream_t st
     } else if (feat & FEAT_TRANSPARENT) {
         if (onepass) launch_trace_feat<FEAT_TRANSPARENT | FEAT_ONEPASS | TALLY>(primary, grid, st, sc, f, lv, hl);
         else launch_trace_feat<FEAT_TRANSPARENT | TALLY>(primary, grid, st, sc, f, lv, hl);
-    } else launch_trace_feat<TALLY>(primary, grid, st, sc, f, lv, hl);
+    } else if (feat & FEAT_TRIS) launch_trace_feat<FEAT_TRIS | TALLY>(primary, grid, st, sc, f, lv, hl);
+    else launch_trace_feat<TALLY>(primary, grid, st, sc, f, lv, hl);
 }
 // feat: the scene's FEAT_* bits, plus FEAT_TALLY when the caller wants the work counted
 void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
@@ -580,11 +581,14 @@ void launch_trace(int feat, bool primary, int grid, cudaStream_t st, const Scene
 template <int TALLY>
 static void launch_shadow_tally(int feat, dim3 grid, cudaStream_t st, const Scene& sc, const FrameParams& f, const LevelParams& lv, const HitList& hl) {
     const bool full = (feat & (FEAT_CSG | FEAT_GATES)) != 0;
+    const bool tris = !full && (feat & FEAT_TRIS) != 0;
     if (sc.all_cast_shadow) {
         if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else if (tris) trace_shadow<FEAT_TRIS | TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
         else trace_shadow<TALLY, true><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     } else {
         if (full) trace_shadow<FEAT_CSG | FEAT_GATES | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
+        else if (tris) trace_shadow<FEAT_TRIS | TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
         else trace_shadow<TALLY, false><<<grid, RTC_BLOCK, 0, st>>>(sc, f, lv, hl);
     }
 }

@@ -546,6 +546,7 @@ static int upload_scene(rtc_scene* s, const PackedScene& p, std::string& err) {
     }
     s->feat = (int)host_stat(h, RTC_STAT_FEATURES);
     if ((s->feat & rtcdev::FEAT_TRANSPARENT) && h.n_bvh_items <= rtcdev::ONEPASS_MAX_ITEMS && !tune.two_pass) s->feat |= rtcdev::FEAT_ONEPASS;
+    if (s->feat == 0 && h.n_bvh_items > 0 && h.all_items_triangles) s->feat |= rtcdev::FEAT_TRIS;  // (only the plain kernel has a triangles-only variant)
     return 0;
 }
 

@@ -710,6 +710,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
     auto t3 = t2;
     // ---- BVH over the bounded items -------------------------------------------------------------
     out.n_bvh_items = (int32_t)item_ids.size();
+    for (int32_t id : item_ids)
+        if (id < 0 || (out.prims[(size_t)id].kind_flags & 0xff) < RTC_TRIANGLE) { out.all_items_triangles = 0; break; }
     if (!item_ids.empty()) {
         Box root;
         for (auto& b : item_boxes) root.add(b);

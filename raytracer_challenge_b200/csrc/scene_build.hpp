@@ -36,6 +36,7 @@ struct HostScene {
     int32_t bvh_root = 0;
     int32_t n_bvh_items = 0;
     int32_t all_cast_shadow = 1;
+    int32_t all_items_triangles = 1;    // every BVH item is a triangle primitive (no sphere, cube, ..., no CSG item)
     int32_t max_children = 0;
     double root_lo[3] = {0, 0, 0}, root_hi[3] = {0, 0, 0};
     // build statistics (reported by tests / DESIGN.md)

@@ -983,12 +983,49 @@ Scene<A> glass_shells(size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- authored: a triangles-only BVH (FEAT_TRIS kernels) with a shape that casts no shadow ---------------------------------
+// Two fans of flat triangles and a strip of smooth ones over a plane; one fan does not cast shadows, so the shadow queries are
+// nearest-hit queries (src/world.rs:43-47) in the triangles-only kernel variant.
+template <class A>
+Scene<A> tri_ghost(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    el.push_back(E::plane(shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.85, 0.85, 0.8)), {{'s', 0.0}, {'r', 0.2}}))));
+    for (int fan = 0; fan < 2; fan++) {
+        std::vector<E> tris;
+        const V apex = V::point(0.0, 1.8, 0.0);
+        for (int i = 0; i < 24; i++) {
+            const double a0 = 2.0 * PI * i / 24.0, a1 = 2.0 * PI * (i + 1) / 24.0;
+            auto args = shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.3 + 0.6 * fan, 0.7 - 0.3 * fan, 0.2 + 0.03 * i)), {{'r', (i % 3 == 0) ? 0.3 : 0.0}}));
+            args.casts_shadow = fan == 0;
+            tris.push_back(E::triangle(args, V::point(std::cos(a0), 0.2, std::sin(a0)), V::point(std::cos(a1), 0.2, std::sin(a1)), apex));
+        }
+        el.push_back(E::composite(M::translation(-1.6 + 3.2 * fan, 0.0, 0.5 * fan) * M::rotation_z(0.15 * fan), std::nullopt, G::Aggregation, std::move(tris)));
+    }
+    std::vector<E> strip;
+    for (int i = 0; i < 40; i++) {
+        const double x0 = -2.0 + 0.1 * i, x1 = x0 + 0.1;
+        auto args = shape_args<A>(M::id(), material_with<A>(P::plain(C::make(0.5, 0.5, 0.9)), {{'r', 0.2}}));
+        const V n0 = V::vector(std::sin(3.0 * x0), 1.0, -0.3).normalize(), n1 = V::vector(std::sin(3.0 * x1), 1.0, -0.3).normalize();
+        strip.push_back(E::smooth_triangle(args, V::point(x0, 0.9, 2.0), V::point(x1, 0.9, 2.0), V::point(x0, 1.6, 2.6), n0, n1, n0));
+        strip.push_back(E::smooth_triangle(args, V::point(x1, 0.9, 2.0), V::point(x1, 1.6, 2.6), V::point(x0, 1.6, 2.6), n1, n1, n0));
+    }
+    el.push_back(E::composite(M::id(), std::nullopt, G::Aggregation, std::move(strip)));
+    s.world.lights.push_back({C::make(0.9, 0.9, 0.9), V::point(-5.0, 8.0, -6.0)});
+    s.world.lights.push_back({C::make(0.3, 0.3, 0.35), V::point(6.0, 4.0, -5.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.0,
+                               A::Camera::transform(V::point(0.3, 3.2, -6.5), V::point(0.0, 0.9, 0.5), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
                                                "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope",
-                                               "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells"};
+                                               "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells", "tri_ghost"};
     return n;
 }
 
@@ -1014,6 +1051,7 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "many_gates") return many_gates<A>(hsize, vsize);
     if (name == "teapot_tess") return teapot_tess<A>(hsize, vsize);
     if (name == "glass_shells") return glass_shells<A>(hsize, vsize);
+    if (name == "tri_ghost") return tri_ghost<A>(hsize, vsize);
     if (name == "benchmark_glass") return benchmark_glass<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");

@@ -29,6 +29,7 @@ CASES = [
     ("axis_aligned", 1, 1),
     ("axis_aligned", 65, 37),
     ("benchmark_glass", 96, 54),        # the 1 000-sphere scene made of glass (two-pass form: > 512 BVH items): up to ~100 crossings on a line
+    ("tri_ghost", 96, 54),              # triangles-only BVH (FEAT_TRIS kernels) with a fan that casts no shadow: nearest-hit shadow queries
     ("many_gates", 96, 54),             # 80 group boxes over finite cones: 64-bit gate masks, slots assigned after the subtree walk
     ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
@@ -48,6 +49,17 @@ def test_scene_matches_oracle(built, name, w, h):
     assert np.array_equal(img, brute)
     # R_ref: the GPU's count of reference-equivalent World::intersect queries equals the oracle's own count
     assert st.rays_ref == int(counts.sum()), (st.as_dict(), counts)
+
+
+def test_kernel_variants_chosen_per_scene(built):
+    """rtc_scene_stat(FEATURES) of an uploaded scene names the kernel variant: 32 = FEAT_TRIS (every BVH item a triangle, plain
+    materials/groups), 16 = FEAT_ONEPASS (transparent, small BVH), 1 / 2 / 4 = transparent / CSG / exact gates."""
+    want = {"teapot": 32, "teapot_low": 32, "tri_ghost": 32, "benchmark": 0, "glass_air_bubble": 1 | 16, "benchmark_glass": 1, "many_gates": 4}
+    for name, feat in want.items():
+        with R.Session(name, 32, 18, device=0) as s:
+            assert s.build_stats["features"] == feat, (name, s.build_stats["features"])
+    with R.Session("csg_noise", 32, 18, device=0) as s:
+        assert s.build_stats["features"] & 2 and s.build_stats["features"] & 16
 
 
 def test_known_answer_pixel(built):
