@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB_DIR = os.environ.get("RTC_LIB_DIR") or os.path.join(ROOT, "raytracer_challenge_b200", "lib")  # (the variable: compile-time variants side by side, tools/build_variant.sh)
 DATA_DIR = os.path.join(ROOT, "data")
 SCENES = ["default_world", "three_spheres", "glass_air_bubble", "hexagon", "benchmark", "teapot", "teapot_low", "csg_noise",
-          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope", "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells", "tri_ghost"]
+          "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope", "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells", "tri_ghost", "csg_cuts"]
 
 
 class RtcError(RuntimeError):

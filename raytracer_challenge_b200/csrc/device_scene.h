@@ -111,10 +111,14 @@ struct LeafItem {
 //   OP_PRIM  a = primitive index
 //   OP_BEGIN                     (push list length)
 //   OP_END   a = group kind, b/c = primitive index range [b, c) of the LEFT child's subtree
+//   OP_SKIP_IF_EMPTY  a = ops to jump over.  Sits between the left and the right operand of a Difference or an
+//            Intersection: when the left operand produced no crossing the filter (src/shape.rs:230-269) keeps nothing
+//            of the right one either (a right crossing survives only inside the left solid), so the right operand's
+//            primitives are not intersected at all and the group's result is the empty list it would have been.
 struct CsgOp {
     int32_t op, a, b, c;
 };
-enum { OP_PRIM = 0, OP_BEGIN = 1, OP_END = 2 };
+enum { OP_PRIM = 0, OP_BEGIN = 1, OP_END = 2, OP_SKIP_IF_EMPTY = 3 };
 struct CsgRoot {
     int32_t first_op, n_ops;
     int32_t prim_begin, prim_end;  // all primitives of the subtree are [prim_begin, prim_end)

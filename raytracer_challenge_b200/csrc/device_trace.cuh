@@ -149,6 +149,8 @@ __device__ __forceinline__ int csg_eval(Query<FEAT>& q, const CsgRoot& root, Cro
             for (int j = 0; j < r.n; ++j) { list[n].t = r.t[j]; list[n].prim = op.a; n++; }
         } else if (op.op == OP_BEGIN) {
             marks[nm++] = n;
+        } else if (op.op == OP_SKIP_IF_EMPTY) {
+            if (n == marks[nm - 1]) { k += op.a; --nm; }  // lands on the group's OP_END; its (empty) segment is closed
         } else {
             const int m = marks[--nm];
             for (int i = m + 1; i < n; ++i) {  // stable insertion sort by t

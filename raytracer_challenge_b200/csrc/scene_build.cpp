@@ -582,11 +582,17 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
     int next_prim = 0;             // primitives must appear in depth-first order
     std::string err;
 
-    // Returns the bounds of the subtree; fills prim range [pb, pe).
-    std::function<Box(int, uint32_t, int, int, int&, int&)> walk;
+    // Returns the bounds of the subtree as the reference computes them (the union of everything below); fills prim range
+    // [pb, pe) and `eff`, the box that holds every crossing the subtree can REPORT: for a Difference that is the left
+    // operand's box, for an Intersection the overlap of the two (a crossing of the right operand survives the filter of
+    // src/shape.rs:230-269 only inside the left solid, and vice versa).  A top-level CSG item enters the BVH with `eff`:
+    // a ray that misses it but hits the reference's box evaluates, in the reference, to the empty list.
+    std::function<Box(int, uint32_t, int, int, int&, int&, Box&)> walk;
     // csg_root: index into out.csg_roots of the enclosing top-level CSG item, or -1.
-    walk = [&](int ni, uint32_t mask, int csg_root, int csg_depth, int& pb, int& pe) -> Box {
+    walk = [&](int ni, uint32_t mask, int csg_root, int csg_depth, int& pb, int& pe, Box& eff) -> Box {
         Box sub;
+        eff = Box();
+        Box child_eff[2];
         (void)mask;
         pb = next_prim;
         pe = next_prim;
@@ -630,8 +636,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
             out.csg_ops.push_back({rtcdev::OP_BEGIN, 0, 0, 0});
         }
         int left_b = 0, left_e = 0;
-        const size_t first_prim_slot = out.prims.size();
-        (void)first_prim_slot;
+        size_t skip_at = 0;
+        const bool skippable = is_csg && (nd.kind == RTC_DIFFERENCE || nd.kind == RTC_INTERSECTION);
         for (int c = 0; c < nd.n_children; ++c) {
             const int32_t ch = d.children[nd.first_child + c];
             int cb = next_prim, ce = next_prim;
@@ -641,6 +647,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
                 next_prim++;
                 ce = next_prim;
                 sub.add(prim_box[(size_t)ch]);
+                eff.add(prim_box[(size_t)ch]);
+                if (c < 2) child_eff[c] = prim_box[(size_t)ch];
                 if (my_root >= 0) {
                     out.csg_ops.push_back({rtcdev::OP_PRIM, ch, 0, 0});
                 } else if (prim_box[(size_t)ch].bounded) {
@@ -651,22 +659,44 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
                     out.unbounded.push_back(ch);
                 }
             } else {
-                Box b = walk(~ch, 0u, my_root, my_depth, cb, ce);
+                Box ceff;
+                Box b = walk(~ch, 0u, my_root, my_depth, cb, ce, ceff);
                 if (!err.empty()) return sub;
                 sub.add(b);
+                eff.add(ceff);
+                if (c < 2) child_eff[c] = ceff;
             }
-            if (c == 0) { left_b = cb; left_e = ce; }
+            if (c == 0) {
+                left_b = cb; left_e = ce;
+                if (skippable) { skip_at = out.csg_ops.size(); out.csg_ops.push_back({rtcdev::OP_SKIP_IF_EMPTY, 0, 0, 0}); }
+            }
         }
         pe = next_prim;
         if (is_csg) {
             out.csg_ops.push_back({rtcdev::OP_END, nd.kind, left_b, left_e});
+            if (skippable) {
+                out.csg_ops[skip_at].a = (int32_t)(out.csg_ops.size() - 1 - skip_at);  // from the skip op to this group's OP_END
+                // (boxes of finite cones are not exact — see ConeGuard — so a subtree that holds one keeps the union)
+                if (child_eff[0].exact && child_eff[1].exact) {
+                    Box t = child_eff[0];
+                    if (nd.kind == RTC_INTERSECTION) {
+                        if (!t.bounded) t = child_eff[1];
+                        else if (child_eff[1].bounded)
+                            for (int k = 0; k < 3; ++k) { t.lo[k] = std::max(t.lo[k], child_eff[1].lo[k]); t.hi[k] = std::min(t.hi[k], child_eff[1].hi[k]); }
+                        bool overlap = true;
+                        for (int k = 0; k < 3; ++k) overlap = overlap && t.lo[k] <= t.hi[k];
+                        if (!overlap) t = child_eff[0];  // disjoint operands: nothing can be reported; any valid box will do
+                    }
+                    eff = t;
+                }
+            }
             if (csg_root < 0) {  // this node is a top-level CSG item
                 rtcdev::CsgRoot& r = out.csg_roots[(size_t)my_root];
                 r.n_ops = (int32_t)out.csg_ops.size() - r.first_op;
                 r.prim_begin = pb;
                 r.prim_end = pe;
-                if (sub.bounded && !sub.empty()) {
-                    item_boxes.push_back(sub);
+                if (eff.bounded && !eff.empty()) {
+                    item_boxes.push_back(eff);
                     item_ids.push_back(~my_root);
                     for (int q = pb; q < pe; ++q) out.prims[(size_t)q].kind_flags |= rtcdev::PRIM_IN_BVH;
                 } else if (pe > pb) {
@@ -702,7 +732,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
         return sub;
     };
     int pb = 0, pe = 0;
-    walk(0, 0u, -1, 0, pb, pe);
+    Box root_eff;
+    walk(0, 0u, -1, 0, pb, pe, root_eff);
     if (!err.empty()) return err;
     if (next_prim != d.n_prims) return "some primitives are not reachable from the root node";
 

@@ -1020,12 +1020,71 @@ Scene<A> tri_ghost(size_t hsize, size_t vsize) {
     return s;
 }
 
+// --- authored: CSG operands whose boxes differ a lot from the box of what the group can report ---------------------------
+// The BVH holds a CSG item under the box of its reportable crossings (left operand of a Difference, overlap of an
+// Intersection) and the CSG program skips the right operand when the left one reports nothing; this scene is made of the
+// cases where that matters: a right operand sticking far out of the left one, a half-space (plane) as the right operand,
+// an unbounded left operand of an Intersection, disjoint operands, a finite cone (inexact box) on either side, nesting.
+template <class A>
+Scene<A> csg_cuts(size_t hsize, size_t vsize) {
+    using M = typename A::Matrix; using V = typename A::Vector; using C = typename A::Color;
+    using P = typename A::Pattern; using E = typename A::Element; using G = typename A::GroupKind;
+    Scene<A> s;
+    auto& el = s.world.elements;
+    auto plain = [](double r, double g, double b) { return P::plain(C::make(r, g, b)); };
+    auto pair = [](E a, E b) { std::vector<E> v; v.push_back(std::move(a)); v.push_back(std::move(b)); return v; };
+    el.push_back(E::plane(shape_args<A>(M::id(), material_with<A>(P::checkers(M::id(), plain(0.8, 0.8, 0.8), plain(0.35, 0.35, 0.4)), {{'s', 0.0}, {'r', 0.25}}))));
+    // (1) small sphere minus a long thin cylinder through it: the cylinder sticks 6 units out on both sides
+    el.push_back(E::composite(M::translation(-3.0, 1.0, 0.0) * M::rotation_z(0.4), std::nullopt, G::Difference,
+                              pair(E::sphere(shape_args<A>(M::id(), material_with<A>(plain(0.9, 0.3, 0.2), {{'r', 0.1}}))),
+                                   E::cylinder(shape_args<A>(M::scaling(0.45, 1.0, 0.45), material_with<A>(plain(0.95, 0.9, 0.3), {})), -6.0, 6.0, true))));
+    // (2) cube cut by a half-space: the right operand is an unbounded plane
+    el.push_back(E::composite(M::translation(-0.6, 0.8, 0.8) * M::rotation_y(0.5), std::nullopt, G::Difference,
+                              pair(E::cube(shape_args<A>(M::scaling(0.8, 0.8, 0.8), material_with<A>(plain(0.2, 0.6, 0.9), {{'r', 0.15}}))),
+                                   E::plane(shape_args<A>(M::translation(0.0, 0.3, 0.0) * M::rotation_z(0.6), material_with<A>(plain(0.9, 0.9, 0.9), {}))))));
+    // (3) half-space AND sphere: the left operand is unbounded, the group can only report inside the sphere
+    el.push_back(E::composite(M::translation(1.6, 0.9, -0.3), std::nullopt, G::Intersection,
+                              pair(E::plane(shape_args<A>(M::rotation_x(0.5), material_with<A>(plain(0.9, 0.7, 0.2), {}))),
+                                   E::sphere(shape_args<A>(M::scaling(0.9, 0.9, 0.9), material_with<A>(plain(0.3, 0.8, 0.4), {{'h', 80.0}}))))));
+    // (4) disjoint operands: never reports anything, but its (large) reference box covers the cone group behind it
+    el.push_back(E::composite(M::translation(0.0, 2.6, 2.5), std::nullopt, G::Intersection,
+                              pair(E::sphere(shape_args<A>(M::translation(-3.0, 0.0, 0.0), material_with<A>(plain(1.0, 0.0, 1.0), {}))),
+                                   E::sphere(shape_args<A>(M::translation(3.0, 0.0, 0.0), material_with<A>(plain(1.0, 0.0, 1.0), {}))))));
+    // (5) a finite cone on the left (box not exact) minus a sphere; (6) a sphere minus a finite cone
+    el.push_back(E::composite(M::translation(3.4, 1.6, 1.2), std::nullopt, G::Difference,
+                              pair(E::cone(shape_args<A>(M::scaling(0.8, 1.4, 0.8), material_with<A>(plain(0.8, 0.5, 0.9), {})), -1.0, 0.0, true),
+                                   E::sphere(shape_args<A>(M::translation(0.3, -0.9, -0.5) * M::scaling(0.6, 0.6, 0.6), material_with<A>(plain(0.2, 0.2, 0.2), {}))))));
+    el.push_back(E::composite(M::translation(0.3, 1.0, 3.2), std::nullopt, G::Difference,
+                              pair(E::sphere(shape_args<A>(M::id(), material_with<A>(plain(0.9, 0.6, 0.3), {{'r', 0.2}}))),
+                                   E::cone(shape_args<A>(M::translation(0.0, 1.2, -0.6) * M::scaling(0.7, 1.6, 0.7), material_with<A>(plain(0.3, 0.3, 0.7), {})), -1.0, 0.0, false))));
+    // (7) nested: (sphere AND cube) minus (cylinder OR (sphere minus cube)), glass, inside a plain group with a transform
+    {
+        std::vector<E> inner = pair(E::sphere(shape_args<A>(M::scaling(1.25, 1.25, 1.25), material_with<A>(plain(0.1, 0.1, 0.15), {{'t', 0.7}, {'i', 1.5}, {'r', 0.3}, {'d', 0.2}}))),
+                                    E::cube(shape_args<A>(M::id(), material_with<A>(plain(0.1, 0.15, 0.1), {{'t', 0.7}, {'i', 1.5}, {'r', 0.3}, {'d', 0.2}}))));
+        std::vector<E> dent = pair(E::sphere(shape_args<A>(M::translation(0.9, 0.9, -0.9) * M::scaling(0.7, 0.7, 0.7), material_with<A>(plain(0.9, 0.2, 0.2), {}))),
+                                   E::cube(shape_args<A>(M::translation(1.4, 1.4, -1.4) * M::scaling(0.5, 0.5, 0.5), material_with<A>(plain(0.2, 0.9, 0.2), {}))));
+        std::vector<E> holes = pair(E::cylinder(shape_args<A>(M::scaling(0.4, 1.0, 0.4), material_with<A>(plain(0.9, 0.9, 0.2), {})), -4.0, 4.0, false),
+                                    E::composite(M::id(), std::nullopt, G::Difference, std::move(dent)));
+        std::vector<E> whole = pair(E::composite(M::id(), std::nullopt, G::Intersection, std::move(inner)),
+                                    E::composite(M::rotation_x(0.3), std::nullopt, G::Union, std::move(holes)));
+        std::vector<E> grp;
+        grp.push_back(E::composite(M::id(), std::nullopt, G::Difference, std::move(whole)));
+        grp.push_back(E::sphere(shape_args<A>(M::translation(0.0, 1.7, 0.0) * M::scaling(0.3, 0.3, 0.3), material_with<A>(plain(0.9, 0.9, 0.9), {{'r', 0.4}}))));
+        el.push_back(E::composite(M::translation(-2.0, 1.1, -2.6) * M::rotation_y(0.7) * M::scaling(0.85, 0.85, 0.85), std::nullopt, G::Aggregation, std::move(grp)));
+    }
+    s.world.lights.push_back({C::make(0.85, 0.85, 0.85), V::point(-6.0, 9.0, -7.0)});
+    s.world.lights.push_back({C::make(0.3, 0.3, 0.3), V::point(7.0, 5.0, -4.0)});
+    s.camera = A::Camera::make(hsize, vsize, 1.1,
+                               A::Camera::transform(V::point(0.5, 4.2, -8.5), V::point(0.0, 1.0, 0.5), V::vector(0.0, 1.0, 0.0)));
+    return s;
+}
+
 // --- registry ---------------------------------------------------------------------------------
 inline const std::vector<std::string>& scene_names() {
     static const std::vector<std::string> n = {"default_world", "three_spheres", "glass_air_bubble", "hexagon",
                                                "benchmark",     "teapot",        "teapot_low",       "csg_noise",
                                                "chapter11_title", "chapter12_title", "chapter13_title", "chapter14_title", "cover", "cone_slope",
-                                               "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells", "tri_ghost"};
+                                               "axis_aligned", "no_shadow_flat", "many_gates", "glass_shells", "tri_ghost", "csg_cuts"};
     return n;
 }
 
@@ -1052,6 +1111,7 @@ Scene<A> build_scene(const std::string& name, size_t hsize, size_t vsize) {
     if (name == "teapot_tess") return teapot_tess<A>(hsize, vsize);
     if (name == "glass_shells") return glass_shells<A>(hsize, vsize);
     if (name == "tri_ghost") return tri_ghost<A>(hsize, vsize);
+    if (name == "csg_cuts") return csg_cuts<A>(hsize, vsize);
     if (name == "benchmark_glass") return benchmark_glass<A>(hsize, vsize);
     if (name.rfind("fuzz:", 0) == 0) return fuzz<A>(std::strtoull(name.c_str() + 5, nullptr, 10), hsize, vsize);
     throw std::runtime_error("scenes: unknown scene '" + name + "'");

@@ -30,6 +30,7 @@ CASES = [
     ("axis_aligned", 65, 37),
     ("benchmark_glass", 96, 54),        # the 1 000-sphere scene made of glass (two-pass form: > 512 BVH items): up to ~100 crossings on a line
     ("tri_ghost", 96, 54),              # triangles-only BVH (FEAT_TRIS kernels) with a fan that casts no shadow: nearest-hit shadow queries
+    ("csg_cuts", 128, 72),              # CSG items under the box of what they can report; right operands skipped when the left reports nothing
     ("many_gates", 96, 54),             # 80 group boxes over finite cones: 64-bit gate masks, slots assigned after the subtree walk
     ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
 ] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
