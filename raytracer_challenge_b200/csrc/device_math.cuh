@@ -261,14 +261,11 @@ struct GenericCall {
     Ray r;
     Roots out;
 };
-__device__ __noinline__ void roots_generic_body(const double* __restrict__ ranges, int kind_flags, int geom, const double* __restrict__ tri_rec, GenericCall* c) {
-    const int kind = kind_flags & 0xff;
-    const Ray r = c->r;
-    Roots out;
+__device__ __forceinline__ void roots_by_kind(const double* __restrict__ ranges, int kind_flags, int geom, const double* __restrict__ tri_rec, const Ray& r, Roots& out) {
     out.n = 0;
     out.u = 0.0;
     out.v = 0.0;
-    switch (kind) {
+    switch (kind_flags & 0xff) {
         case 0: isect_sphere(r, out); break;
         case 1: isect_plane(r, out); break;
         case 2: isect_cube(r, out); break;
@@ -280,6 +277,11 @@ __device__ __noinline__ void roots_generic_body(const double* __restrict__ range
             isect_triangle(r, p1, e1, e2, out);
         }
     }
+}
+__device__ __noinline__ void roots_generic_body(const double* __restrict__ ranges, int kind_flags, int geom, const double* __restrict__ tri_rec, GenericCall* c) {
+    const Ray r = c->r;
+    Roots out;
+    roots_by_kind(ranges, kind_flags, geom, tri_rec, r, out);
     c->out = out;
 }
 __device__ __forceinline__ void roots_generic(const Scene& sc, int kind_flags, int geom, const double* __restrict__ tri_rec, const Ray& r, Roots& out) {
@@ -353,6 +355,8 @@ __device__ __forceinline__ void prim_roots(const Scene& sc, int kind_flags, int 
     } else if ((HOT & 0x01) && kind == 0) {
         if (skip_negative) isect_sphere_nearest(r, out);
         else isect_sphere(r, out);
+    } else if (HOT & 0x400) {  // the caller is itself an out-of-line routine (a CSG program): the dispatch is inlined into it
+        roots_by_kind(sc.ranges, kind_flags, geom, tri_rec, r, out);
     } else {
         roots_generic(sc, kind_flags, geom, tri_rec, r, out);
     }
