@@ -14,6 +14,17 @@
 #pragma once
 #include "device_math.cuh"
 
+// The loops that hand an intersector's roots (1 for a triangle or a plane, 2 for a sphere, up to 4 for a capped cylinder) to a
+// visitor are inlined at every place a primitive is tested; unrolled four times each they were ~1 200 of the 6-13 K
+// instructions of a trace kernel (tools/code_footprint.py).  Kept rolled: the footprint is what the kernels with the most
+// code (CSG, gates) stall on (`no_instruction`), a rolled loop of <= 4 trips costs nothing measurable.
+#ifndef RTC_ROOTS_UNROLL
+#define RTC_ROOTS_UNROLL 1
+#endif
+#define RTC_PRAGMA_(x) _Pragma(#x)
+#define RTC_PRAGMA(x) RTC_PRAGMA_(x)
+#define RTC_ROOTS_LOOP RTC_PRAGMA(unroll RTC_ROOTS_UNROLL)
+
 namespace rtcdev {
 
 struct Hit {
@@ -463,6 +474,7 @@ struct ClosestVisitor {
         }
     }
     __device__ __forceinline__ void offer_roots(const Roots& r, int id) {
+        RTC_ROOTS_LOOP
         for (int k = 0; k < r.n; ++k) offer(r.t[k], id, r.u, r.v);
     }
     __device__ __forceinline__ bool csg(int root) {
@@ -527,6 +539,24 @@ __device__ __forceinline__ Hit closest_hit(const Scene& sc, const Ray& ray, doub
 // transparent shapes, a second time for that list.  Here one walk without a lower bound on t does both: every crossing
 // not beyond the nearest hit found so far is kept in `out`, and whenever the list fills up the entries the hit has since
 // overtaken are dropped.  The hit cannot move further away, so a crossing at t <= t_hit is never discarded or culled.
+// Drops the crossings the nearest hit has overtaken (t > t_hit) from a full list.  `take` is inlined at every place a
+// crossing is offered, and with n == MAX_CROSSINGS known the compiler unrolls this rarely-run loop completely at each of
+// them: 5 588 of the 13 648 instructions of trace_spawn<23,0> (tools/code_footprint.py, r02x) — in the CSG kernels, whose
+// dominant stall is the instruction fetch, the loop stays ROLLED.  The small transparent-only kernels measure the other way
+// (glass bubble 4.06 ms unrolled, 4.39 ms rolled, 4.14-4.35 ms as an out-of-line call), so they keep the unrolled form.
+template <bool ROLLED>
+__device__ __forceinline__ int drop_overtaken(Cross* list, int n, double t_hit) {
+    int k = 0;
+    if (ROLLED) {
+#pragma unroll 1
+        for (int i = 0; i < n; ++i)
+            if (list[i].t <= t_hit) list[k++] = list[i];
+    } else {
+        for (int i = 0; i < n; ++i)
+            if (list[i].t <= t_hit) list[k++] = list[i];
+    }
+    return k;
+}
 template <int FEAT>
 struct ClosestCollectVisitor {
     static constexpr bool kTally = (FEAT & FEAT_TALLY) != 0;
@@ -541,12 +571,7 @@ struct ClosestCollectVisitor {
     __device__ __forceinline__ double tmax() const { return best.prim >= 0 ? best.t : CUDART_INF; }
     __device__ __forceinline__ void take(double t, int prim, double u, double v) {
         if (best.prim < 0 || t <= best.t) {
-            if (n == MAX_CROSSINGS && best.prim >= 0) {  // drop what the hit has overtaken
-                int k = 0;
-                for (int i = 0; i < n; ++i)
-                    if (out[i].t <= best.t) out[k++] = out[i];
-                n = k;
-            }
+            if (n == MAX_CROSSINGS && best.prim >= 0) n = drop_overtaken<(FEAT & FEAT_CSG) != 0>(out, n, best.t);
             if (n == MAX_CROSSINGS) full = true;
             else { out[n].t = t; out[n].prim = prim; n++; }
         }
@@ -555,6 +580,7 @@ struct ClosestCollectVisitor {
         }
     }
     __device__ __forceinline__ bool take_roots(const Roots& r, int id) {
+        RTC_ROOTS_LOOP
         for (int k = 0; k < r.n; ++k) take(r.t[k], id, r.u, r.v);
         return full;
     }
@@ -716,6 +742,7 @@ struct CollectVisitor {
         return false;
     }
     __device__ __forceinline__ bool push_roots(const Roots& r, int id) {
+        RTC_ROOTS_LOOP
         for (int k = 0; k < r.n; ++k)
             if (push(r.t[k], id)) return true;
         return false;
