@@ -297,7 +297,8 @@ typedef struct rtc_tuning {
     int32_t bvh_builder;      /* 0: as rtc_scene_desc.build_flags says; 1: device (LBVH) whenever possible; 2: host (binned SAH) always */
     int32_t build_threads;    /* host BVH build: threads it may use (default: all cores; one process per GPU should pass cores / ranks) */
     int32_t sah_leaf_weight_x100, sah_bins, sah_small_node; /* host SAH build: leaf cost x 100 (default 300), bins 2..16 (16), exact-sweep size 2..8 (8) */
-    int32_t reserved[15];
+    int32_t host_paced_copies; /* 1: rtc_render into a host buffer issues each batch's copy from the calling thread once the batch's event has fired, instead of making the copy stream wait for it on the device (no CUDA-graph replay in this mode) */
+    int32_t reserved[14];
 } rtc_tuning;
 void rtc_set_tuning(const rtc_tuning* tuning); /* NULL: back to the defaults */
 void rtc_get_tuning(rtc_tuning* out);

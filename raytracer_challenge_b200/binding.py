@@ -55,7 +55,7 @@ class Stats(C.Structure):  # rtc_stats
 class Tuning(C.Structure):  # rtc_tuning
     _fields_ = [(n, C.c_int32) for n in ("batches", "batch_samples", "pipes", "blocks_per_sm", "no_taper", "no_copy_stream", "no_stream_priorities",
                                            "no_graphs", "no_fast_planes", "no_plain_shade", "two_pass", "lbvh_leaf", "bvh_builder", "build_threads",
-                                           "sah_leaf_weight_x100", "sah_bins", "sah_small_node")] + [("reserved", C.c_int32 * 15)]
+                                           "sah_leaf_weight_x100", "sah_bins", "sah_small_node", "host_paced_copies")] + [("reserved", C.c_int32 * 14)]
 
 
 BVH_DEVICE, BVH_HOST = 1, 2  # rtc_tuning.bvh_builder

@@ -806,6 +806,16 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     int* h_overflow = (int*)(ctx.counters_host + n_batches * COUNTERS_PER_BATCH);
     // Everything one frame puts on the device's streams, from clearing the counters to reading them back: issued directly,
     // or once under stream capture and replayed as a graph afterwards.
+    struct CopyOp { double* dst; size_t dpitch; const double* src; size_t spitch; size_t width, height; int batch; };  // height 1: contiguous
+    auto issue_copy = [&](const CopyOp& c, cudaStream_t cs) -> int {
+        if (c.height == 1) CU(cudaMemcpyAsync(c.dst, c.src, c.width, cudaMemcpyDeviceToHost, cs));
+        else CU(cudaMemcpy2DAsync(c.dst, c.dpitch, c.src, c.spitch, c.width, c.height, cudaMemcpyDeviceToHost, cs));
+        return 0;
+    };
+    // Host-paced copies (rtc_tuning.host_paced_copies): the copy of a batch is not made to wait for the batch's event ON
+    // THE DEVICE; this thread polls the events and issues each copy once its batch is done.
+    const bool host_paced = host_out != nullptr && copy_on_own_stream && tune.host_paced_copies && !profile && !timeline;
+    std::vector<CopyOp> paced;
     auto enqueue = [&]() -> int {
     CU(cudaMemsetAsync(ctx.counters, 0, counter_bytes, st0));
     CU(cudaMemsetAsync(ctx.overflow, 0, sizeof(int), st0));
@@ -862,14 +872,16 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
             if (copy_on_own_stream) {
                 CU(cudaEventRecord(ctx.batch_events[b], st));
                 cst = ctx.copy_stream[b % (uint64_t)n_pipes];
-                CU(cudaStreamWaitEvent(cst, ctx.batch_events[b], 0));
+                if (!host_paced) CU(cudaStreamWaitEvent(cst, ctx.batch_events[b], 0));
             }
-            uint64_t off_px, len_px;
+            // the batch's copies: one contiguous piece, or (bands of a sharded frame) one strided piece + a partial last band
+            CopyOp ops[2];
+            int n_ops = 0;
             if (row_major) {
                 const uint64_t row0 = first / unit * (uint64_t)o.tile_h;
                 const uint64_t row1 = std::min<uint64_t>((first + npix) / unit * (uint64_t)o.tile_h, (uint64_t)wh);
-                off_px = row0 * (uint64_t)ww;
-                len_px = (row1 - row0) * (uint64_t)ww;
+                const uint64_t off_px = row0 * (uint64_t)ww, len_px = (row1 - row0) * (uint64_t)ww;
+                if (len_px) ops[n_ops++] = CopyOp{host_out + 3 * off_px, 0, ctx.out + 3 * off_px, 0, len_px * 3 * sizeof(double), 1, (int)b};
             } else if (scatter_rows) {
                 // tiles are full-width rows of tile_h pixel rows: owned tile row k of this shard is global tile row
                 // shard_index + k * shard_count, i.e. one strided 2-D copy puts the batch where it belongs in the frame
@@ -880,25 +892,24 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
                 const bool partial_last = k1 > k0 && global_y(k1 - 1) + (uint64_t)o.tile_h > (uint64_t)wh;
                 const uint64_t n_full = (k1 - k0) - (partial_last ? 1 : 0);
                 if (n_full)
-                    CU(cudaMemcpy2DAsync(host_out + 3 * global_y(k0) * (uint64_t)ww, (uint64_t)o.shard_count * (uint64_t)o.tile_h * row_bytes,
-                                         ctx.out + 3 * k0 * per_tile, per_tile * 3 * sizeof(double), (uint64_t)o.tile_h * row_bytes, n_full,
-                                         cudaMemcpyDeviceToHost, cst));
+                    ops[n_ops++] = CopyOp{host_out + 3 * global_y(k0) * (uint64_t)ww, (uint64_t)o.shard_count * (uint64_t)o.tile_h * row_bytes,
+                                          ctx.out + 3 * k0 * per_tile, per_tile * 3 * sizeof(double), (uint64_t)o.tile_h * row_bytes, n_full, (int)b};
                 if (partial_last) {
                     const uint64_t y0 = global_y(k1 - 1);
-                    CU(cudaMemcpyAsync(host_out + 3 * y0 * (uint64_t)ww, ctx.out + 3 * (k1 - 1) * per_tile, ((uint64_t)wh - y0) * row_bytes,
-                                       cudaMemcpyDeviceToHost, cst));
+                    ops[n_ops++] = CopyOp{host_out + 3 * y0 * (uint64_t)ww, 0, ctx.out + 3 * (k1 - 1) * per_tile, 0, ((uint64_t)wh - y0) * row_bytes, 1, (int)b};
                 }
-                continue;
-            } else {
-                off_px = first;
-                len_px = npix;
+            } else if (npix) {
+                ops[n_ops++] = CopyOp{host_out + 3 * first, 0, ctx.out + 3 * first, 0, npix * 3 * sizeof(double), 1, (int)b};
             }
-            if (len_px) CU(cudaMemcpyAsync(host_out + 3 * off_px, ctx.out + 3 * off_px, len_px * 3 * sizeof(double), cudaMemcpyDeviceToHost, cst));
-            if (timeline) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, cst)); tl_events.push_back(e); }
+            for (int k = 0; k < n_ops; ++k) {
+                if (host_paced) paced.push_back(ops[k]);
+                else if (int rc = issue_copy(ops[k], cst)) return rc;
+            }
+            if (timeline && !host_paced) { cudaEvent_t e; CU(cudaEventCreate(&e)); CU(cudaEventRecord(e, cst)); tl_events.push_back(e); }
         }
     }
     CU(cudaGetLastError());
-    if (host_out && copy_on_own_stream) {
+    if (host_out && copy_on_own_stream && !host_paced) {
         for (int p = 0; p < n_pipes; ++p) {
             CU(cudaEventRecord(ctx.copy_done, ctx.copy_stream[p]));
             CU(cudaStreamWaitEvent(st0, ctx.copy_done, 0));
@@ -908,13 +919,14 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
         CU(cudaEventRecord(ctx.pipe[p].done, ctx.pipe[p].stream));
         CU(cudaStreamWaitEvent(st0, ctx.pipe[p].done, 0));
     }
+    if (host_paced) return 0;  // (the read-back follows the paced copies, below)
     CU(cudaMemcpyAsync(ctx.counters_host, ctx.counters, counter_bytes, cudaMemcpyDeviceToHost, st0));
     CU(cudaMemcpyAsync(h_overflow, ctx.overflow, sizeof(int), cudaMemcpyDeviceToHost, st0));
     return 0;
     };  // enqueue
 
     // ---- replay a captured graph when the frame repeats ----
-    bool use_graph = !profile && !timeline && !tune.no_graphs;
+    bool use_graph = !profile && !timeline && !tune.no_graphs && !host_paced;
     if (use_graph && host_out) {  // (copies into pageable memory cannot be captured)
         cudaPointerAttributes attr{};
         if (cudaPointerGetAttributes(&attr, host_out) != cudaSuccess || attr.type != cudaMemoryTypeHost) { use_graph = false; cudaGetLastError(); }
@@ -961,6 +973,27 @@ static int render_impl(rtc_scene* s, const rtc_camera* cam, const rtc_opts* o_in
     } else {
         CU(cudaEventRecord(ctx.ev[0], st0));
         if (int rc = enqueue()) return rc;
+        if (host_paced) {
+            std::vector<char> issued(paced.size(), 0);
+            size_t left = paced.size();
+            while (left) {
+                for (size_t k = 0; k < paced.size(); ++k) {
+                    if (issued[k]) continue;
+                    const cudaError_t q = cudaEventQuery(ctx.batch_events[paced[k].batch]);
+                    if (q == cudaErrorNotReady) continue;
+                    if (q != cudaSuccess) return fail(std::string("rtc_render: cudaEventQuery: ") + cudaGetErrorString(q));
+                    if (int rc = issue_copy(paced[k], ctx.copy_stream[(size_t)paced[k].batch % (size_t)n_pipes])) return rc;
+                    issued[k] = 1;
+                    --left;
+                }
+            }
+            for (int p = 0; p < n_pipes; ++p) {
+                CU(cudaEventRecord(ctx.copy_done, ctx.copy_stream[p]));
+                CU(cudaStreamWaitEvent(st0, ctx.copy_done, 0));
+            }
+            CU(cudaMemcpyAsync(ctx.counters_host, ctx.counters, counter_bytes, cudaMemcpyDeviceToHost, st0));
+            CU(cudaMemcpyAsync(h_overflow, ctx.overflow, sizeof(int), cudaMemcpyDeviceToHost, st0));
+        }
         CU(cudaEventRecord(ctx.ev[1], st0));
     }
     CU(cudaStreamSynchronize(st0));

@@ -170,7 +170,8 @@ pub struct rtc_tuning {
     pub sah_leaf_weight_x100: i32,
     pub sah_bins: i32,
     pub sah_small_node: i32,
-    pub reserved: [i32; 15],
+    pub host_paced_copies: i32,
+    pub reserved: [i32; 14],
 }
 
 #[repr(C)]

@@ -50,7 +50,7 @@ def test_struct_layouts_match_a_c_compiler(built, tmp_path):
     assert sizes[1] == C.sizeof(R.Stats)
     assert sizes[8] == R.Stats.ms_trace.offset
     assert sizes[2] == 4 + 4 + 16 * 8 + 3 * 8
-    assert C.sizeof(R.Tuning) == 32 * 4  # rtc_tuning: 17 knobs + 15 reserved int32
+    assert C.sizeof(R.Tuning) == 32 * 4  # rtc_tuning: 18 knobs + 14 reserved int32
 
 
 def test_build_flags_live_in_the_former_padding_of_the_scene_descriptor(built, tmp_path, lib_types):

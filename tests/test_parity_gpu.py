@@ -203,7 +203,20 @@ def test_repeated_renders_are_identical_and_batches_do_not_matter(built):
             with R.tuning(no_graphs=1):  # launch by launch instead of the captured graph
                 c, _ = s.render(R.Opts())
         d, _ = s.render(R.Opts())
+        # copies issued by the calling thread once a batch's event has fired (rtc_tuning.host_paced_copies), into page-locked and
+        # into pageable memory, whole frame and a shard whose bands are scattered to their rows
+        frame, _ptr = R.pinned_array((90, 160, 3))
+        frame[:] = np.nan
+        with R.tuning(host_paced_copies=1, batches=7):
+            e, st_e = s.render(R.Opts(), out=frame)
+            g, _ = s.render(R.Opts())
+            from raytracer_challenge_b200 import sharding
+            full = np.full((90, 160, 3), np.nan)
+            for r in range(3):
+                s.render(sharding.band_opts(160, r, 3), out=full)
+        assert st_e.kernel_launches > 0
     assert np.array_equal(a, b) and np.array_equal(a, c) and np.array_equal(a, d)
+    assert np.array_equal(a, e) and np.array_equal(a, g) and np.array_equal(a, full)
 
 
 def test_ppm_through_the_host_api(built):
