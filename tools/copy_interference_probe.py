@@ -1,5 +1,7 @@
 """Does a device -> host copy running on a copy engine slow the wavefront kernels down?  Device-resident teapot frames with and
-without an unrelated 199 MB D2H copy loop on another stream (torch)."""
+without an unrelated 199 MB D2H copy loop on another stream (torch).
+(What it measures is NOT a kernel slowdown: the frame's own tiny read-back queues behind the copy backlog on the D2H engine —
+tools/copy_interference_probe4.py, profiles/README.md r02z.)"""
 import os, sys, threading, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

@@ -1,4 +1,4 @@
-"""What about a device -> host copy slows the wavefront kernels (tools/copy_interference_probe.py: ~35 %)?  The same PCIe
+"""What about a device -> host copy slows the wavefront kernels (tools/copy_interference_probe.py: +35 % frame time; probe4 shows it is the read-back queueing, not the kernels)?  The same PCIe
 traffic from (a) ONE 8 MB device region (always L2-resident) and (b) successive regions of a 200 MB buffer (every read a miss to
 HBM), (c) at half the rate (a sleep between chunks), (d) device -> device copies on the copy engine (no PCIe)."""
 import os, sys, threading, time
