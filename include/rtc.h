@@ -293,7 +293,7 @@ typedef struct rtc_tuning {
     int32_t no_fast_planes;   /* 1: always-tested planes go through the general primitive list, not the kernel parameters */
     int32_t no_plain_shade;   /* 1: scenes of plain-colour materials still use the pattern evaluator's kernel */
     int32_t two_pass;         /* 1: transparent hits re-walk the scene for their n1 / n2 crossing list (no one-pass collection) */
-    int32_t lbvh_leaf;        /* device-built BVH: items per leaf, 1..4 (default 1) */
+    int32_t lbvh_leaf;        /* device-built BVH: items per leaf, 1..4 (default 1; 2 when every item is a triangle) */
     int32_t bvh_builder;      /* 0: as rtc_scene_desc.build_flags says; 1: device (LBVH) whenever possible; 2: host (binned SAH) always */
     int32_t build_threads;    /* host BVH build: threads it may use (default: all cores; one process per GPU should pass cores / ranks) */
     int32_t sah_leaf_weight_x100, sah_bins, sah_small_node; /* host SAH build: leaf cost x 100 (default 300), bins 2..16 (16), exact-sweep size 2..8 (8) */
