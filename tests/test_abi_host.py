@@ -118,6 +118,9 @@ def test_host_scene_build(built, name):
         assert b["features"] & 1
     if name == "chapter14_title":  # 36 finite open cones: BVH items behind per-ray guards, only the backdrop plane is tested for every ray
         assert b["unbounded"] == 1 and b["bvh_items"] == 72 and b["cone_guards"] == 36 and (b["features"] & 4)
+    if name == "csg_cuts":  # CSG items enter the BVH under the box of what they can report: a cube cut by a half-space and a half-space
+        # AND a sphere are bounded items although one operand is a plane; only the floor is tested for every ray
+        assert b["csg_roots"] == 7 and b["unbounded"] == 1 and b["bvh_items"] == 8
     if name == "many_gates":  # every box above a finite cone is an exact gate; the 10 outer boxes that also hold a sphere still are
         assert b["gates_exact"] > 32 and b["cone_guards"] >= 1
     if name == "cone_slope":  # boxes above a finite cone stay exact gates: its single-root crossing may lie outside them
