@@ -364,27 +364,50 @@ void rtc_release_device_memory(int device) {
 
 // Every array of the flattened scene in one staging blob (256-byte aligned sections): one cudaMalloc + one copy per device.
 struct PackedScene {
-    std::vector<unsigned char> blob;
+    // Page-locked staging from the library's pool (rtc_alloc_host parks and reuses it): the upload is one DMA straight from
+    // it instead of the driver's bounce-buffer path for pageable memory, and nothing is zero-filled first.
+    struct Blob {
+        unsigned char* p = nullptr;
+        size_t used = 0, cap = 0;
+        bool pooled = false;
+        Blob() = default;
+        Blob(const Blob&) = delete;
+        Blob& operator=(const Blob&) = delete;
+        ~Blob() { if (pooled) rtc_free_host(p); else std::free(p); }
+        void allocate(size_t bytes) {
+            p = (unsigned char*)rtc_alloc_host(bytes);
+            pooled = p != nullptr;
+            if (!p) p = (unsigned char*)std::malloc(bytes);
+            cap = p ? bytes : 0;
+        }
+        unsigned char* data() const { return p; }
+        size_t size() const { return used; }
+    } blob;
     size_t o_prims, o_xforms, o_matinvs, o_tri_pe, o_tri_n, o_ranges, o_materials, o_patterns, o_lights, o_gates, o_bvh, o_leaf_items,
         o_leaf_tri, o_unbounded, o_csg_ops, o_csg_roots, o_guards;
     // device-side BVH build only (HostScene::device_build): staging + scratch sections
     size_t upload_bytes = 0, total_bytes = 0;  // host -> device copy / arena size
     size_t o_item_ids = 0, o_box32 = 0, o_keys = 0, o_keys_alt = 0, o_radix_hist = 0, o_child = 0, o_parent = 0, o_range = 0, o_nbox = 0, o_counter = 0, o_dense = 0, o_result = 0;
 };
-static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
+static bool pack_scene(rtchost::HostScene& h, PackedScene& p) {
+    bool fits = true;
     auto place = [&](const void* src, size_t bytes) -> size_t {
-        const size_t off = (p.blob.size() + 255) & ~(size_t)255;
-        p.blob.resize(off + std::max<size_t>(bytes, 16));
-        if (bytes) std::memcpy(p.blob.data() + off, src, bytes);
+        const size_t off = (p.blob.used + 255) & ~(size_t)255;
+        const size_t end = off + std::max<size_t>(bytes, 16);
+        if (end > p.blob.cap) { fits = false; return off; }  // (the capacity below is the sum of the padded sections)
+        if (bytes) std::memcpy(p.blob.p + off, src, bytes);
+        else std::memset(p.blob.p + off, 0, 16);
+        p.blob.used = end;
         return off;
     };
 #define PLACE(vec) place((vec).data(), (vec).size() * sizeof((vec)[0]))
 #define BYTES(vec) (((vec).size() * sizeof((vec)[0]) + 16 + 255) & ~(size_t)255)
-    p.blob.reserve(BYTES(h.prims) + BYTES(h.xforms) + BYTES(h.matinvs) + BYTES(h.tri_pe) + BYTES(h.tri_n) + BYTES(h.ranges) + BYTES(h.materials) +
+    p.blob.allocate(BYTES(h.prims) + BYTES(h.xforms) + BYTES(h.matinvs) + BYTES(h.tri_pe) + BYTES(h.tri_n) + BYTES(h.ranges) + BYTES(h.materials) +
                    BYTES(h.patterns) + BYTES(h.lights) + BYTES(h.gates) + BYTES(h.bvh) + BYTES(h.leaf_items) + BYTES(h.leaf_tri) + BYTES(h.unbounded) +
                    BYTES(h.csg_ops) + BYTES(h.csg_roots) + BYTES(h.guards) + 4096 +
-                   (h.device_build ? BYTES(h.item_ids) + BYTES(h.item_box32) + 4096 : 0));  // one allocation: no regrow-and-copy per section
+                   (h.device_build ? BYTES(h.item_ids) + BYTES(h.item_box32) + 4096 : 0));  // one allocation for every section
 #undef BYTES
+    if (!p.blob.p) return false;
     p.o_prims = PLACE(h.prims); p.o_xforms = PLACE(h.xforms); p.o_matinvs = PLACE(h.matinvs); p.o_tri_pe = PLACE(h.tri_pe);
     p.o_tri_n = PLACE(h.tri_n); p.o_ranges = PLACE(h.ranges); p.o_materials = PLACE(h.materials); p.o_patterns = PLACE(h.patterns);
     p.o_lights = PLACE(h.lights); p.o_gates = PLACE(h.gates); p.o_bvh = PLACE(h.bvh); p.o_leaf_items = PLACE(h.leaf_items);
@@ -422,6 +445,7 @@ static void pack_scene(rtchost::HostScene& h, PackedScene& p) {
     }
 #undef PLACE
     h.device_bytes = (int64_t)p.total_bytes;
+    return fits;
 }
 
 // Device half of rtc_scene_create: arena (reused from the device context when one is parked there), copy, pointers.
@@ -573,7 +597,8 @@ int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n
     if (!err.empty()) return fail("rtc_scene_create: " + err);
     const auto t_build1 = std::chrono::steady_clock::now();
     PackedScene packed;
-    pack_scene(*host, packed);
+    cudaSetDevice(devices[0]);  // (the staging buffer is page-locked by the first device's context, portable to the others)
+    if (!pack_scene(*host, packed)) return fail("rtc_scene_create: out of host memory for the upload staging");
     std::vector<std::unique_ptr<rtc_scene>> made((size_t)n);
     std::vector<std::string> errors((size_t)n);
     std::vector<int> rcs((size_t)n, 0);

@@ -145,6 +145,46 @@ float f32_up(double x) {
     return f;
 }
 
+// n records of 8 doubles (lo.xyz, 0, hi.xyz, 0) -> 8 floats each, the first four rounded towards -inf and the last four
+// towards +inf by the conversion instruction itself (MXCSR rounding control).  The compiler does not model MXCSR as an input
+// of cvtpd2ps, so the conversions sit between two compiler barriers and only touch memory.
+__attribute__((noinline)) void convert_directed(const double* in, float* out, size_t n) {
+    const unsigned saved = _mm_getcsr();
+    for (int pass = 0; pass < 2; ++pass) {
+        _mm_setcsr((saved & ~0x6000u) | (pass == 0 ? 0x2000u : 0x4000u));  // round down, then round up
+        __asm__ volatile("" ::: "memory");
+        for (size_t i = 0; i < n; ++i) {
+            const double* q = in + i * 8 + pass * 4;
+            const __m128 a = _mm_cvtpd_ps(_mm_loadu_pd(q)), b = _mm_cvtpd_ps(_mm_loadu_pd(q + 2));
+            _mm_storeu_ps(out + i * 8 + pass * 4, _mm_movelh_ps(a, b));
+        }
+        __asm__ volatile("" ::: "memory");
+    }
+    _mm_setcsr(saved);
+}
+
+// Checked once per process against the scalar f32_down / f32_up on values that round, values that are exact, both signs,
+// the float range's ends and the denormal range: should a compiler ever move the conversions out of their rounding-mode
+// bracket, the staging falls back to the scalar form instead of handing the device inward-rounded boxes.
+bool directed_conversion_is_exact() {
+    static const bool ok = [] {
+        const double v[16] = {0.1, -0.1, 1.0, -1.0, 1.0 + 1e-12, -(1.0 + 1e-12), 3.4028234663852886e38, 3.5e38,
+                              -3.5e38, 1e-46, -1e-46, 0.0, 123456.789, -98765.4321, 1e-39, -1e-39};
+        double in[32];
+        float got[32];
+        for (int r = 0; r < 4; ++r)
+            for (int k = 0; k < 4; ++k) { in[r * 8 + k] = v[r * 4 + k]; in[r * 8 + 4 + k] = v[r * 4 + k]; }
+        convert_directed(in, got, 4);
+        for (int r = 0; r < 4; ++r)
+            for (int k = 0; k < 4; ++k) {
+                const float lo = f32_down(v[r * 4 + k]), hi = f32_up(v[r * 4 + k]);
+                if (std::memcmp(&got[r * 8 + k], &lo, 4) != 0 || std::memcmp(&got[r * 8 + 4 + k], &hi, 4) != 0) return false;
+            }
+        return true;
+    }();
+    return ok;
+}
+
 // ---- binned-SAH BVH2 over item boxes ------------------------------------------------------
 // The build runs on the boxes the device will test: per item the fp32 box, padded and rounded outwards.  Rounding
 // outwards is monotone, so the union of the rounded item boxes IS the rounded union — a node's stored box is the
@@ -579,6 +619,8 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
     std::vector<int> visited_node((size_t)d.n_nodes, 0), visited_prim((size_t)d.n_prims, 0);
     std::vector<Box> item_boxes;   // per BVH item
     std::vector<int32_t> item_ids; // per BVH item: prim index or ~csg index
+    item_boxes.reserve((size_t)d.n_prims);
+    item_ids.reserve((size_t)d.n_prims);
     int next_prim = 0;             // primitives must appear in depth-first order
     std::string err;
 
@@ -758,19 +800,25 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
             // host build would use, and the leaf records in item order.
             out.device_build = 1;
             out.item_box32.resize((size_t)n_items * 8);
+            // f32_down / f32_up of every padded bound, two at a time: the double -> float conversion itself rounds towards
+            // -inf / +inf when MXCSR says so (identical values: test_staged_item_boxes_round_outwards)
+            std::vector<double> padded((size_t)n_items * 8);
             for (int i = 0; i < n_items; ++i) {
-                float* b = &out.item_box32[(size_t)i * 8];
-                for (int k = 0; k < 3; ++k) {
-                    b[k] = f32_down(item_boxes[(size_t)i].lo[k] - pad);
-                    b[4 + k] = f32_up(item_boxes[(size_t)i].hi[k] + pad);
-                }
-                b[3] = 0.0f;
-                b[7] = 0.0f;
+                double* q = &padded[(size_t)i * 8];
+                for (int k = 0; k < 3; ++k) { q[k] = item_boxes[(size_t)i].lo[k] - pad; q[4 + k] = item_boxes[(size_t)i].hi[k] + pad; }
+                q[3] = 0.0;
+                q[7] = 0.0;
+            }
+            if (directed_conversion_is_exact()) {
+                convert_directed(padded.data(), out.item_box32.data(), (size_t)n_items);
+            } else {
+                for (size_t i = 0; i < (size_t)n_items * 8; ++i) out.item_box32[i] = (i & 4) ? f32_up(padded[i]) : f32_down(padded[i]);
             }
             out.item_ids = std::move(item_ids);
             out.bvh_root = 0;
             out.bvh_depth = 0;  // known after the device build
-            if (trace) std::fprintf(stderr, "build_host_scene: prims %.3f ms, group tree %.3f ms, device-build staging %.3f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, now()));
+            if (trace) std::fprintf(stderr, "build_host_scene: prims %.3f ms, group tree %.3f ms, device-build staging %.3f ms%s\n", ms(t0, t1), ms(t1, t2), ms(t2, now()),
+                                    directed_conversion_is_exact() ? "" : " (scalar rounding: the directed conversion failed its self-check)");
             return "";
         }
         Builder bld(item_boxes, pad, tune);
