@@ -597,8 +597,12 @@ int rtc_scene_create_multi(const rtc_scene_desc* desc, const int* devices, int n
     if (!err.empty()) return fail("rtc_scene_create: " + err);
     const auto t_build1 = std::chrono::steady_clock::now();
     PackedScene packed;
+    int caller_device = -1;
+    cudaGetDevice(&caller_device);
     cudaSetDevice(devices[0]);  // (the staging buffer is page-locked by the first device's context, portable to the others)
-    if (!pack_scene(*host, packed)) return fail("rtc_scene_create: out of host memory for the upload staging");
+    const bool packed_ok = pack_scene(*host, packed);
+    if (n > 1 && caller_device >= 0) cudaSetDevice(caller_device);  // (n = 1 renders from this thread: upload_scene selects the device anyway)
+    if (!packed_ok) return fail("rtc_scene_create: out of host memory for the upload staging");
     std::vector<std::unique_ptr<rtc_scene>> made((size_t)n);
     std::vector<std::string> errors((size_t)n);
     std::vector<int> rcs((size_t)n, 0);
