@@ -310,3 +310,21 @@ def test_rust_ffi_functions_and_constants_mirror_the_header():
     assert "bvh_build.cu" in names and "render_kernels.cu" in names
     for n in names:
         assert os.path.exists(os.path.join(ROOT, "raytracer_challenge_b200", "csrc", n)), n
+
+
+def test_staged_item_boxes_round_outwards(built):
+    """The device-build staging rounds the padded item boxes outwards with the double -> float conversion itself (MXCSR
+    rounding control, scene_build.cpp: convert_directed) and checks that against the scalar f32_down / f32_up once per
+    process; a build whose compiler broke the bracket would fall back to the scalar form and say so in the RTC_TRACE line."""
+    import os
+    import subprocess
+    import sys
+
+    code = ("import raytracer_challenge_b200 as R\n"
+            "R.set_tuning(bvh_builder=R.BVH_DEVICE)\n"
+            "s = R.Session('teapot', 64, 36, device=-1); print(s.build_stats['bvh_items']); s.close()\n")
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, RTC_TRACE="1", PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))),
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "6320" in r.stdout
+    assert "device-build staging" in r.stderr and "scalar rounding" not in r.stderr
