@@ -25,12 +25,15 @@ struct Box {
     double lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF};
     bool bounded = true;  // false: must be tested for every ray
     bool exact = true;    // false: holds a finite cone, whose single-root crossing may lie outside (see rtcdev::ConeGuard)
+    bool closed = true;   // everything below is a closed solid: a line crosses its surface an even number of times (sphere, cube,
+                          // capped finite cylinder), so "inside" as filter_by_group counts it ends where the solid ends
     void add(const double p[3]) {
         for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); }
     }
     void add(const Box& b) {
         if (!b.bounded) bounded = false;
         if (!b.exact) exact = false;
+        if (!b.closed) closed = false;
         for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], b.lo[k]); hi[k] = std::max(hi[k], b.hi[k]); }
     }
     bool empty() const { return lo[0] > hi[0]; }
@@ -72,6 +75,7 @@ void xf_point(const double m[12], const double p[3], double out[3]) {
 // fwd: object -> world (invert_affine of p.transform_inv), or null if that matrix is singular
 Box prim_bounds(const rtc_prim& p, const double* fwd) {
     Box b;
+    b.closed = p.kind == RTC_SPHERE || p.kind == RTC_CUBE || (p.kind == RTC_CYLINDER && p.closed && std::isfinite(p.min) && std::isfinite(p.max));
     if (!fwd) { b.bounded = false; return b; }
     double olo[3], ohi[3];
     switch (p.kind) {
@@ -718,17 +722,23 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
             out.csg_ops.push_back({rtcdev::OP_END, nd.kind, left_b, left_e});
             if (skippable) {
                 out.csg_ops[skip_at].a = (int32_t)(out.csg_ops.size() - 1 - skip_at);  // from the skip op to this group's OP_END
-                // (boxes of finite cones are not exact — see ConeGuard — so a subtree that holds one keeps the union)
-                if (child_eff[0].exact && child_eff[1].exact) {
-                    Box t = child_eff[0];
-                    if (nd.kind == RTC_INTERSECTION) {
-                        if (!t.bounded) t = child_eff[1];
-                        else if (child_eff[1].bounded)
-                            for (int k = 0; k < 3; ++k) { t.lo[k] = std::max(t.lo[k], child_eff[1].lo[k]); t.hi[k] = std::min(t.hi[k], child_eff[1].hi[k]); }
+                // Tightening needs CLOSED operands.  filter_by_group keeps a right crossing while "inside the left operand", and
+                // inside is a parity count: a left operand a line can cross ONCE (a plane, a triangle, an open cylinder — entered
+                // through the wall, left through the open end) stays "entered" to the end of the line, so right crossings far
+                // outside its box are reported (fuzz:20, 38, 57 ... differed from brute force before this rule).  With a closed
+                // left operand everything a Difference reports lies in the left box; an Intersection reports inside every
+                // closed operand's box.  (Boxes of finite cones are not exact — see ConeGuard — so a subtree that holds one keeps
+                // the union too.)
+                const bool c0 = child_eff[0].closed && child_eff[0].bounded, c1 = child_eff[1].closed && child_eff[1].bounded;
+                if (child_eff[0].exact && child_eff[1].exact && (c0 || (nd.kind == RTC_INTERSECTION && c1))) {
+                    Box t = c0 ? child_eff[0] : child_eff[1];
+                    if (nd.kind == RTC_INTERSECTION && c0 && c1) {
+                        for (int k = 0; k < 3; ++k) { t.lo[k] = std::max(t.lo[k], child_eff[1].lo[k]); t.hi[k] = std::min(t.hi[k], child_eff[1].hi[k]); }
                         bool overlap = true;
                         for (int k = 0; k < 3; ++k) overlap = overlap && t.lo[k] <= t.hi[k];
                         if (!overlap) t = child_eff[0];  // disjoint operands: nothing can be reported; any valid box will do
                     }
+                    t.closed = child_eff[0].closed && child_eff[1].closed;
                     eff = t;
                 }
             }

@@ -33,7 +33,7 @@ CASES = [
     ("csg_cuts", 128, 72),              # CSG items under the box of what they can report; right operands skipped when the left reports nothing
     ("many_gates", 96, 54),             # 80 group boxes over finite cones: 64-bit gate masks, slots assigned after the subtree walk
     ("no_shadow_flat", 96, 54),         # casts_shadow = false in front of a casting shape (src/world.rs:40-47); flat triangles
-] + [(f"fuzz:{s}", 96, 54) for s in range(1, 13)]
+] + [(f"fuzz:{s}", 96, 54) for s in list(range(1, 13)) + [20, 38, 57, 80, 168, 192]]  # (20 ...: CSG groups with an OPEN left operand — tools/fuzz_sweep.py)
 
 
 @pytest.mark.parametrize("name,w,h", CASES)
