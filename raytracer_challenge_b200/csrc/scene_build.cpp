@@ -631,7 +631,7 @@ std::string build_host_scene(const rtc_scene_desc& d, HostScene& out, const rtc_
     // Returns the bounds of the subtree as the reference computes them (the union of everything below); fills prim range
     // [pb, pe) and `eff`, the box that holds every crossing the subtree can REPORT: for a Difference that is the left
     // operand's box, for an Intersection the overlap of the two (a crossing of the right operand survives the filter of
-    // src/shape.rs:230-269 only inside the left solid, and vice versa).  A top-level CSG item enters the BVH with `eff`:
+    // src/shape.rs:230-269 only inside the left solid, and vice versa) — for CLOSED operands only, see below.  A top-level CSG item enters the BVH with `eff`:
     // a ray that misses it but hits the reference's box evaluates, in the reference, to the empty list.
     std::function<Box(int, uint32_t, int, int, int&, int&, Box&)> walk;
     // csg_root: index into out.csg_roots of the enclosing top-level CSG item, or -1.
